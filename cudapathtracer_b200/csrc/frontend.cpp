@@ -1,0 +1,450 @@
+// frontend.cpp — host front end kept from the reference so the core is a drop-in:
+//   .rendertron config parser   (objects.cuh:844-943, accepts both spellings of the radius key)
+//   OBJ loader                  (main.cu:936-1068: v/vt/vn/f, fan triangulation, area cull, light list)
+//   24-entry material table     (main.cu:397-467)
+//   camera                      (objects.cuh:221-266, 309-325)
+//   BMP texture reader / BMP + PFM writers with the ACES-fit tonemap (imageUtil.cu:69-100, 144-232)
+// Differences from the reference, all deliberate: Material fields the reference leaves indeterminate are
+// zero; faces without vn/vt get a flat face normal / a zero uv instead of index -1.
+#include "scene.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+namespace nv {
+
+static std::string trim(const std::string& s) {
+    size_t a = s.find_first_not_of(" \t\r\n");
+    if (a == std::string::npos) return s;
+    size_t b = s.find_last_not_of(" \t\r\n");
+    return s.substr(a, b - a + 1);
+}
+static bool parseBool(std::string v) {
+    std::transform(v.begin(), v.end(), v.begin(), ::tolower);
+    return v == "true";
+}
+static void parseVec3(const std::string& v, float out[3]) {
+    std::stringstream ss(v);
+    out[0] = out[1] = out[2] = 0.f;
+    ss >> out[0] >> out[1] >> out[2];
+}
+
+struct MeshCfg { std::string path; float mult = 0.f; float color[3] = {0, 0, 0}; int materialID = 0; };
+
+int matchIntegrator(const std::string& name) {   // objects.cuh:583-593
+    if (name == "UNIDIRECTIONAL") return NOVUM_UNIDIRECTIONAL;
+    if (name == "BIDIRECTIONAL" || name == "BDPT") return NOVUM_BIDIRECTIONAL;
+    if (name == "NAIVE_UNIDIRECTIONAL") return NOVUM_NAIVE_UNIDIRECTIONAL;
+    if (name == "VCM") return NOVUM_VCM;
+    if (name == "SPPM") return NOVUM_SPPM;
+    return -1;
+}
+
+int loadConfigFull(const char* path, NovumRenderConfig* cfg, std::vector<MeshCfg>* meshes) {
+    std::ifstream file(path);
+    if (!file.is_open()) return NOVUM_E_IO;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->integrator = -1;
+    std::string line;
+    bool inMeshes = false;
+    try {
+    while (std::getline(file, line)) {
+        line = trim(line);
+        if (line.empty()) continue;
+        if (line.rfind("Meshes", 0) == 0) { inMeshes = true; continue; }
+        if (inMeshes) {   // path; multiplier * (r, g, b); materialID
+            MeshCfg m;
+            std::stringstream ss(line);
+            std::string seg;
+            if (std::getline(ss, seg, ';')) m.path = trim(seg);
+            if (std::getline(ss, seg, ';')) {
+                std::string e = trim(seg);
+                size_t star = e.find('*'), op = e.find('('), cp = e.find(')');
+                if (star != std::string::npos && op != std::string::npos) {
+                    m.mult = std::stof(e.substr(0, star));
+                    std::string vec = e.substr(op + 1, cp - op - 1);
+                    std::replace(vec.begin(), vec.end(), ',', ' ');
+                    parseVec3(vec, m.color);
+                }
+            }
+            if (std::getline(ss, seg, ';')) m.materialID = std::stoi(trim(seg));
+            if (meshes) meshes->push_back(m);
+            cfg->numMeshes++;
+            continue;
+        }
+        size_t d = line.find(':');
+        if (d == std::string::npos) continue;
+        std::string key = trim(line.substr(0, d)), val = trim(line.substr(d + 1));
+        if (val.empty()) continue;
+        if (key == "width") cfg->width = std::stoi(val);
+        else if (key == "height") cfg->height = std::stoi(val);
+        else if (key == "Integrator") cfg->integrator = matchIntegrator(val);
+        else if (key == "Name") { strncpy(cfg->name, val.c_str(), sizeof(cfg->name) - 1); }
+        else if (key == "Sample Count") cfg->sampleCount = std::stoi(val);
+        else if (key == "Unidirectional Max Depth") cfg->maxDepth = std::stoi(val);
+        else if (key == "BVH recommended leaf size") cfg->bvhLeafSize = std::stoi(val);
+        else if (key == "Bidirectional Eye Depth") cfg->bdptEyeDepth = std::stoi(val);
+        else if (key == "Bidirectional Light Depth") cfg->bdptLightDepth = std::stoi(val);
+        else if (key == "BDPT_LIGHTTRACE") cfg->bdptLightTrace = parseBool(val);
+        else if (key == "BDPT_NEE") cfg->bdptNee = parseBool(val);
+        else if (key == "BDPT_NAIVE") cfg->bdptNaive = parseBool(val);
+        else if (key == "BDPT_CONNECTION") cfg->bdptConnection = parseBool(val);
+        else if (key == "BDPT_DRAWPATH") cfg->bdptDrawPath = parseBool(val);
+        else if (key == "BDPT_DOMIS") cfg->bdptDoMis = parseBool(val);
+        else if (key == "BDPT_PAINTWEIGHT") cfg->bdptPaintWeight = parseBool(val);
+        else if (key == "Pinhole Camera") cfg->pinholeCamera = parseBool(val);
+        else if (key == "SAMPLE_ENVIRONMENT") cfg->sampleEnvironment = parseBool(val);
+        else if (key == "Post Process") cfg->postProcess = parseBool(val);
+        else if (key == "VCM_DOMERGE") cfg->vcmDoMerge = parseBool(val);
+        else if (key == "Camera Position") parseVec3(val, cfg->camPos);
+        else if (key == "Camera Rotation") parseVec3(val, cfg->camRot);
+        else if (key == "Camera FOV") cfg->camFov = std::stof(val);
+        else if (key == "Camera Apeture") cfg->camApeture = std::stof(val);
+        else if (key == "Camera FocalDist") cfg->camFocalDist = std::stof(val);
+        else if (key == "VCM Merge Radius Power Factor") cfg->vcmMergeConst = std::stof(val);
+        else if (key == "VCM Initial Merge Radius Multiplier" || key == "VCM Initial Merge Radius Multipler")
+            cfg->vcmInitialMergeRadiusMultiplier = std::stof(val);   // the shipped config misspells the key (config.rendertron:27)
+    }
+    } catch (...) { return NOVUM_E_IO; }
+    if (cfg->integrator == NOVUM_SPPM) {   // main.cu:314-333
+        cfg->bdptConnection = cfg->bdptNaive = cfg->bdptNee = cfg->bdptLightTrace = cfg->bdptDoMis = 0;
+        cfg->vcmDoMerge = 1; cfg->doSPPM = 1;
+    }
+    return 0;
+}
+
+// ---- material table (main.cu:397-467); every field the factories leave unset is zero ---------------
+static NovumMaterial matBase(int type) {
+    NovumMaterial m; memset(&m, 0, sizeof(m));
+    m.type = type;
+    m.albedo = {0.8f, 0.8f, 0.8f, 0.f}; m.roughness = 0.5f; m.ior = 1.5f; m.metallic = 0.f; m.specular = 1.f;   // objects.cuh:640-643
+    return m;
+}
+static NovumMaterial matDiffuse(float r, float g, float b) {   // objects.cuh:645-657
+    NovumMaterial m = matBase(NOVUM_MAT_DIFFUSE);
+    m.albedo = {r, g, b, 0.f}; m.roughness = 1.0f;
+    return m;
+}
+static NovumMaterial matDiffuseTex(int start, int w, int h) {   // objects.cuh:659-675
+    NovumMaterial m = matBase(NOVUM_MAT_DIFFUSE);
+    m.hasTexture = (w > 0 && h > 0) ? 1 : 0; m.startInd = start; m.width = w; m.height = h; m.roughness = 1.0f;
+    return m;
+}
+static NovumMaterial matMetal(const float eta[3], const float k[3], float rough) {   // objects.cuh:677-693
+    NovumMaterial m = matBase(NOVUM_MAT_METAL);
+    m.eta = {eta[0], eta[1], eta[2], 0.f}; m.k = {k[0], k[1], k[2], 0.f}; m.roughness = rough;
+    m.albedo = {1.f, 1.f, 1.f, 0.f}; m.metallic = 1.0f;
+    return m;
+}
+static NovumMaterial matDielectric(float ior, float ax, float ay, float az, int pri) {   // objects.cuh:695-710
+    NovumMaterial m = matBase(NOVUM_MAT_SMOOTHDIELECTRIC);
+    m.ior = ior; m.albedo = {1.f, 1.f, 1.f, 0.f}; m.priority = pri; m.isSpecular = 1; m.boundary = 1;
+    m.absorption = {ax, ay, az, 0.f};
+    return m;
+}
+static NovumMaterial matLeaf(int start, int w, int h, float ior, float rough, float trans) {   // objects.cuh:726-749
+    NovumMaterial m = matBase(NOVUM_MAT_LEAF);
+    m.hasTexture = (w > 0 && h > 0) ? 1 : 0; m.ior = ior; m.roughness = rough; m.albedo = {0.22f, 0.75f, 0.28f, 0.f};
+    m.transmission = trans; m.startInd = start; m.width = w; m.height = h; m.thinWalled = 1;
+    return m;
+}
+
+void buildMaterialTable(NovumMaterial* out, const int texStart[4], const int texW[4], const int texH[4]) {
+    const float etaSteel[3] = {0.14f, 0.16f, 0.13f}, etaGold[3] = {0.17f, 0.35f, 1.5f};
+    out[0] = matDielectric(1.0f, 0, 0, 0, 99);                       // air
+    out[1] = matDiffuse(0.4f, 0.4f, 0.8f);
+    out[2] = matDiffuse(0.9f, 0.9f, 0.9f);
+    out[3] = matDiffuse(0.2f, 0.6f, 0.6f);
+    out[4] = matMetal(etaGold, etaGold, 0.05f);                      // k = eta, as in main.cu:419
+    out[5] = matDielectric(1.5f, 0, 0, 0, 1);                        // glass
+    out[6] = matDiffuse(0.90f, 0.1f, 0.1f);
+    out[7] = matMetal(etaSteel, etaSteel, 0.15f);
+    out[8] = matDielectric(1.333f, 2.5f * 0.180f, 2.5f * 1.5f, 2.5f * 2.996f, 2);   // tea
+    out[9] = matDielectric(1.31f, 0.2f, 0.2f, 0.2f, 0);             // ice
+    out[10] = matDielectric(1.333f, 0, 0, 0, 2);                     // water
+    out[11] = matDiffuseTex(texStart[0], texW[0], texH[0]);
+    out[12] = matDiffuseTex(texStart[1], texW[1], texH[1]);
+    out[13] = matLeaf(texStart[2], texW[2], texH[2], 1.5f, 0.10f, 0.15f);
+    out[14] = matDiffuse(0.90f, 0.9f, 0.83f);
+    out[15] = matDiffuse(0.4f, 0.4f, 1.00f);
+    out[16] = matLeaf(texStart[3], texW[3], texH[3], 1.5f, 0.8f, 0.6f);
+    out[17] = matDiffuse(0.8f, 0.8f, 0.8f);
+    out[18] = matDielectric(2.42f, 0, 0, 0, 1);                      // diamond
+    out[19] = matBase(NOVUM_MAT_DELTAMIRROR); out[19].isSpecular = 1;
+    out[20] = matDiffuse(0.0f, 0.0f, 0.0f);
+    out[21] = matDiffuse(0.95f, 0.95f, 0.95f);
+    out[22] = matDiffuse(0.5f, 0.5f, 0.5f);
+    out[23] = matDiffuse(0.1f, 0.9f, 0.1f);
+}
+
+// ---- camera (objects.cuh:221-266, 309-325) ------------------------------------------------------------
+static void rotX(float v[3], float a) { float c = cosf(a), s = sinf(a); float y = v[1] * c - v[2] * s, z = v[1] * s + v[2] * c; v[1] = y; v[2] = z; }
+static void rotY(float v[3], float a) { float c = cosf(a), s = sinf(a); float x = v[0] * c + v[2] * s, z = -v[0] * s + v[2] * c; v[0] = x; v[2] = z; }
+static void rotZ(float v[3], float a) { float c = cosf(a), s = sinf(a); float x = v[0] * c - v[1] * s, y = v[0] * s + v[1] * c; v[0] = x; v[1] = y; }
+static NovumFloat4 rotAll(float x, float y, float z, const NovumCamera& c) {
+    float v[3] = {x, y, z};
+    rotX(v, c.xRot); rotY(v, c.yRot); rotZ(v, c.zRot);
+    float il = 1.0f / sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    return {v[0] * il, v[1] * il, v[2] * il, 0.f};
+}
+
+void makeCamera(const NovumRenderConfig* cfg, NovumCamera* c) {
+    memset(c, 0, sizeof(*c));
+    c->w = cfg->width; c->h = cfg->height;
+    c->cameraOrigin = {cfg->camPos[0], cfg->camPos[1], cfg->camPos[2], 0.f};
+    c->fovScale = tanf((cfg->camFov * 0.5f) * (3.141592f / 180.0f));
+    c->xRot = cfg->camRot[0] * (3.14159265f / 180.0f);
+    c->yRot = cfg->camRot[1] * (3.14159265f / 180.0f);
+    c->zRot = cfg->camRot[2] * (3.14159265f / 180.0f);
+    if (cfg->pinholeCamera) { c->aperture = 0.000001f; c->focalDist = 1.0f / cfg->camFov; }   // objects.cuh:235-236
+    else { c->aperture = cfg->camApeture; c->focalDist = cfg->camFocalDist; }
+    c->antiAliasJitterDist = 2.0f;
+    c->forward = rotAll(0.f, 0.f, -1.f, *c);
+    c->right = rotAll(1.f, 0.f, 0.f, *c);
+    c->up = rotAll(0.f, 1.f, 0.f, *c);
+}
+
+// ---- OBJ (main.cu:936-1068) ---------------------------------------------------------------------------
+struct HostMesh {
+    std::vector<NovumFloat4> pos, nrm;
+    std::vector<NovumFloat2> uv;
+    std::vector<NovumTriangle> tris;
+    int numLights = 0;
+};
+
+int loadObj(const std::string& file, HostMesh& M, const float emission[3], int materialID, float yOffset) {
+    std::ifstream in(file);
+    if (!in.is_open()) return NOVUM_E_IO;
+    int startIndex = (int)M.pos.size(), nStart = (int)M.nrm.size(), uvStart = (int)M.uv.size();
+    bool isLight = emission[0] * emission[0] + emission[1] * emission[1] + emission[2] * emission[2] > 0.f;
+    int sharedZeroUV = -1;
+    std::string line;
+    std::vector<int> vi, ti, ni;
+    while (std::getline(in, line)) {
+        if (line.empty() || line[0] == '#' || line[0] == 's') continue;
+        const char* p = line.c_str();
+        if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) {
+            double x = 0, y = 0, z = 0;
+            sscanf(p + 2, "%lf %lf %lf", &x, &y, &z);
+            NovumFloat4 q = {(float)x, (float)y, (float)z, 0.f};
+            q.y = q.y + yOffset;
+            M.pos.push_back(q);
+        } else if (p[0] == 'v' && p[1] == 't') {
+            double u = 0, v = 0;
+            sscanf(p + 3, "%lf %lf", &u, &v);
+            M.uv.push_back({(float)u, 1.0f - (float)v});
+        } else if (p[0] == 'v' && p[1] == 'n') {
+            double x = 0, y = 0, z = 0;
+            int got = sscanf(p + 3, "%lf %lf %lf", &x, &y, &z);
+            NovumFloat4 n = {(float)x, (float)y, (float)z, 0.f};
+            if (got != 3 || std::isnan(x) || std::isnan(y) || std::isnan(z) || n.x * n.x + n.y * n.y + n.z * n.z < 1e-12f)
+                n = {0.f, 1.f, 0.f, 0.f};
+            M.nrm.push_back(n);
+        } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
+            vi.clear(); ti.clear(); ni.clear();
+            std::istringstream iss(line.substr(2));
+            std::string tok;
+            while (iss >> tok) {
+                int a = 0, b = 0, c = 0;
+                const char* s = tok.c_str();
+                a = atoi(s);
+                const char* s1 = strchr(s, '/');
+                if (s1) { if (s1[1] != '/' && s1[1] != 0) b = atoi(s1 + 1); const char* s2 = strchr(s1 + 1, '/'); if (s2 && s2[1]) c = atoi(s2 + 1); }
+                if (a != 0) vi.push_back(a - 1);
+                if (b != 0) ti.push_back(b - 1);
+                if (c != 0) ni.push_back(c - 1);
+            }
+            bool hasUV = ti.size() == vi.size(), hasN = ni.size() == vi.size();
+            int n = (int)vi.size();
+            for (int i = 1; i < n - 1; ++i) {
+                int i0 = vi[0] + startIndex, i1 = vi[i] + startIndex, i2 = vi[i + 1] + startIndex;
+                if (i0 < 0 || i1 < 0 || i2 < 0 || i0 >= (int)M.pos.size() || i1 >= (int)M.pos.size() || i2 >= (int)M.pos.size()) continue;
+                const NovumFloat4 &p0 = M.pos[i0], &p1 = M.pos[i1], &p2 = M.pos[i2];
+                float e1[3] = {p1.x - p0.x, p1.y - p0.y, p1.z - p0.z}, e2[3] = {p2.x - p0.x, p2.y - p0.y, p2.z - p0.z};
+                float cp[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+                float areaSq = cp[0] * cp[0] + cp[1] * cp[1] + cp[2] * cp[2];
+                if (areaSq < 1e-18f) continue;
+                NovumTriangle t; memset(&t, 0, sizeof(t));
+                t.aInd = i0; t.bInd = i1; t.cInd = i2;
+                if (hasN) { t.naInd = ni[0] + nStart; t.nbInd = ni[i] + nStart; t.ncInd = ni[i + 1] + nStart; }
+                else {   // the reference would index normals[-1]; use the face normal instead
+                    float il = 1.0f / sqrtf(areaSq);
+                    M.nrm.push_back({cp[0] * il, cp[1] * il, cp[2] * il, 0.f});
+                    t.naInd = t.nbInd = t.ncInd = (int)M.nrm.size() - 1;
+                }
+                if (hasUV) { t.uvaInd = ti[0] + uvStart; t.uvbInd = ti[i] + uvStart; t.uvcInd = ti[i + 1] + uvStart; }
+                else {
+                    if (sharedZeroUV < 0) { M.uv.push_back({0.f, 0.f}); sharedZeroUV = (int)M.uv.size() - 1; }
+                    t.uvaInd = t.uvbInd = t.uvcInd = sharedZeroUV;
+                }
+                t.materialID = materialID;
+                t.emission = {emission[0], emission[1], emission[2], 0.f};
+                t.lightInd = isLight ? M.numLights : -51;
+                t.triInd = (int)M.tris.size();
+                M.tris.push_back(t);
+                if (isLight) M.numLights++;
+            }
+        }
+    }
+    return 0;
+}
+
+// ---- images -------------------------------------------------------------------------------------------
+#pragma pack(push, 1)
+struct BmpFileHeader { uint16_t type; uint32_t size; uint16_t r1, r2; uint32_t offBits; };
+struct BmpInfoHeader { uint32_t size; int32_t w, h; uint16_t planes, bitCount; uint32_t compression, sizeImage; int32_t xppm, yppm; uint32_t clrUsed, clrImportant; };
+#pragma pack(pop)
+
+bool loadBmpTexture(const std::string& file, std::vector<NovumFloat4>& px, int& w, int& h) {   // imageUtil.cu:144-190
+    w = h = 0;
+    std::ifstream in(file, std::ios::binary);
+    if (!in.is_open()) return false;
+    BmpFileHeader fh; BmpInfoHeader ih;
+    in.read((char*)&fh, sizeof(fh)); in.read((char*)&ih, sizeof(ih));
+    if (fh.type != 0x4D42 || ih.bitCount != 24) return false;
+    w = ih.w; h = ih.h;
+    size_t base = px.size();
+    px.resize(base + (size_t)w * h);
+    int rowSize = (3 * w + 3) & (~3);
+    std::vector<unsigned char> row(rowSize);
+    for (int y = 0; y < h; ++y) {
+        in.read((char*)row.data(), rowSize);
+        for (int x = 0; x < w; ++x) {
+            float b = powf(row[x * 3 + 0] / 255.0f, 2.2f), g = powf(row[x * 3 + 1] / 255.0f, 2.2f), r = powf(row[x * 3 + 2] / 255.0f, 2.2f);
+            px[base + (size_t)(h - 1 - y) * w + x] = {r, g, b, 1.0f};
+        }
+    }
+    return true;
+}
+
+static float tone1(float c) {   // imageUtil.cu:202-210 then :212-221
+    float t = (c * (2.51f * c + 0.03f)) / (c * (2.43f * c + 0.59f) + 0.14f);
+    t = t < 0.f ? 0.f : (t > 1.f ? 1.f : t);
+    return powf(t, 1.0f / 2.2f);
+}
+
+}  // namespace nv
+
+using namespace nv;
+
+extern "C" {
+
+int novum_abi_version(void) { return NOVUM_ABI_VERSION; }
+
+const char* novum_error_string(int code) {
+    switch (code) {
+        case NOVUM_OK: return "ok";
+        case NOVUM_E_ARG: return "invalid argument";
+        case NOVUM_E_IO: return "file could not be read or written";
+        case NOVUM_E_NOSCENE: return "null scene handle";
+        case NOVUM_E_NOGPU: return "no CUDA device";
+        case NOVUM_E_UNSUPPORTED: return "unsupported";
+        default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
+    }
+}
+
+int novum_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+int novum_set_device(int device) { return (int)cudaSetDevice(device); }
+int novum_sync(void) { return (int)cudaDeviceSynchronize(); }
+
+int novum_config_load(const char* path, NovumRenderConfig* out) {
+    if (!path || !out) return NOVUM_E_ARG;
+    return loadConfigFull(path, out, nullptr);
+}
+
+int novum_material_table(NovumMaterial* out24) {
+    if (!out24) return NOVUM_E_ARG;
+    int z[4] = {0, 0, 0, 0};
+    buildMaterialTable(out24, z, z, z);
+    return 0;
+}
+
+int novum_camera_make(const NovumRenderConfig* cfg, NovumCamera* out) {
+    if (!cfg || !out) return NOVUM_E_ARG;
+    makeCamera(cfg, out);
+    return 0;
+}
+
+int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene** out, NovumRenderConfig* cfgOut) {
+    if (!configPath || !out) return NOVUM_E_ARG;
+    NovumRenderConfig cfg; std::vector<MeshCfg> meshes;
+    int rc = loadConfigFull(configPath, &cfg, &meshes);
+    if (rc) return rc;
+    if (cfgOut) *cfgOut = cfg;
+    // textures (main.cu:371-391): missing files give empty images, like the reference
+    std::vector<NovumFloat4> texels; int ts[4], tw[4], th[4];
+    const char* texNames[4] = {"textures/enkidutexture.bmp", "textures/enkiduchibitexture.bmp", "textures/leaftex2.bmp", "textures/leafautumn.bmp"};
+    for (int i = 0; i < 4; ++i) { ts[i] = (int)texels.size(); loadBmpTexture(texNames[i], texels, tw[i], th[i]); }
+    NovumMaterial mats[24];
+    buildMaterialTable(mats, ts, tw, th);
+    // paths in the config are relative to the working directory in the reference; also try the config's directory
+    std::string cfgDir = configPath;
+    size_t slash = cfgDir.find_last_of('/');
+    cfgDir = slash == std::string::npos ? std::string(".") : cfgDir.substr(0, slash);
+    HostMesh M;
+    for (const MeshCfg& m : meshes) {
+        float e[3] = {m.mult * m.color[0], m.mult * m.color[1], m.mult * m.color[2]};
+        bool emissive = m.color[0] * m.color[0] + m.color[1] * m.color[1] + m.color[2] * m.color[2] > 0.f;
+        float yoff = emissive ? -0.01f * renderNumber : 0.f;   // main.cu:476-478
+        if (m.materialID < 0 || m.materialID >= 24) return NOVUM_E_ARG;
+        int r = loadObj(m.path, M, e, m.materialID, yoff);
+        if (r) r = loadObj(cfgDir + "/" + m.path, M, e, m.materialID, yoff);
+        if (r) r = loadObj(cfgDir + "/../" + m.path, M, e, m.materialID, yoff);
+        if (r) fprintf(stderr, "Error: Could not open OBJ file %s\n", m.path.c_str());   // main.cu:941-944: keeps going
+    }
+    if (M.tris.empty()) return NOVUM_E_IO;   // main.cu:505-508
+    rc = novum_scene_create(M.pos.data(), (int)M.pos.size(), M.nrm.data(), (int)M.nrm.size(), M.uv.data(), (int)M.uv.size(),
+                            M.tris.data(), (int)M.tris.size(), mats, 24, texels.data(), (int)texels.size(), out);
+    if (rc == 0) for (const MeshCfg& m : meshes) (*out)->meshPaths.push_back(m.path);
+    return rc;
+}
+
+int novum_save_bmp(const char* path, const NovumFloat4* colors, int w, int h, float scale, int postProcess) {
+    if (!path || !colors || w <= 0 || h <= 0) return NOVUM_E_ARG;
+    FILE* f = fopen(path, "wb");
+    if (!f) return NOVUM_E_IO;
+    int rowSize = (3 * w + 3) & (~3);
+    BmpFileHeader fh = {0x4D42, (uint32_t)(sizeof(BmpFileHeader) + sizeof(BmpInfoHeader) + rowSize * h), 0, 0,
+                        (uint32_t)(sizeof(BmpFileHeader) + sizeof(BmpInfoHeader))};
+    BmpInfoHeader ih = {sizeof(BmpInfoHeader), w, h, 1, 24, 0, (uint32_t)(rowSize * h), 0, 0, 0, 0};
+    fwrite(&fh, sizeof(fh), 1, f); fwrite(&ih, sizeof(ih), 1, f);
+    std::vector<unsigned char> row(rowSize, 0);
+    for (int y = 0; y < h; ++y) {   // row order as imageUtil.cu:82-93 writes it
+        for (int x = 0; x < w; ++x) {
+            const NovumFloat4& c = colors[(size_t)y * w + x];
+            float v[3] = {c.x * scale, c.y * scale, c.z * scale};
+            for (int k = 0; k < 3; ++k) {
+                float t = postProcess ? tone1(v[k]) : v[k];
+                t = t < 0.f ? 0.f : (t > 1.f ? 1.f : t);
+                row[x * 3 + (2 - k)] = (unsigned char)(t * 255.0f + 0.5f);
+            }
+        }
+        fwrite(row.data(), 1, rowSize, f);
+    }
+    fclose(f);
+    return 0;
+}
+
+int novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, float scale) {
+    if (!path || !colors || w <= 0 || h <= 0) return NOVUM_E_ARG;
+    FILE* f = fopen(path, "wb");
+    if (!f) return NOVUM_E_IO;
+    fprintf(f, "PF\n%d %d\n-1.0\n", w, h);
+    std::vector<float> row((size_t)w * 3);
+    for (int y = h - 1; y >= 0; --y) {
+        for (int x = 0; x < w; ++x) {
+            const NovumFloat4& c = colors[(size_t)y * w + x];
+            row[x * 3 + 0] = c.x * scale; row[x * 3 + 1] = c.y * scale; row[x * 3 + 2] = c.z * scale;
+        }
+        fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    fclose(f);
+    return 0;
+}
+
+}  // extern "C"

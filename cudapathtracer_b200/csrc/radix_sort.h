@@ -1,0 +1,36 @@
+// radix_sort.h — hand-written LSD radix sort of (u32 key, u32 value) pairs on the device.
+// Replaces the reference's cub::DeviceRadixSort::SortPairs call (deviceCode.cu:3172, 3298) and is
+// also the sorter of the LBVH builder. Only the key bits that can be non-zero are sorted
+// (the reference always sorts all 32 bits of a hash that is < tableSize).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+namespace nv {
+
+struct RadixSortPlan {
+    int maxN = 0;
+    int numTilesMax = 0;
+    uint32_t* keysAlt = nullptr;    // ping-pong buffers
+    uint32_t* valsAlt = nullptr;
+    uint32_t* hist = nullptr;       // [256][numTiles] per pass
+    uint32_t* blockSums = nullptr;  // scan scratch
+    size_t bytes = 0;
+};
+
+constexpr int kSortTile = 4096;     // keys per block per pass
+
+cudaError_t radixSortPlanCreate(RadixSortPlan& plan, int maxN);
+void radixSortPlanDestroy(RadixSortPlan& plan);
+
+// Sorts keys[0..n) ascending on bits [0, numBits) (rounded up to whole 8-bit digits), stable.
+// On return the sorted data is in `keys`/`vals` (the plan's alternates are scratch).
+// Returns the number of kernels launched through *launches (may be null).
+cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, int n, int numBits,
+                           cudaStream_t stream, int* launches);
+
+// exclusive prefix sum over u32, in place; scratch must hold >= ceil(n/2048)+1 entries
+cudaError_t exclusiveScanU32(uint32_t* data, int n, uint32_t* scratch, cudaStream_t stream, int* launches);
+
+}  // namespace nv

@@ -1,0 +1,335 @@
+// scene.cu — scene object lifetime, material compaction, and the ray-batch intersection entry points
+// (novum_trace_closest / novum_trace_shadow) that mirror BVHSceneIntersect / BVHShadowRay
+// (integratorUtilities.cuh:84, :188) on whole batches.
+#include "scene.h"
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+
+using namespace nv;
+
+namespace nv {
+
+int smCount() {
+    static int n = 0;
+    if (!n) {
+        int dev = 0; cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+__global__ void compactMaterialsKernel(const NovumMaterial* __restrict__ in, DMat* __restrict__ out, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const NovumMaterial& m = in[i];
+    DMat d;
+    d.albedo[0] = m.albedo.x; d.albedo[1] = m.albedo.y; d.albedo[2] = m.albedo.z; d.type = m.type;
+    d.eta[0] = m.eta.x; d.eta[1] = m.eta.y; d.eta[2] = m.eta.z; d.roughness = m.roughness;
+    d.k[0] = m.k.x; d.k[1] = m.k.y; d.k[2] = m.k.z; d.ior = m.ior;
+    d.absorption[0] = m.absorption.x; d.absorption[1] = m.absorption.y; d.absorption[2] = m.absorption.z;
+    d.transmission = m.transmission;
+    d.texStart = m.startInd; d.texW = m.width; d.texH = m.height;
+    d.flags = (m.hasTexture ? MF_TEXTURE : 0u) | (m.hasTransMap ? MF_TRANSMAP : 0u) | (m.isSpecular ? MF_SPECULAR : 0u) |
+              (m.boundary ? MF_BOUNDARY : 0u) | (m.thinWalled ? MF_THINWALLED : 0u);
+    d.priority = m.priority; d.pad[0] = d.pad[1] = d.pad[2] = 0;
+    out[i] = d;
+}
+
+int ensureStage(NovumScene* s, size_t bytes) {
+    if (bytes <= s->stageBytes) return 0;
+    if (s->d_stage) cudaFree(s->d_stage);
+    s->d_stage = nullptr; s->stageBytes = 0;
+    size_t want = bytes + bytes / 4;
+    cudaError_t e = cudaMalloc(&s->d_stage, want);
+    if (e != cudaSuccess) return (int)e;
+    s->stageBytes = want;
+    return 0;
+}
+
+int sceneFinalize(NovumScene* s) {
+    cudaError_t e;
+    if (!s->stream && (e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+    if (!s->ev0) { cudaEventCreate(&s->ev0); cudaEventCreate(&s->ev1); }
+    if ((e = cudaMalloc(&s->d_mats, sizeof(DMat) * (s->nMat > 0 ? s->nMat : 1))) != cudaSuccess) return (int)e;
+    if (s->nMat > 0) compactMaterialsKernel<<<(s->nMat + 63) / 64, 64, 0, s->stream>>>(s->d_matsRef, s->d_mats, s->nMat);
+    if ((e = cudaMalloc(&s->d_counters, 2 * sizeof(unsigned long long))) != cudaSuccess) return (int)e;
+    cudaMemsetAsync(s->d_counters, 0, 2 * sizeof(unsigned long long), s->stream);
+    if ((e = cudaMalloc(&s->d_queueCounter, 4 * sizeof(int))) != cudaSuccess) return (int)e;
+    e = buildBvh8(s->d_positions, s->d_tris, s->nTri, s->d_mats, s->stream, s->bvh);
+    if (e != cudaSuccess) return (int)e;
+    // main.cu:532-535: centre / radius / min of the root box
+    for (int k = 0; k < 3; ++k) { s->sceneMin[k] = s->bvh.boundsMin[k]; s->sceneMax[k] = s->bvh.boundsMax[k]; }
+    float c[3], d2 = 0.f;
+    for (int k = 0; k < 3; ++k) { c[k] = (s->sceneMax[k] + s->sceneMin[k]) * 0.5f; float d = s->sceneMax[k] - c[k]; d2 += d * d; s->sceneCenter[k] = c[k]; }
+    s->sceneRadius = sqrtf(d2) + 0.01f;
+    return 0;
+}
+
+// ---- ray-batch kernels -----------------------------------------------------------------------------
+constexpr int kTraceThreads = 128;
+
+// Persistent warps pull 32-ray packets from a global counter; stack lives in shared memory.
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceThreads) closestBatchKernel(SceneView sc, const NovumRay* __restrict__ rays, int n,
+                                                                     NovumHit* __restrict__ hits, int* __restrict__ counter,
+                                                                     TravCounters cnt) {
+    __shared__ uint2 stackMem[kSmemStack * kTraceThreads];
+    TravStack st; st.init(stackMem + threadIdx.x, kTraceThreads);
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(counter, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        if (i < n) {
+            const float4* rp = reinterpret_cast<const float4*>(rays + i);
+            float4 o = __ldg(rp), d = __ldg(rp + 1);
+            HitRec h = traceClosest<COUNT>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, st, cnt);
+            reinterpret_cast<float4*>(hits)[i] = make_float4(__int_as_float(h.tri), h.tri >= 0 ? h.t : 0.f, h.u, h.v);
+        }
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceThreads) shadowBatchKernel(SceneView sc, const NovumRay* __restrict__ rays,
+                                                                    const float* __restrict__ maxT, const int* __restrict__ skip, int n,
+                                                                    float4* __restrict__ out, int* __restrict__ counter, TravCounters cnt) {
+    __shared__ uint2 stackMem[kSmemStack * kTraceThreads];
+    TravStack st; st.init(stackMem + threadIdx.x, kTraceThreads);
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(counter, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        if (i < n) {
+            const float4* rp = reinterpret_cast<const float4*>(rays + i);
+            float4 o = __ldg(rp), d = __ldg(rp + 1);
+            V3 t = traceShadow<COUNT>(sc, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), maxT[i], skip ? skip[i] : -1, st, cnt);
+            out[i] = make_float4(t.x, t.y, t.z, 0.f);
+        }
+    }
+}
+
+}  // namespace nv
+
+SceneView NovumScene::view() const {
+    SceneView v;
+    v.bvh.nodes = bvh.nodes; v.bvh.tris = bvh.tris; v.bvh.numNodes = bvh.numNodes; v.bvh.numTris = bvh.numTris;
+    v.positions = d_positions; v.normals = d_normals; v.uvs = d_uvs;
+    v.tris = d_tris; v.lights = d_lights; v.mats = d_mats; v.textures = d_textures;
+    v.numTris = nTri; v.numLights = nLights; v.numMats = nMat;
+    for (int k = 0; k < 3; ++k) { v.sceneMin[k] = sceneMin[k]; v.sceneCenter[k] = sceneCenter[k]; }
+    v.sceneRadius = sceneRadius;
+    return v;
+}
+
+extern "C" {
+
+int novum_scene_create(const NovumFloat4* positions, int nPos, const NovumFloat4* normals, int nNorm,
+                       const NovumFloat2* uvs, int nUV, const NovumTriangle* tris, int nTri,
+                       const NovumMaterial* mats, int nMat, const NovumFloat4* textures, int nTexels, NovumScene** out) {
+    if (!positions || !tris || !out || nPos <= 0 || nTri <= 0 || nMat <= 0 || !mats) return NOVUM_E_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return NOVUM_E_NOGPU;
+    for (int i = 0; i < nTri; ++i) {   // the reference indexes normals[-1]/uvs[-1] when vn/vt are missing (main.cu:1044-1050): refuse
+        const NovumTriangle& t = tris[i];
+        if (t.aInd < 0 || t.bInd < 0 || t.cInd < 0 || t.aInd >= nPos || t.bInd >= nPos || t.cInd >= nPos) return NOVUM_E_ARG;
+        if (t.naInd < 0 || t.nbInd < 0 || t.ncInd < 0 || t.naInd >= nNorm || t.nbInd >= nNorm || t.ncInd >= nNorm) return NOVUM_E_ARG;
+        if (t.uvaInd < 0 || t.uvbInd < 0 || t.uvcInd < 0 || t.uvaInd >= nUV || t.uvbInd >= nUV || t.uvcInd >= nUV) return NOVUM_E_ARG;
+        if (t.materialID < 0 || t.materialID >= nMat) return NOVUM_E_ARG;
+    }
+    NovumScene* s = new NovumScene();
+    s->nPos = nPos; s->nNorm = nNorm; s->nUV = nUV; s->nTri = nTri; s->nMat = nMat; s->nTexels = nTexels;
+    std::vector<NovumTriangle> lights;
+    for (int i = 0; i < nTri; ++i) {   // main.cu:1018, 1060-1063: emissive triangles form the light list
+        const NovumFloat4& e = tris[i].emission;
+        if (e.x * e.x + e.y * e.y + e.z * e.z > 0.f) lights.push_back(tris[i]);
+    }
+    s->nLights = (int)lights.size();
+    cudaError_t e = cudaSuccess;
+    auto up = [&](void** dst, const void* src, size_t bytes) {
+        if (e != cudaSuccess) return;
+        e = cudaMalloc(dst, bytes ? bytes : 16);
+        if (e == cudaSuccess && bytes) e = cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+    };
+    up((void**)&s->d_positions, positions, sizeof(float4) * nPos);
+    up((void**)&s->d_normals, normals, sizeof(float4) * nNorm);
+    up((void**)&s->d_uvs, uvs, sizeof(float2) * nUV);
+    up((void**)&s->d_tris, tris, sizeof(NovumTriangle) * nTri);
+    up((void**)&s->d_lights, lights.data(), sizeof(NovumTriangle) * lights.size());
+    up((void**)&s->d_matsRef, mats, sizeof(NovumMaterial) * nMat);
+    up((void**)&s->d_textures, textures, sizeof(float4) * (nTexels > 0 ? nTexels : 0));
+    if (e != cudaSuccess) { novum_scene_destroy(s); return (int)e; }
+    int rc = sceneFinalize(s);
+    if (rc) { novum_scene_destroy(s); return rc; }
+    *out = s;
+    return 0;
+}
+
+int novum_scene_from_device(const NovumVertices* d_vertices, int vertNum, const NovumTriangle* d_scene, int triNum,
+                            const NovumTriangle* d_lights, int lightNum, const NovumMaterial* d_materials, int nMat,
+                            const NovumFloat4* d_textures, NovumScene** out) {
+    if (!d_vertices || !d_scene || !d_materials || !out || triNum <= 0 || nMat <= 0) return NOVUM_E_ARG;
+    NovumVertices v;
+    cudaError_t e = cudaMemcpy(&v, d_vertices, sizeof(v), cudaMemcpyDeviceToHost);   // the 32 B struct of device pointers
+    if (e != cudaSuccess) return (int)e;
+    NovumScene* s = new NovumScene();
+    s->borrowed = true;
+    s->d_positions = (float4*)v.positions; s->d_normals = (float4*)v.normals; s->d_uvs = (float2*)v.uvs;
+    s->d_tris = (NovumTriangle*)d_scene; s->d_lights = (NovumTriangle*)d_lights;
+    s->d_matsRef = (NovumMaterial*)d_materials; s->d_textures = (float4*)d_textures;
+    s->nPos = vertNum; s->nNorm = 0; s->nUV = 0; s->nTri = triNum; s->nLights = lightNum; s->nMat = nMat;
+    int rc = sceneFinalize(s);
+    if (rc) { novum_scene_destroy(s); return rc; }
+    *out = s;
+    return 0;
+}
+
+void novum_scene_destroy(NovumScene* s) {
+    if (!s) return;
+    if (s->wfEngine && s->wfEngineFree) s->wfEngineFree(s->wfEngine);
+    if (s->vcmEngine && s->vcmEngineFree) s->vcmEngineFree(s->vcmEngine);
+    if (!s->borrowed) {
+        cudaFree(s->d_positions); cudaFree(s->d_normals); cudaFree(s->d_uvs); cudaFree(s->d_tris);
+        cudaFree(s->d_lights); cudaFree(s->d_matsRef); cudaFree(s->d_textures);
+    }
+    cudaFree(s->d_mats); cudaFree(s->d_counters); cudaFree(s->d_queueCounter); cudaFree(s->d_stage);
+    freeBvh8(s->bvh);
+    if (s->ev0) { cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); }
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+int novum_scene_info(const NovumScene* s, int* nTri, int* nLights, int* nBvh8Nodes, float sceneMin[3], float sceneMax[3],
+                     float* sceneRadius) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (nTri) *nTri = s->nTri;
+    if (nLights) *nLights = s->nLights;
+    if (nBvh8Nodes) *nBvh8Nodes = s->bvh.numNodes;
+    for (int k = 0; k < 3; ++k) { if (sceneMin) sceneMin[k] = s->sceneMin[k]; if (sceneMax) sceneMax[k] = s->sceneMax[k]; }
+    if (sceneRadius) *sceneRadius = s->sceneRadius;
+    return 0;
+}
+
+int novum_scene_counts(const NovumScene* s, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (nPos) *nPos = s->nPos; if (nNorm) *nNorm = s->nNorm; if (nUV) *nUV = s->nUV;
+    if (nTri) *nTri = s->nTri; if (nLights) *nLights = s->nLights;
+    return 0;
+}
+
+int novum_scene_download(const NovumScene* s, NovumFloat4* positions, NovumFloat4* normals, NovumFloat2* uvs,
+                         NovumTriangle* tris, NovumTriangle* lights) {
+    if (!s) return NOVUM_E_NOSCENE;
+    cudaError_t e = cudaSuccess;
+    auto dl = [&](void* dst, const void* src, size_t bytes) {
+        if (dst && bytes && e == cudaSuccess) e = cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost);
+    };
+    dl(positions, s->d_positions, sizeof(float4) * s->nPos);
+    dl(normals, s->d_normals, sizeof(float4) * s->nNorm);
+    dl(uvs, s->d_uvs, sizeof(float2) * s->nUV);
+    dl(tris, s->d_tris, sizeof(NovumTriangle) * s->nTri);
+    dl(lights, s->d_lights, sizeof(NovumTriangle) * s->nLights);
+    return (int)e;
+}
+
+static int traceGrid() { return smCount() * 8; }
+
+int novum_trace_closest_device(NovumScene* s, const NovumRay* d_rays, int n, NovumHit* d_hits, int sync) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (n < 0 || (n > 0 && (!d_rays || !d_hits))) return NOVUM_E_ARG;
+    if (n == 0) return 0;
+    cudaMemsetAsync(s->d_queueCounter, 0, sizeof(int), s->stream);
+    TravCounters cnt{s->d_counters, s->d_counters + 1};
+    cudaEventRecord(s->ev0, s->stream);
+    int grid = min(traceGrid(), (n + kTraceThreads - 1) / kTraceThreads);
+    if (s->countersOn) closestBatchKernel<true><<<grid, kTraceThreads, 0, s->stream>>>(s->view(), d_rays, n, d_hits, s->d_queueCounter, cnt);
+    else closestBatchKernel<false><<<grid, kTraceThreads, 0, s->stream>>>(s->view(), d_rays, n, d_hits, s->d_queueCounter, cnt);
+    cudaEventRecord(s->ev1, s->stream);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    if (sync) { e = cudaStreamSynchronize(s->stream); if (e == cudaSuccess) cudaEventElapsedTime(&s->lastTraceMs, s->ev0, s->ev1); }
+    return (int)e;
+}
+
+int novum_trace_shadow_device(NovumScene* s, const NovumRay* d_rays, const float* d_maxT, const int32_t* d_skipTri, int n,
+                              NovumFloat4* d_throughput, int sync) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (n < 0 || (n > 0 && (!d_rays || !d_maxT || !d_throughput))) return NOVUM_E_ARG;
+    if (n == 0) return 0;
+    cudaMemsetAsync(s->d_queueCounter, 0, sizeof(int), s->stream);
+    TravCounters cnt{s->d_counters, s->d_counters + 1};
+    cudaEventRecord(s->ev0, s->stream);
+    int grid = min(traceGrid(), (n + kTraceThreads - 1) / kTraceThreads);
+    if (s->countersOn) shadowBatchKernel<true><<<grid, kTraceThreads, 0, s->stream>>>(s->view(), d_rays, d_maxT, d_skipTri, n, (float4*)d_throughput, s->d_queueCounter, cnt);
+    else shadowBatchKernel<false><<<grid, kTraceThreads, 0, s->stream>>>(s->view(), d_rays, d_maxT, d_skipTri, n, (float4*)d_throughput, s->d_queueCounter, cnt);
+    cudaEventRecord(s->ev1, s->stream);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    if (sync) { e = cudaStreamSynchronize(s->stream); if (e == cudaSuccess) cudaEventElapsedTime(&s->lastTraceMs, s->ev0, s->ev1); }
+    return (int)e;
+}
+
+int novum_trace_closest(NovumScene* s, const NovumRay* rays, int n, NovumHit* hits) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (n < 0 || (n > 0 && (!rays || !hits))) return NOVUM_E_ARG;
+    if (n == 0) return 0;
+    size_t rb = sizeof(NovumRay) * (size_t)n, hb = sizeof(NovumHit) * (size_t)n;
+    int rc = ensureStage(s, rb + hb);
+    if (rc) return rc;
+    NovumRay* dr = (NovumRay*)s->d_stage; NovumHit* dh = (NovumHit*)((char*)s->d_stage + rb);
+    cudaMemcpyAsync(dr, rays, rb, cudaMemcpyHostToDevice, s->stream);
+    rc = novum_trace_closest_device(s, dr, n, dh, 0);
+    if (rc) return rc;
+    cudaMemcpyAsync(hits, dh, hb, cudaMemcpyDeviceToHost, s->stream);
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    if (e == cudaSuccess) cudaEventElapsedTime(&s->lastTraceMs, s->ev0, s->ev1);
+    return (int)e;
+}
+
+int novum_trace_shadow(NovumScene* s, const NovumRay* rays, const float* maxT, const int32_t* skipTri, int n,
+                       NovumFloat4* throughput) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (n < 0 || (n > 0 && (!rays || !maxT || !throughput))) return NOVUM_E_ARG;
+    if (n == 0) return 0;
+    size_t rb = sizeof(NovumRay) * (size_t)n, tb = sizeof(float) * (size_t)n, ob = sizeof(float4) * (size_t)n;
+    int rc = ensureStage(s, rb + 2 * tb + ob);
+    if (rc) return rc;
+    char* base = (char*)s->d_stage;
+    NovumRay* dr = (NovumRay*)base; float4* dout = (float4*)(base + rb); float* dt = (float*)(base + rb + ob);
+    int* dk = (int*)(base + rb + ob + tb);
+    cudaMemcpyAsync(dr, rays, rb, cudaMemcpyHostToDevice, s->stream);
+    cudaMemcpyAsync(dt, maxT, tb, cudaMemcpyHostToDevice, s->stream);
+    if (skipTri) cudaMemcpyAsync(dk, skipTri, tb, cudaMemcpyHostToDevice, s->stream);
+    rc = novum_trace_shadow_device(s, dr, dt, skipTri ? dk : nullptr, n, (NovumFloat4*)dout, 0);
+    if (rc) return rc;
+    cudaMemcpyAsync(throughput, dout, ob, cudaMemcpyDeviceToHost, s->stream);
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    if (e == cudaSuccess) cudaEventElapsedTime(&s->lastTraceMs, s->ev0, s->ev1);
+    return (int)e;
+}
+
+int novum_trace_last_ms(NovumScene* s, float* ms) {
+    if (!s || !ms) return NOVUM_E_ARG;
+    *ms = s->lastTraceMs;
+    return 0;
+}
+
+int novum_trace_counters(NovumScene* s, int enable, uint64_t* nodeVisits, uint64_t* triTests) {
+    if (!s) return NOVUM_E_NOSCENE;
+    unsigned long long h[2] = {0, 0};
+    cudaStreamSynchronize(s->stream);
+    cudaError_t e = cudaMemcpy(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost);
+    if (nodeVisits) *nodeVisits = h[0];
+    if (triTests) *triTests = h[1];
+    cudaMemset(s->d_counters, 0, sizeof(h));
+    s->countersOn = enable != 0;
+    return (int)e;
+}
+
+}  // extern "C"

@@ -1,0 +1,47 @@
+// scene.h — host-side scene object behind the opaque NovumScene handle.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "../../include/novum_b200.h"
+#include "bvh8_build.h"
+#include "scene_dev.cuh"
+
+struct NovumScene {
+    // device geometry in the reference's layouts (owned unless borrowed from the caller)
+    float4* d_positions = nullptr;
+    float4* d_normals = nullptr;
+    float2* d_uvs = nullptr;
+    NovumTriangle* d_tris = nullptr;
+    NovumTriangle* d_lights = nullptr;
+    NovumMaterial* d_matsRef = nullptr;   // 176 B reference-layout table
+    nv::DMat* d_mats = nullptr;           // compact table
+    float4* d_textures = nullptr;
+    bool borrowed = false;                // geometry/material arrays belong to the caller (from_device)
+    int nPos = 0, nNorm = 0, nUV = 0, nTri = 0, nLights = 0, nMat = 0, nTexels = 0;
+    nv::Bvh8Device bvh;
+    float sceneMin[3] = {0, 0, 0}, sceneMax[3] = {0, 0, 0}, sceneCenter[3] = {0, 0, 0};
+    float sceneRadius = 0.f;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float lastTraceMs = 0.f;
+    // traversal counters
+    bool countersOn = false;
+    unsigned long long* d_counters = nullptr;   // [0] node visits, [1] tri tests
+    int* d_queueCounter = nullptr;              // persistent-kernel work counter
+    // staging for the host-pointer trace API (grown on demand)
+    void* d_stage = nullptr; size_t stageBytes = 0;
+    // host-side config meshes (when loaded from a .rendertron)
+    std::vector<std::string> meshPaths;
+    // lazily created integrator engines (owned; freed through the stored deleter)
+    void* wfEngine = nullptr;  void (*wfEngineFree)(void*) = nullptr;
+    void* vcmEngine = nullptr; void (*vcmEngineFree)(void*) = nullptr;
+
+    nv::SceneView view() const;
+};
+
+namespace nv {
+int sceneFinalize(NovumScene* s);     // compact materials, BVH8 build, bounds, stream/events
+int ensureStage(NovumScene* s, size_t bytes);
+int smCount();
+}

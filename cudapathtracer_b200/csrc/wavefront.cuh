@@ -1,0 +1,64 @@
+// wavefront.cuh — state of the wavefront path-tracing engine that replaces the reference's one-thread-per-
+// pixel megakernels (Li_unidirectional deviceCode.cu:285-542, Li_naive_unidirectional :158-205).
+//
+// A fixed pool of path slots lives in HBM as SoA. Each iteration runs
+//   advance -> extend (closest hit) -> shade (material-class queues, NEE, BSDF sampling, regeneration) -> shadow
+// on persistent warps that pull 32-entry packets from device-side queues; nothing goes back to the host
+// except a counter read every few iterations. Terminated paths are regenerated in place from a global
+// path counter, so the pool stays full until the last samples drain.
+#pragma once
+#include "scene_dev.cuh"
+
+namespace nv {
+
+enum : int { CLS_REGEN = 0, CLS_DIFFUSE = 1, CLS_METAL = 2, CLS_DIELECTRIC = 3, CLS_LEAF = 4, CLS_OTHER = 5, NUM_CLS = 6 };
+
+// device counters (ints), one cache line apart where contended
+enum : int {
+    C_EXTEND_COUNT = 0,      // entries in the current extend queue
+    C_NEXT_COUNT = 1,        // entries appended to the next extend queue
+    C_SHADOW_COUNT = 2,
+    C_CLASS_COUNT = 4,       // .. +NUM_CLS
+    C_FETCH_EXTEND = 16, C_FETCH_SHADE = 32, C_FETCH_SHADOW = 48,
+    C_PATH_COUNTER_LO = 64,  // next path id to generate (64-bit, two ints)
+    C_TOTAL = 96
+};
+
+struct ShadowRec { float4 o_maxT; float4 d_pix; float4 contrib; };   // 48 B
+
+struct WfState {
+    // per path slot
+    float4* rayO;        // xyz origin, w = pdf of the last BSDF sample
+    float4* rayD;        // xyz direction, w = bits: depth (low 16) | flags (high 16)
+    float4* beta;        // xyz throughput, w = bits: pixel index
+    float4* prevP;       // xyz last true-hit point (neePDF needs it), w = bits: medium stack top
+    uint4* medium;       // 16 x u8 medium stack (deviceCode.cu:306 keeps 16 ints)
+    unsigned long long* rng;
+    float4* hit;         // bits tri, t, u, v
+    int* hitFlags;       // triangle flags of the hit (material id in the low 16 bits)
+    // queues
+    int* extendQ[2];
+    int* classQ;         // NUM_CLS x capacity
+    ShadowRec* shadowQ;
+    int* counters;       // C_TOTAL ints
+    unsigned long long* rayCounters;   // [0] closest, [1] shadow, [2] paths finished, [3] paths started
+    int capacity;
+};
+
+enum : unsigned { PF_NONSPEC_SEEN = 1u << 16 };   // hitFirstnonSpecular (deviceCode.cu:314)
+
+struct WfParams {
+    NovumCamera cam;
+    int w, h;
+    int maxDepth;
+    int useMIS;
+    int naive;
+    unsigned long long seed;
+    // sample passes rendered by this call: firstSample + rank + k*world, k in [0, localSamples)
+    int firstSample, localSamples, rank, world;
+    int tilesX, tilesY;                  // 8x4 pixel tiles
+    unsigned long long totalIds;         // localSamples * tilesX*tilesY*32
+    float4* colors;                      // w*h accumulator (sum over samples)
+};
+
+}  // namespace nv

@@ -1,0 +1,161 @@
+// wavefront_host.inl — pool allocation and the host loop of the unidirectional wavefront engine.
+
+namespace nv {
+
+struct WfEngine {
+    WfState st{};
+    int* pinnedCounters = nullptr;      // host-pinned mirror for the periodic "anything left?" read
+    cudaEvent_t evRead = nullptr;
+    size_t bytes = 0;
+};
+
+static int wfAlloc(WfEngine& e, int capacity) {
+    WfState& s = e.st;
+    s.capacity = capacity;
+    cudaError_t err = cudaSuccess;
+    auto A = [&](void** p, size_t b) { if (err == cudaSuccess) { err = cudaMalloc(p, b); e.bytes += b; } };
+    size_t n = (size_t)capacity;
+    A((void**)&s.rayO, n * sizeof(float4)); A((void**)&s.rayD, n * sizeof(float4)); A((void**)&s.beta, n * sizeof(float4));
+    A((void**)&s.prevP, n * sizeof(float4)); A((void**)&s.medium, n * sizeof(uint4)); A((void**)&s.rng, n * sizeof(unsigned long long));
+    A((void**)&s.hit, n * sizeof(float4)); A((void**)&s.hitFlags, n * sizeof(int));
+    A((void**)&s.extendQ[0], n * sizeof(int)); A((void**)&s.extendQ[1], n * sizeof(int));
+    A((void**)&s.classQ, n * NUM_CLS * sizeof(int)); A((void**)&s.shadowQ, n * sizeof(ShadowRec));
+    A((void**)&s.counters, C_TOTAL * sizeof(int)); A((void**)&s.rayCounters, 4 * sizeof(unsigned long long));
+    if (err != cudaSuccess) return (int)err;
+    if ((err = cudaHostAlloc((void**)&e.pinnedCounters, C_TOTAL * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    cudaEventCreateWithFlags(&e.evRead, cudaEventDisableTiming);
+    return 0;
+}
+
+static void wfFree(WfEngine& e) {
+    WfState& s = e.st;
+    cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.medium); cudaFree(s.rng);
+    cudaFree(s.hit); cudaFree(s.hitFlags); cudaFree(s.extendQ[0]); cudaFree(s.extendQ[1]); cudaFree(s.classQ); cudaFree(s.shadowQ);
+    cudaFree(s.counters); cudaFree(s.rayCounters);
+    if (e.pinnedCounters) cudaFreeHost(e.pinnedCounters);
+    if (e.evRead) cudaEventDestroy(e.evRead);
+    e = WfEngine();
+}
+
+// Renders `numSample` sample passes of this shard into d_colors (sum accumulator). Blocking.
+static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, int w, int h, int maxDepth, int useMIS, int naive,
+                    int firstSample, int numSample, NovumShard shard, unsigned long long seed, float4* d_colors,
+                    NovumRenderStats* stats) {
+    if (shard.world < 1) shard.world = 1;
+    int local = 0;
+    for (int s = shard.rank; s < numSample; s += shard.world) ++local;
+    WfParams P;
+    P.cam = cam; P.w = w; P.h = h; P.maxDepth = maxDepth; P.useMIS = useMIS; P.naive = naive; P.seed = seed;
+    P.firstSample = firstSample; P.localSamples = local; P.rank = shard.rank; P.world = shard.world;
+    P.tilesX = (w + 7) / 8; P.tilesY = (h + 3) / 4;
+    P.totalIds = (unsigned long long)local * P.tilesX * P.tilesY * 32ull;
+    P.colors = d_colors;
+    cudaStream_t stream = scene->stream;
+    SceneView sc = scene->view();
+    WfState& st = eng.st;
+    unsigned long long poolWanted = P.totalIds < (unsigned long long)st.capacity ? P.totalIds : (unsigned long long)st.capacity;
+    int pool = (int)poolWanted;
+    unsigned long long launches = 0;
+    cudaEventRecord(scene->ev0, stream);
+    if (pool > 0) {
+        cudaMemsetAsync(st.rayCounters, 0, 4 * sizeof(unsigned long long), stream);
+        wfInit<<<(pool + 255) / 256, 256, 0, stream>>>(st, pool);
+        ++launches;
+        const int grid = smCount() * 8;
+        int cur = 0;
+        bool first = true;
+        for (long iter = 0;; ++iter) {
+            if (!first) {
+                wfAdvance<<<1, 32, 0, stream>>>(st.counters);
+                wfExtend<<<grid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur]);
+                launches += 2;
+            }
+            wfShade<<<grid, kWfThreads, 0, stream>>>(sc, st, P, st.extendQ[cur ^ 1]);
+            wfShadow<<<grid, kWfThreads, 0, stream>>>(sc, st, d_colors);
+            launches += 2;
+            cur ^= 1;
+            first = false;
+            if ((iter & 3) == 3) {      // every 4th iteration: is anything still in flight?
+                cudaMemcpyAsync(eng.pinnedCounters, st.counters, C_TOTAL * sizeof(int), cudaMemcpyDeviceToHost, stream);
+                cudaEventRecord(eng.evRead, stream);
+                cudaError_t e = cudaEventSynchronize(eng.evRead);
+                if (e != cudaSuccess) return (int)e;
+                if (eng.pinnedCounters[C_NEXT_COUNT] == 0) break;
+            }
+            if (iter > 2000000) return (int)cudaErrorLaunchTimeout;
+        }
+    }
+    cudaEventRecord(scene->ev1, stream);
+    cudaError_t e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) return (int)e;
+    if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
+    if (stats) {
+        unsigned long long rc[4] = {0, 0, 0, 0};
+        if (pool > 0) cudaMemcpy(rc, st.rayCounters, sizeof(rc), cudaMemcpyDeviceToHost);
+        memset(stats, 0, sizeof(*stats));
+        stats->closestRays = rc[0]; stats->shadowRays = rc[1]; stats->paths = rc[3];
+        stats->kernelLaunches = launches;
+        cudaEventElapsedTime(&stats->deviceMs, scene->ev0, scene->ev1);
+    }
+    return 0;
+}
+
+}  // namespace nv
+
+// ---- C ABI: render entry points ------------------------------------------------------------------------------
+namespace nv {
+int vcmRenderDevice(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                    NovumShard shard, unsigned long long seed, float4* d_colors, NovumRenderStats* stats);   // vcm.cu
+static void wfEngineFree(void* p) { WfEngine* e = (WfEngine*)p; wfFree(*e); delete e; }
+static NovumConstants g_constants = {0, 1, 1, 1, 1, 1, 0, 0, 1, 0};
+const NovumConstants& currentConstants() { return g_constants; }
+}
+
+extern "C" {
+
+int novum_update_constants(const NovumConstants* c) {
+    if (!c) return NOVUM_E_ARG;
+    nv::g_constants = *c;
+    return 0;
+}
+
+int novum_render_device(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                        NovumShard shard, uint64_t seed, NovumFloat4* d_colors, NovumRenderStats* stats) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (!cfg || !cam || !d_colors || numSample < 0 || cfg->width <= 0 || cfg->height <= 0) return NOVUM_E_ARG;
+    if (shard.world < 1 || shard.rank < 0 || shard.rank >= shard.world) return NOVUM_E_ARG;
+    int integ = cfg->integrator;
+    if (integ == NOVUM_UNIDIRECTIONAL || integ == NOVUM_NAIVE_UNIDIRECTIONAL) {
+        if (!s->wfEngine) {
+            nv::WfEngine* e = new nv::WfEngine();
+            long long px = (long long)cfg->width * cfg->height;
+            long long cap = px < (1 << 20) ? (1 << 20) : (px > (1 << 22) ? (1 << 22) : px);   // 1M .. 4M path slots
+            cap = (cap + 31) & ~31LL;
+            int rc = nv::wfAlloc(*e, (int)cap);
+            if (rc) { nv::wfFree(*e); delete e; return rc; }
+            s->wfEngine = e; s->wfEngineFree = nv::wfEngineFree;
+        }
+        return nv::wfRender(s, *(nv::WfEngine*)s->wfEngine, *cam, cfg->width, cfg->height, cfg->maxDepth, 1,
+                            integ == NOVUM_NAIVE_UNIDIRECTIONAL, firstSample, numSample, shard, seed, (float4*)d_colors, stats);
+    }
+    if (integ == NOVUM_VCM || integ == NOVUM_SPPM || integ == NOVUM_BIDIRECTIONAL)
+        return nv::vcmRenderDevice(s, cfg, cam, firstSample, numSample, shard, seed, (float4*)d_colors, stats);
+    return NOVUM_E_UNSUPPORTED;
+}
+
+int novum_render(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                 NovumShard shard, uint64_t seed, NovumFloat4* colors, NovumRenderStats* stats) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (!cfg || !colors) return NOVUM_E_ARG;
+    size_t bytes = sizeof(float4) * (size_t)cfg->width * cfg->height;
+    float4* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, bytes);
+    if (e != cudaSuccess) return (int)e;
+    cudaMemsetAsync(d, 0, bytes, s->stream);
+    int rc = novum_render_device(s, cfg, cam, firstSample, numSample, shard, seed, (NovumFloat4*)d, stats);
+    if (rc == 0) rc = (int)cudaMemcpy(colors, d, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,303 @@
+// wavefront_shade.inl — the shading stage: one warp-uniform material class per 32-path packet.
+// Follows Li_unidirectional (deviceCode.cu:285-542) bounce by bounce, including its quirks: pdf floor 0.01
+// (:481), EPSILON ray offsets (:504-506) but RAY_EPSILON pass-through on false hits (:517), emission counted
+// directly until the first non-specular vertex (:438) and MIS-weighted with neePDF afterwards (:442-453), the
+// un-normalised first-vertex light normal in the NEE pdf (:76, :134), Russian roulette only past maxDepth (:523).
+
+namespace nv {
+
+// ---- 16 x u8 medium stack held in four registers -----------------------------------------------------------
+struct MediumStack {
+    unsigned w[4]; int top;
+    NV_D int get(int i) const {
+        unsigned word = (i >> 2) == 0 ? w[0] : ((i >> 2) == 1 ? w[1] : ((i >> 2) == 2 ? w[2] : w[3]));
+        return (int)((word >> ((i & 3) * 8)) & 0xffu);
+    }
+    NV_D void set(int i, int v) {
+        unsigned sh = (i & 3) * 8, m = ~(0xffu << sh), b = ((unsigned)v & 0xffu) << sh;
+        switch (i >> 2) {
+            case 0: w[0] = (w[0] & m) | b; break;
+            case 1: w[1] = (w[1] & m) | b; break;
+            case 2: w[2] = (w[2] & m) | b; break;
+            default: w[3] = (w[3] & m) | b; break;
+        }
+    }
+    NV_D void push(int v) { if (top < 16) { set(top, v); ++top; } }
+    NV_D void remove(int mat) {           // integratorUtilities.cuh:414-434: searches down to index 1, never slot 0
+        int found = -1;
+        for (int i = top - 1; i > 0; --i) if (get(i) == mat) { found = i; break; }
+        if (found != -1) { for (int i = found; i < top - 1; ++i) set(i, get(i + 1)); --top; }
+    }
+};
+
+// Camera::generateCameraRay (objects.cuh:268-307)
+NV_D void cameraRay(const NovumCamera& c, Rng& rng, int x, int y, V3& o, V3& d) {
+    float aspect = (float)c.w / (float)c.h;
+    float jx = (rng.uniform() - 0.5f) * c.antiAliasJitterDist;
+    float jy = (rng.uniform() - 0.5f) * c.antiAliasJitterDist;
+    float u = (2.0f * ((x + jx) / (float)c.w) - 1.0f) * aspect * c.fovScale;
+    float v = (2.0f * ((y + jy) / (float)c.h) - 1.0f) * c.fovScale;
+    V3 org(c.cameraOrigin.x, c.cameraOrigin.y, c.cameraOrigin.z);
+    V3 right(c.right.x, c.right.y, c.right.z), up(c.up.x, c.up.y, c.up.z), fwd(c.forward.x, c.forward.y, c.forward.z);
+    V3 focal = org + (right * (u * c.focalDist)) + (up * (v * c.focalDist)) + (fwd * c.focalDist);
+    V3 lens(0.0f);
+    if (c.aperture > 0.0f) {
+        float rr = rng.uniform();
+        float theta = 2.0f * 3.141592f * rng.uniform();
+        float radius = c.aperture * sqrtf(rr);
+        float s, co; sincosf(theta, &s, &co);
+        lens = (right * (radius * co)) + (up * (radius * s));
+    }
+    o = org + lens;
+    d = normalize(focal - o);
+}
+
+struct PathRegs {
+    V3 o, d, beta, prevP;
+    float pdf;
+    int depth; unsigned flags;
+    int pix;
+    MediumStack ms;
+    Rng rng;
+};
+
+NV_D void loadPath(const WfState& st, int slot, PathRegs& p) {
+    float4 a = st.rayO[slot], b = st.rayD[slot], c = st.beta[slot], e = st.prevP[slot];
+    uint4 m = st.medium[slot];
+    p.o = V3(a.x, a.y, a.z); p.pdf = a.w;
+    p.d = V3(b.x, b.y, b.z);
+    unsigned df = __float_as_uint(b.w); p.depth = (int)(df & 0xffffu); p.flags = df & 0xffff0000u;
+    p.beta = V3(c.x, c.y, c.z); p.pix = __float_as_int(c.w);
+    p.prevP = V3(e.x, e.y, e.z); p.ms.top = __float_as_int(e.w);
+    p.ms.w[0] = m.x; p.ms.w[1] = m.y; p.ms.w[2] = m.z; p.ms.w[3] = m.w;
+    p.rng.state = st.rng[slot];
+}
+NV_D void storePath(const WfState& st, int slot, const PathRegs& p) {
+    st.rayO[slot] = make_float4(p.o.x, p.o.y, p.o.z, p.pdf);
+    st.rayD[slot] = make_float4(p.d.x, p.d.y, p.d.z, __uint_as_float(((unsigned)p.depth & 0xffffu) | p.flags));
+    st.beta[slot] = make_float4(p.beta.x, p.beta.y, p.beta.z, __int_as_float(p.pix));
+    st.prevP[slot] = make_float4(p.prevP.x, p.prevP.y, p.prevP.z, __int_as_float(p.ms.top));
+    st.medium[slot] = make_uint4(p.ms.w[0], p.ms.w[1], p.ms.w[2], p.ms.w[3]);
+    st.rng[slot] = p.rng.state;
+}
+
+NV_D void addColor(float4* colors, int pix, V3 c) {
+    if (c.x != 0.0f || c.y != 0.0f || c.z != 0.0f) atomicAdd(&colors[pix], make_float4(c.x, c.y, c.z, 0.f));
+}
+
+// neePDF (deviceCode.cu:63-85): area-to-solid-angle pdf of having picked the hit point on light triangle `tri`
+NV_D float neePdfOf(const SceneView& sc, int tri, V3 prevPoint, V3 hitPoint) {
+    int4 idx = __ldg(reinterpret_cast<const int4*>(sc.tris + tri));     // a b c na
+    V3 a(__ldg(sc.positions + idx.x)), b(__ldg(sc.positions + idx.y)), c(__ldg(sc.positions + idx.z));
+    V3 stl = hitPoint - prevPoint;
+    V3 wi = normalize(stl);
+    float d2 = lengthSq(stl);
+    V3 ln(__ldg(sc.normals + idx.w));
+    float cosL = dot(ln, -wi);
+    float area = 0.5f * length(cross(b - a, c - a));
+    return d2 / (cosL * sc.numLights * area);
+}
+
+// One bounce of the NEE+MIS integrator. Returns true if the path continues (p holds the next ray).
+NV_D bool shadeMIS(const SceneView& sc, const WfState& st, const WfParams& P, PathRegs& p, const HitRec& h, int hitFlags) {
+    const DMat* mats = sc.mats;
+    Surface s = makeSurface(sc, h, p.o, p.d);
+    Frame fr(s.n);
+    V3 wiLocal = fr.toLocal(p.d);
+    Shading sh = resolveShading(mats, s.mat, sc.textures, s.uv);
+    const bool isSpecular = (sh.m.flags & MF_SPECULAR) != 0;
+    bool trueHit = true;
+    // dominant medium = lowest priority on the stack (:337-346)
+    int minPriorID = p.ms.get(0);
+    int minPrior = __ldg(&mats[minPriorID].priority);
+    for (int i = 1; i < p.ms.top; ++i) {
+        int id = p.ms.get(i); int pr = __ldg(&mats[id].priority);
+        if (pr < minPrior) { minPrior = pr; minPriorID = id; }
+    }
+    MatView dom = loadMat(mats, minPriorID);
+    if (s.dist > kEps) {     // Beer-Lambert through the dominant medium (:347-358)
+        p.beta *= V3(expf(-dom.absorption.x * s.dist), expf(-dom.absorption.y * s.dist), expf(-dom.absorption.z * s.dist));
+    }
+    float etaI = dom.ior;
+    if (sh.m.flags & MF_BOUNDARY) {
+        if (sh.m.priority > minPrior) {       // false hit: a lower-priority surface inside the dominant medium (:413-425)
+            trueHit = false;
+            if (!s.backface) p.ms.push(s.mat);
+            else p.ms.remove(s.mat);
+        }
+        // true hit: the reference derives etaT here (:372-411) but the live dielectric sampler ignores it
+    }
+    int dEff = p.depth;
+    if (trueHit) {
+        bool emissive = lengthSq(s.emission) > kEps;
+        if (emissive) {
+            if (p.depth == 0 || !(p.flags & PF_NONSPEC_SEEN)) addColor(P.colors, p.pix, p.beta * s.emission);
+            else if (P.useMIS && !isSpecular) {
+                float lp = neePdfOf(sc, s.tri, p.prevP, s.p);
+                if (lp > kEps) {
+                    float wgt = p.pdf * p.pdf / (lp * lp + p.pdf * p.pdf);
+                    addColor(P.colors, p.pix, p.beta * s.emission * wgt);
+                }
+            }
+        }
+        if (P.useMIS && lengthSq(s.emission) < kEps && !isSpecular && sc.numLights > 0) {
+            // nextEventEstimation (:87-156); the shadow ray itself is deferred to the shadow stage
+            int index = min((int)(p.rng.uniform() * sc.numLights), sc.numLights - 1);
+            const NovumTriangle* lt = sc.lights + index;
+            int4 idx = __ldg(reinterpret_cast<const int4*>(lt));
+            float4 em = __ldg(reinterpret_cast<const float4*>(lt) + 3);
+            float4 pa4 = __ldg(sc.positions + idx.x), pb4 = __ldg(sc.positions + idx.y), pc4 = __ldg(sc.positions + idx.z);
+            V3 a(pa4), b(pb4), c(pc4);
+            float u = sqrtf(p.rng.uniform());
+            float v = p.rng.uniform();
+            V3 lp = (1.0f - u) * a + (u * (1.0f - v)) * b + (u * v) * c;
+            V3 stl = lp - s.p;
+            V3 wi = normalize(stl);
+            V3 ro = s.p + wi * kEps;
+            float tl = 0.f, tu, tv;
+            float4 e1 = make_float4(pb4.x - pa4.x, pb4.y - pa4.y, pb4.z - pa4.z, 0.f);
+            float4 e2 = make_float4(pc4.x - pa4.x, pc4.y - pa4.y, pc4.z - pa4.z, 0.f);
+            if (!triTest(pa4, e1, e2, ro, wi, tl, tu, tv)) tl = 0.f;
+            float d2 = lengthSq(stl);
+            V3 ln(__ldg(sc.normals + idx.w));
+            float cosL = dot(ln, -wi);
+            float cosS = fabsf(dot(s.n, wi));
+            float area = 0.5f * length(cross(b - a, c - a));
+            float lightPdf = d2 / (cosL * sc.numLights * area);
+            if (lightPdf > kEps) {
+                V3 toLight = fr.toLocal(wi);
+                V3 f = bsdfEval(sh, wiLocal, toLight, etaI);
+                float bp = bsdfPdf(sh, wiLocal, toLight, etaI);
+                float wgt = lightPdf * lightPdf / (bp * bp + lightPdf * lightPdf);
+                V3 contrib = p.beta * (f * V3(em.x, em.y, em.z) * cosS / lightPdf) * wgt;
+                bool push = contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f;
+                // (no warp aggregation: lanes reach this point divergently inside a class only via lightPdf)
+                if (push) {
+                    int pos = atomicAdd(&st.counters[C_SHADOW_COUNT], 1);
+                    float4* rec = reinterpret_cast<float4*>(st.shadowQ + pos);
+                    rec[0] = make_float4(ro.x, ro.y, ro.z, tl * (1.0f - kEps));
+                    rec[1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(p.pix));
+                    rec[2] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
+                }
+            }
+        }
+        V3 wo, f; float pdf;
+        bsdfSample(p.rng, sh, wiLocal, etaI, s.backface, MODE_RADIANCE, wo, f, pdf);
+        V3 woWorld = fr.toWorld(wo);
+        pdf = fmaxf(pdf, 0.01f);
+        if (wo.z < 0.0f) {       // refracted: enter / leave the medium (:484-497)
+            if (!s.backface) p.ms.push(s.mat);
+            else p.ms.remove(s.mat);
+        }
+        p.beta *= (f * fabsf(wo.z) / pdf);
+        p.o = (wo.z > 0.0f) ? s.p + s.n * kEps : s.p - s.n * kEps;
+        p.d = normalize(woWorld);
+        p.pdf = pdf;
+        p.prevP = s.p;
+    } else {
+        p.o = s.p + p.d * kRayEps;       // pass straight through (:517); depth is not consumed (:520)
+        dEff = p.depth - 1;
+    }
+    if (dEff > P.maxDepth) {             // Russian roulette (:523-532)
+        float lum = luminance(p.beta);
+        float q = clampf(lum, 0.05f, 0.99f);
+        if (p.rng.uniform() > q) return false;
+        p.beta /= q;
+    }
+    if (!isSpecular) p.flags |= PF_NONSPEC_SEEN;
+    p.depth = dEff + 1;
+    if (p.depth >= 100) return false;    // hard bounce cap (:318)
+    // a path whose throughput is exactly zero can never contribute again: stop tracing it (the reference keeps going)
+    if (p.beta.x == 0.0f && p.beta.y == 0.0f && p.beta.z == 0.0f) return false;
+    return true;
+}
+
+// One bounce of the naive integrator (deviceCode.cu:158-205)
+NV_D bool shadeNaive(const SceneView& sc, const WfParams& P, PathRegs& p, const HitRec& h) {
+    Surface s = makeSurface(sc, h, p.o, p.d);
+    Frame fr(s.n);
+    V3 toSurf = fr.toLocal(p.d);
+    Shading sh = resolveShading(sc.mats, s.mat, sc.textures, s.uv);
+    V3 wo, f; float pdf;
+    bsdfSample(p.rng, sh, toSurf, 1.0f, s.backface, MODE_RADIANCE, wo, f, pdf);
+    if (pdf <= 0.0f || lengthSq(f) < kEps) return false;
+    addColor(P.colors, p.pix, s.emission * p.beta);
+    p.beta *= f * fabsf(wo.z) / pdf;
+    p.o = s.p + ((wo.z > 0.0f) ? (s.n * kRayEps) : (-s.n * kRayEps));
+    p.d = fr.toWorld(wo);
+    p.depth += 1;
+    return p.depth < P.maxDepth;
+}
+
+__global__ void __launch_bounds__(kWfThreads) wfShade(SceneView sc, WfState st, WfParams P, int* __restrict__ nextQueue) {
+    const int lane = laneId();
+    int cnt[NUM_CLS], chunkStart[NUM_CLS + 1];
+    chunkStart[0] = 0;
+#pragma unroll
+    for (int c = 0; c < NUM_CLS; ++c) { cnt[c] = st.counters[C_CLASS_COUNT + c]; chunkStart[c + 1] = chunkStart[c] + (cnt[c] + 31) / 32; }
+    const int totalChunks = chunkStart[NUM_CLS];
+    const unsigned long long idsPerSample = (unsigned long long)P.tilesX * P.tilesY * 32ull;
+    unsigned long long* pathCounter = reinterpret_cast<unsigned long long*>(st.counters + C_PATH_COUNTER_LO);
+    unsigned long long finished = 0, started = 0;
+    while (true) {
+        int chunk = 0;
+        if (lane == 0) chunk = atomicAdd(&st.counters[C_FETCH_SHADE], 1);
+        chunk = __shfl_sync(0xffffffffu, chunk, 0);
+        if (chunk >= totalChunks) break;
+        int cls = 0;
+#pragma unroll
+        for (int c = 1; c < NUM_CLS; ++c) if (chunk >= chunkStart[c]) cls = c;
+        int i = (chunk - chunkStart[cls]) * 32 + lane;
+        bool valid = i < cnt[cls];
+        int slot = valid ? st.classQ[cls * st.capacity + i] : -1;
+        bool alive = false;
+        PathRegs p;
+        if (valid && cls != CLS_REGEN) {
+            loadPath(st, slot, p);
+            float4 hf = st.hit[slot];
+            HitRec h; h.tri = __float_as_int(hf.x); h.t = hf.y; h.u = hf.z; h.v = hf.w; h.flags = st.hitFlags[slot];
+            alive = P.naive ? shadeNaive(sc, P, p, h) : shadeMIS(sc, st, P, p, h, h.flags);
+            if (!alive) ++finished;
+        } else if (valid && cls == CLS_REGEN) {
+            // missed the scene: sampleSky is black (integratorUtilities.cuh:438); slots of the first iteration land here too
+        }
+        // regeneration: dead lanes pull new path ids until they get a pixel inside the image or the work runs out
+        bool need = valid && !alive;
+        while (true) {
+            unsigned m = __ballot_sync(0xffffffffu, need);
+            if (m == 0) break;
+            int leader = __ffs(m) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(pathCounter, (unsigned long long)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (need) {
+                unsigned long long id = base + __popc(m & ((1u << lane) - 1u));
+                if (id >= P.totalIds) need = false;
+                else {
+                    unsigned long long k = id / idsPerSample;
+                    unsigned l = (unsigned)(id - k * idsPerSample);
+                    unsigned tile = l >> 5, in = l & 31u;
+                    int x = (int)(tile % P.tilesX) * 8 + (int)(in & 7u), y = (int)(tile / P.tilesX) * 4 + (int)(in >> 3);
+                    if (x < P.w && y < P.h) {
+                        int sample = P.firstSample + P.rank + (int)k * P.world;
+                        p.pix = y * P.w + x;
+                        p.rng.seed(P.seed, (unsigned long long)p.pix, (unsigned long long)sample, 0);
+                        cameraRay(P.cam, p.rng, x, y, p.o, p.d);
+                        p.beta = V3(1.0f); p.prevP = V3(0.0f); p.pdf = kEps; p.depth = 0; p.flags = 0;
+                        p.ms.w[0] = p.ms.w[1] = p.ms.w[2] = p.ms.w[3] = 0; p.ms.top = 1;   // slot 0 = material 0 = air (:308)
+                        alive = true; need = false; ++started;
+                    }
+                }
+            }
+        }
+        int pos = warpAppend(&st.counters[C_NEXT_COUNT], alive);
+        if (alive) { storePath(st, slot, p); nextQueue[pos] = slot; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        finished += __shfl_xor_sync(0xffffffffu, finished, o);
+        started += __shfl_xor_sync(0xffffffffu, started, o);
+    }
+    if (lane == 0) { if (finished) atomicAdd(&st.rayCounters[2], finished); if (started) atomicAdd(&st.rayCounters[3], started); }
+}
+
+}  // namespace nv

@@ -1,0 +1,293 @@
+/*
+ * novum_b200.h — C ABI of the B200-native rendering core that replaces the hot path of
+ * DanielQ-51/cudapathtracer ("Novum") behind its own launch boundary.
+ *
+ * Every entry point is extern "C", takes plain pointers and sizes, and returns an int
+ * (0 = ok, >0 = cudaError_t, <0 = NOVUM_E_*).  No C++ / torch types cross this boundary.
+ *
+ * Reference interfaces replaced (citations into the reference tree):
+ *   deviceCode.cuh:6        updateConstants(RenderConfig&)            -> novum_update_constants
+ *   deviceCode.cuh:8-9      launch_unidirectional(...)                -> novum_launch_unidirectional
+ *   deviceCode.cuh:11-12    launch_naive_unidirectional(...)          -> novum_launch_naive_unidirectional
+ *   deviceCode.cuh:14-15    launch_bidirectional(...)                 -> novum_launch_bidirectional
+ *   deviceCode.cuh:17-18    launch_VCM(...)                           -> novum_launch_vcm
+ *   integratorUtilities.cuh:84   BVHSceneIntersect (per ray)          -> novum_trace_closest (ray batch)
+ *   integratorUtilities.cuh:188  BVHShadowRay (per ray)               -> novum_trace_shadow  (ray batch)
+ *   deviceCode.cu:3140      buildHashGrid(...)                        -> novum_hashgrid_build
+ *   objects.cuh:844         loadConfig, main.cu:936 readObjSimple,
+ *   main.cu:397-467         material table, main.cu:235 initRender    -> novum_scene_load_config / novum_render
+ *
+ * The POD structs below are layout-compatible (sizeof and every offset, checked by
+ * tests/test_abi.py against numbers printed from the reference headers) with the reference's
+ * Triangle (80 B), Material (176 B), Camera (112 B), Vertices (32 B), BVHnode (48 B) so that the
+ * reference's main.cu can hand its device buffers to these entry points unchanged.
+ */
+#ifndef NOVUM_B200_H
+#define NOVUM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NOVUM_ABI_VERSION 1
+
+/* error codes (negative; positive return values are cudaError_t) */
+#define NOVUM_OK             0
+#define NOVUM_E_ARG        (-1)
+#define NOVUM_E_IO         (-2)
+#define NOVUM_E_NOSCENE    (-3)
+#define NOVUM_E_NOGPU      (-4)
+#define NOVUM_E_UNSUPPORTED (-5)
+
+typedef struct NovumFloat4 { float x, y, z, w; } NovumFloat4;   /* 16 B, 16-aligned in device arrays */
+typedef struct NovumFloat2 { float x, y; } NovumFloat2;
+
+/* objects.cuh:159-183 Triangle, 80 B */
+typedef struct __attribute__((aligned(16))) NovumTriangle {
+    int32_t aInd, bInd, cInd;          /* position indices            off 0  */
+    int32_t naInd, nbInd, ncInd;       /* normal indices              off 12 */
+    int32_t uvaInd, uvbInd, uvcInd;    /* uv indices                  off 24 */
+    int32_t materialID;                /*                             off 36 */
+    int32_t _pad0[2];
+    NovumFloat4 emission;              /*                             off 48 */
+    int32_t lightInd;                  /* index in light list, -51 if not a light   off 64 */
+    int32_t triInd;                    /* index in the scene triangle list          off 68 */
+    int32_t _pad1[2];
+} NovumTriangle;
+
+/* objects.cuh:605-643 Material, 176 B (bools are 1 byte) */
+typedef struct __attribute__((aligned(16))) NovumMaterial {
+    uint8_t hasTexture; uint8_t _p0[3];
+    int32_t startInd, width, height;
+    uint8_t hasTransMap; uint8_t _p1[3];
+    int32_t tstartInd, twidth, theight;
+    int32_t type;                      /* off 32 */
+    int32_t _p2[3];
+    NovumFloat4 albedo;                /* off 48 */
+    float roughness;                   /* off 64 */
+    float _p3[3];
+    NovumFloat4 eta;                   /* off 80 */
+    NovumFloat4 k;                     /* off 96 */
+    float ior, metallic, specular, transmission;   /* off 112 */
+    uint8_t isSpecular, boundary, thinWalled, _p4; /* off 128 */
+    int32_t _p5[3];
+    NovumFloat4 absorption;            /* off 144 */
+    int32_t priority;                  /* off 160 */
+    int32_t _p6[3];
+} NovumMaterial;
+
+enum NovumMaterialType {               /* objects.cuh:595-603 */
+    NOVUM_MAT_DIFFUSE = 0, NOVUM_MAT_METAL = 1, NOVUM_MAT_SMOOTHDIELECTRIC = 2,
+    NOVUM_MAT_MICROFACETDIELECTRIC = 3, NOVUM_MAT_LEAF = 4, NOVUM_MAT_FLOWER = 5,
+    NOVUM_MAT_DELTAMIRROR = 6
+};
+
+/* objects.cuh:199-219 Camera, 112 B */
+typedef struct __attribute__((aligned(16))) NovumCamera {
+    NovumFloat4 cameraOrigin;
+    int32_t w, h;
+    float xRot, yRot, zRot;
+    float aperture, focalDist, fovScale;
+    float antiAliasJitterDist;
+    int32_t _pad[3];
+    NovumFloat4 forward, right, up;
+} NovumCamera;
+
+/* objects.cuh:151-157 Vertices, 32 B: struct of four device pointers */
+typedef struct NovumVertices {
+    NovumFloat4* positions;
+    NovumFloat4* normals;
+    NovumFloat4* colors;
+    NovumFloat2* uvs;
+} NovumVertices;
+
+/* objects.cuh:12-25 BVHnode, 48 B — accepted at the boundary and ignored (we build our own BVH8) */
+typedef struct __attribute__((aligned(16))) NovumBVHnode {
+    NovumFloat4 aabbMIN, aabbMAX;
+    int32_t left, right, first, primCount;
+} NovumBVHnode;
+
+/* objects.cuh:185-197 Ray, 32 B */
+typedef struct NovumRay { NovumFloat4 origin, direction; } NovumRay;
+
+/* result of a closest-hit query: the fields of the reference's Intersection (objects.cuh:550-568)
+ * that identify the hit; barycentrics follow triangleIntersect's convention
+ * (integratorUtilities.cuh:33: u weights vertex b, v weights vertex c). tri = -1 on a miss. */
+typedef struct NovumHit { int32_t tri; float t, u, v; } NovumHit;
+
+/* integrator ids, objects.cuh:570-576 */
+enum NovumIntegrator {
+    NOVUM_UNIDIRECTIONAL = 0, NOVUM_BIDIRECTIONAL = 1, NOVUM_NAIVE_UNIDIRECTIONAL = 2,
+    NOVUM_VCM = 3, NOVUM_SPPM = 4
+};
+
+/* scalar part of RenderConfig (objects.cuh:801-842); mesh list stays inside the scene object */
+typedef struct NovumRenderConfig {
+    int32_t width, height;
+    int32_t integrator;                /* NovumIntegrator, -1 if the name was not recognised */
+    int32_t sampleCount, maxDepth, bvhLeafSize;
+    int32_t sampleEnvironment, postProcess;
+    int32_t bdptEyeDepth, bdptLightDepth;
+    int32_t bdptLightTrace, bdptNee, bdptNaive, bdptConnection, bdptDrawPath, bdptDoMis, bdptPaintWeight;
+    int32_t vcmDoMerge, doSPPM;
+    float vcmMergeConst, vcmInitialMergeRadiusMultiplier;
+    int32_t pinholeCamera;
+    float camPos[3], camRot[3];
+    float camFov, camApeture, camFocalDist;
+    int32_t numMeshes;
+    char name[64];
+} NovumRenderConfig;
+
+/* the ten strategy toggles updateConstants uploads (deviceCode.cu:9-51) */
+typedef struct NovumConstants {
+    int32_t sampleEnvironment;
+    int32_t bdptLightTrace, bdptNee, bdptNaive, bdptConnection;
+    int32_t vcmDoMerge, doSPPM;
+    int32_t bdptDrawPath, bdptDoMis, bdptPaintWeight;
+} NovumConstants;
+
+/* sharding of one render across ranks (one process per GPU): this rank renders sample passes /
+ * light-path slabs / pixel tiles numbered rank, rank+world, ... ; world=1 is the reference's
+ * single-GPU behaviour. */
+typedef struct NovumShard { int32_t rank, world; } NovumShard;
+
+/* counters returned by a render (device ray counters, summed over the call) */
+typedef struct NovumRenderStats {
+    uint64_t closestRays, shadowRays, paths, photons, lightVertices;
+    uint64_t kernelLaunches;
+    float    deviceMs;                 /* CUDA-event time of the sample loop on the launch stream */
+    float    _pad;
+    uint64_t bvhNodeVisits, triTests;  /* only filled by the counter build / counter mode */
+} NovumRenderStats;
+
+typedef struct NovumScene NovumScene;  /* opaque: device geometry + BVH8 + materials + lights */
+
+/* ---- library -------------------------------------------------------------------------- */
+int  novum_abi_version(void);
+const char* novum_error_string(int code);
+int  novum_device_count(void);
+int  novum_set_device(int device);
+
+/* ---- scene (host front end: config / OBJ / material table / camera) --------------------- */
+/* objects.cuh:844 loadConfig — accepts both spellings of "...Merge Radius Multipl(i)er". */
+int  novum_config_load(const char* path, NovumRenderConfig* out);
+/* main.cu:235-557: config -> meshes -> material table -> device upload -> BVH8 build. */
+int  novum_scene_load_config(const char* configPath, int renderNumber, NovumScene** out, NovumRenderConfig* cfgOut);
+/* scene from caller arrays (host pointers) in the reference's layouts */
+int  novum_scene_create(const NovumFloat4* positions, int nPos, const NovumFloat4* normals, int nNorm,
+                        const NovumFloat2* uvs, int nUV, const NovumTriangle* tris, int nTri,
+                        const NovumMaterial* mats, int nMat, const NovumFloat4* textures, int nTexels,
+                        NovumScene** out);
+/* scene from the reference's DEVICE buffers (what launch_* receives); nothing is copied to host
+ * except the 32 B Vertices struct. */
+int  novum_scene_from_device(const NovumVertices* d_vertices, int vertNum, const NovumTriangle* d_scene, int triNum,
+                             const NovumTriangle* d_lights, int lightNum, const NovumMaterial* d_materials, int nMat,
+                             const NovumFloat4* d_textures, NovumScene** out);
+void novum_scene_destroy(NovumScene* s);
+int  novum_scene_info(const NovumScene* s, int* nTri, int* nLights, int* nBvh8Nodes, float sceneMin[3], float sceneMax[3],
+                      float* sceneRadius);
+int  novum_material_table(NovumMaterial* out24);                      /* main.cu:397-467, 24 entries */
+int  novum_camera_make(const NovumRenderConfig* cfg, NovumCamera* out); /* objects.cuh:221-266, 309-325 */
+/* copies of the scene arrays back to host, for oracles and tests */
+int  novum_scene_counts(const NovumScene* s, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights);
+int  novum_scene_download(const NovumScene* s, NovumFloat4* positions, NovumFloat4* normals, NovumFloat2* uvs,
+                          NovumTriangle* tris, NovumTriangle* lights);
+
+/* ---- intersection on ray batches (integratorUtilities.cuh:84, :188) --------------------- */
+/* device pointers; asynchronous on the library stream unless sync != 0 */
+int  novum_trace_closest_device(NovumScene* s, const NovumRay* d_rays, int n, NovumHit* d_hits, int sync);
+int  novum_trace_shadow_device(NovumScene* s, const NovumRay* d_rays, const float* d_maxT, const int32_t* d_skipTri,
+                               int n, NovumFloat4* d_throughput, int sync);
+/* host pointers: H2D of rays, trace, D2H of results, all inside the call */
+int  novum_trace_closest(NovumScene* s, const NovumRay* rays, int n, NovumHit* hits);
+int  novum_trace_shadow(NovumScene* s, const NovumRay* rays, const float* maxT, const int32_t* skipTri, int n,
+                        NovumFloat4* throughput);
+/* last trace's device time in ms (CUDA events on the library stream) and counters */
+int  novum_trace_last_ms(NovumScene* s, float* ms);
+int  novum_trace_counters(NovumScene* s, int enable, uint64_t* nodeVisits, uint64_t* triTests);
+
+/* ---- integrators ------------------------------------------------------------------------ */
+int  novum_update_constants(const NovumConstants* c);                 /* deviceCode.cu:38 */
+/* Scene-object form: adds `numSample` sample passes (pass indices firstSample .. firstSample+numSample-1,
+ * strided by shard.world) into d_colors (w*h float4 SUM accumulator, like the reference's `colors`). */
+int  novum_render_device(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample,
+                         int numSample, NovumShard shard, uint64_t seed, NovumFloat4* d_colors, NovumRenderStats* stats);
+/* Host form: renders and copies the accumulator to host memory (w*h float4). */
+int  novum_render(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                  NovumShard shard, uint64_t seed, NovumFloat4* colors, NovumRenderStats* stats);
+
+/* Reference-signature shims (device pointers exactly as main.cu passes them; deviceCode.cuh:8-18).
+ * BVH / BVHindices are accepted and ignored. PathVertices / VCMPathVertices / Photons scratch of the
+ * reference is accepted as void* and ignored: this core owns its own compact light-vertex cache. */
+int  novum_launch_unidirectional(int maxDepth, NovumCamera camera, NovumMaterial* materials, NovumFloat4* textures,
+                                 NovumBVHnode* BVH, int* BVHindices, NovumVertices* vertices, int vertNum,
+                                 NovumTriangle* scene, int triNum, NovumTriangle* lights, int lightNum, int numSample,
+                                 int useMIS, int w, int h, NovumFloat4* colors);
+int  novum_launch_naive_unidirectional(int maxDepth, NovumCamera camera, NovumMaterial* materials, NovumFloat4* textures,
+                                 NovumBVHnode* BVH, int* BVHindices, NovumVertices* vertices, int vertNum,
+                                 NovumTriangle* scene, int triNum, NovumTriangle* lights, int lightNum, int numSample,
+                                 int useMIS, int w, int h, NovumFloat4* colors);
+int  novum_launch_bidirectional(int eyeDepth, int lightDepth, NovumCamera camera, void* eyePath, void* lightPath,
+                                 NovumMaterial* materials, NovumFloat4* textures, NovumBVHnode* BVH, int* BVHindices,
+                                 NovumVertices* vertices, int vertNum, NovumTriangle* scene, int triNum,
+                                 NovumTriangle* lights, int lightNum, int numSample, int w, int h,
+                                 NovumFloat4 sceneCenter, float sceneRadius, NovumFloat4* colors, NovumFloat4* overlay,
+                                 int postProcess);
+int  novum_launch_vcm(int eyeDepth, int lightDepth, NovumCamera camera, void* lightPath, void* photons,
+                                 void* photons_sorted, NovumMaterial* materials, NovumFloat4* textures, NovumBVHnode* BVH,
+                                 int* BVHindices, NovumVertices* vertices, int vertNum, NovumTriangle* scene, int triNum,
+                                 NovumTriangle* lights, int lightNum, int numSample, int w, int h,
+                                 NovumFloat4 sceneCenter, float sceneRadius, NovumFloat4 sceneMin, NovumFloat4* colors,
+                                 NovumFloat4* overlay, int postProcess, float mergeRadiusPower,
+                                 float initialRadiusMultiplier);
+
+/* ---- photon hash grid (deviceCode.cu:3067-3198; integratorUtilities.cuh:382-412) -------- */
+typedef struct NovumHashGrid NovumHashGrid;
+int  novum_hashgrid_create(int maxPhotons, NovumHashGrid** out);      /* table size = nextPrime(2*maxPhotons) */
+void novum_hashgrid_destroy(NovumHashGrid* g);
+/* positions: device float x/y/z arrays (SoA, like Photons.pos_*). Produces sorted order + cell tables. */
+int  novum_hashgrid_build_device(NovumHashGrid* g, const float* d_px, const float* d_py, const float* d_pz, int n,
+                                 const float sceneMin[3], float mergeRadius, int sync);
+int  novum_hashgrid_table_size(const NovumHashGrid* g);
+/* host-facing: positions in, sorted photon indices + cell_start/cell_end out (tableSize entries each) */
+int  novum_hashgrid_build(NovumHashGrid* g, const float* px, const float* py, const float* pz, int n,
+                          const float sceneMin[3], float mergeRadius, uint32_t* sortedIndex, uint32_t* sortedHash,
+                          uint32_t* cellStart, uint32_t* cellEnd);
+/* radius query on the last-built grid: for each query point count photons within mergeRadius the way
+ * doEyePass's 27-cell loop does (deviceCode.cu:2968-3048; duplicates from hash collisions included) */
+int  novum_hashgrid_query_count(NovumHashGrid* g, const float* qx, const float* qy, const float* qz, int nq,
+                                uint32_t* counts);
+int  novum_hashgrid_last_ms(NovumHashGrid* g, float* ms);
+
+/* ---- multi-GPU phase API (one process per GPU; the exchange itself is done by the caller with
+ *      NCCL / torch.distributed on the device pointers returned here) -------------------------- */
+typedef struct NovumVcmState NovumVcmState;
+int  novum_vcm_create(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, NovumShard shard,
+                      uint64_t seed, NovumVcmState** out);
+void novum_vcm_destroy(NovumVcmState* v);
+/* light pass for this rank's slab of light paths of iteration `iter`; fills the local slab of the
+ * light-vertex cache and splats t=1 contributions into d_splat (w*h float4). */
+int  novum_vcm_light_pass(NovumVcmState* v, int iter, NovumFloat4* d_splat);
+/* device address + byte size of this rank's fixed-capacity slab inside the world-sized cache, so the caller
+ * can all-gather in place (ncclAllGather / dist.all_gather_into_tensor on the whole cache). */
+int  novum_vcm_cache_buffer(NovumVcmState* v, void** d_cacheBase, uint64_t* slabBytes, uint64_t* totalBytes);
+/* after the gather: hash grid over all ranks' photons, then the eye pass over this rank's pixel tiles. */
+int  novum_vcm_build_grid(NovumVcmState* v, int iter);
+int  novum_vcm_eye_pass(NovumVcmState* v, int iter, NovumFloat4* d_colors);
+int  novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats);
+int  novum_sync(void);
+
+/* ---- synthetic scene generator (stand-ins for the reference's LFS-pointer OBJ files) ----- */
+/* writes OBJ files + a .rendertron config under outDir; name in {cornell, dragon, water, rainbow}. */
+int  novum_make_scene(const char* name, const char* outDir, int detail);
+
+/* ---- image output (imageUtil.cu:69-142, 202-232) ---------------------------------------- */
+int  novum_save_bmp(const char* path, const NovumFloat4* colors, int w, int h, float scale, int postProcess);
+int  novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, float scale);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NOVUM_B200_H */
