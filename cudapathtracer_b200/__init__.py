@@ -1,0 +1,10 @@
+"""cudapathtracer_b200 — ctypes binding of libnovum_b200.so (the C ABI in include/novum_b200.h).
+
+The product is the shared library (hand-written sm_100a CUDA behind the reference's launch boundary); this
+package only loads it for tests and bench.py. There is no CPU fallback: a missing library or a missing GPU
+raises, loudly.
+"""
+from .binding import (  # noqa: F401
+    NovumError, lib, lib_path, Scene, HashGrid, RenderConfig, Camera, RenderStats, Shard, Constants,
+    make_scene, load_config, material_table, camera_make, device_count, DECLARED_SYMBOLS,
+)

@@ -1,0 +1,319 @@
+"""ctypes mirror of include/novum_b200.h. Every call goes through the C ABI; nothing here computes."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class NovumError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "libnovum_b200.so")
+
+
+def lib():
+    """Loads the CUDA library. Fails loudly when it has not been built (python __graft_entry__.py build)."""
+    global _LIB
+    if _LIB is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise NovumError(f"{p} is missing: build it with `make -C cudapathtracer_b200` (no CPU fallback exists)")
+        _LIB = C.CDLL(p)
+        _declare(_LIB)
+    return _LIB
+
+
+class F4(C.Structure):
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("z", C.c_float), ("w", C.c_float)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("cameraOrigin", F4), ("w", C.c_int32), ("h", C.c_int32), ("xRot", C.c_float), ("yRot", C.c_float),
+                ("zRot", C.c_float), ("aperture", C.c_float), ("focalDist", C.c_float), ("fovScale", C.c_float),
+                ("antiAliasJitterDist", C.c_float), ("_pad", C.c_int32 * 3), ("forward", F4), ("right", F4), ("up", F4)]
+
+
+class RenderConfig(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("integrator", C.c_int32), ("sampleCount", C.c_int32),
+                ("maxDepth", C.c_int32), ("bvhLeafSize", C.c_int32), ("sampleEnvironment", C.c_int32),
+                ("postProcess", C.c_int32), ("bdptEyeDepth", C.c_int32), ("bdptLightDepth", C.c_int32),
+                ("bdptLightTrace", C.c_int32), ("bdptNee", C.c_int32), ("bdptNaive", C.c_int32),
+                ("bdptConnection", C.c_int32), ("bdptDrawPath", C.c_int32), ("bdptDoMis", C.c_int32),
+                ("bdptPaintWeight", C.c_int32), ("vcmDoMerge", C.c_int32), ("doSPPM", C.c_int32),
+                ("vcmMergeConst", C.c_float), ("vcmInitialMergeRadiusMultiplier", C.c_float),
+                ("pinholeCamera", C.c_int32), ("camPos", C.c_float * 3), ("camRot", C.c_float * 3),
+                ("camFov", C.c_float), ("camApeture", C.c_float), ("camFocalDist", C.c_float),
+                ("numMeshes", C.c_int32), ("name", C.c_char * 64)]
+
+
+class Constants(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("sampleEnvironment", "bdptLightTrace", "bdptNee", "bdptNaive", "bdptConnection",
+                                         "vcmDoMerge", "doSPPM", "bdptDrawPath", "bdptDoMis", "bdptPaintWeight")]
+
+
+class Shard(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("closestRays", C.c_uint64), ("shadowRays", C.c_uint64), ("paths", C.c_uint64), ("photons", C.c_uint64),
+                ("lightVertices", C.c_uint64), ("kernelLaunches", C.c_uint64), ("deviceMs", C.c_float), ("_pad", C.c_float),
+                ("bvhNodeVisits", C.c_uint64), ("triTests", C.c_uint64), ("stageMs", C.c_float * 4), ("stageLaunches", C.c_uint64 * 4)]
+
+
+# numpy dtypes with the reference's struct layouts (objects.cuh Triangle 80 B, Material 176 B)
+TRI_DTYPE = np.dtype({"names": ["aInd", "bInd", "cInd", "naInd", "nbInd", "ncInd", "uvaInd", "uvbInd", "uvcInd", "materialID",
+                                "emission", "lightInd", "triInd"],
+                      "formats": ["<i4"] * 10 + [("<f4", 4), "<i4", "<i4"],
+                      "offsets": [0, 4, 8, 12, 16, 20, 24, 28, 32, 36, 48, 64, 68], "itemsize": 80})
+MAT_DTYPE = np.dtype({"names": ["hasTexture", "startInd", "width", "height", "hasTransMap", "tstartInd", "twidth", "theight", "type",
+                                "albedo", "roughness", "eta", "k", "ior", "metallic", "specular", "transmission", "isSpecular",
+                                "boundary", "thinWalled", "absorption", "priority"],
+                      "formats": ["u1", "<i4", "<i4", "<i4", "u1", "<i4", "<i4", "<i4", "<i4", ("<f4", 4), "<f4", ("<f4", 4),
+                                  ("<f4", 4), "<f4", "<f4", "<f4", "<f4", "u1", "u1", "u1", ("<f4", 4), "<i4"],
+                      "offsets": [0, 4, 8, 12, 16, 20, 24, 28, 32, 48, 64, 80, 96, 112, 116, 120, 124, 128, 129, 130, 144, 160],
+                      "itemsize": 176})
+HIT_DTYPE = np.dtype([("tri", "<i4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4")])
+
+
+def _header_symbols():
+    hdr = os.path.join(_HERE, "..", "include", "novum_b200.h")
+    with open(hdr) as f:
+        text = f.read()
+    return sorted(set(re.findall(r"\b(novum_[a-z0-9_]+)\s*\(", text)))
+
+
+DECLARED_SYMBOLS = _header_symbols()
+
+
+def _declare(L):
+    vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+    L.novum_error_string.restype = C.c_char_p
+    L.novum_error_string.argtypes = [ci]
+    L.novum_scene_destroy.restype = None
+    L.novum_hashgrid_destroy.restype = None
+    L.novum_vcm_destroy.restype = None
+    L.novum_scene_load_config.argtypes = [C.c_char_p, ci, C.POINTER(vp), C.POINTER(RenderConfig)]
+    L.novum_config_load.argtypes = [C.c_char_p, C.POINTER(RenderConfig)]
+    L.novum_scene_create.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, vp, ci, vp, ci, C.POINTER(vp)]
+    L.novum_scene_destroy.argtypes = [vp]
+    L.novum_scene_info.argtypes = [vp, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(cf * 3), C.POINTER(cf * 3), C.POINTER(cf)]
+    L.novum_scene_counts.argtypes = [vp] + [C.POINTER(ci)] * 5
+    L.novum_scene_download.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.novum_material_table.argtypes = [vp]
+    L.novum_camera_make.argtypes = [C.POINTER(RenderConfig), C.POINTER(Camera)]
+    L.novum_trace_closest.argtypes = [vp, vp, ci, vp]
+    L.novum_trace_shadow.argtypes = [vp, vp, vp, vp, ci, vp]
+    L.novum_trace_closest_device.argtypes = [vp, vp, ci, vp, ci]
+    L.novum_trace_shadow_device.argtypes = [vp, vp, vp, vp, ci, vp, ci]
+    L.novum_trace_last_ms.argtypes = [vp, C.POINTER(cf)]
+    L.novum_trace_counters.argtypes = [vp, ci, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.novum_set_profile.argtypes = [vp, ci]
+    L.novum_update_constants.argtypes = [C.POINTER(Constants)]
+    L.novum_render.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), ci, ci, Shard, C.c_uint64, vp, C.POINTER(RenderStats)]
+    L.novum_render_device.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), ci, ci, Shard, C.c_uint64, vp, C.POINTER(RenderStats)]
+    L.novum_make_scene.argtypes = [C.c_char_p, C.c_char_p, ci]
+    L.novum_save_bmp.argtypes = [C.c_char_p, vp, ci, ci, cf, ci]
+    L.novum_save_pfm.argtypes = [C.c_char_p, vp, ci, ci, cf]
+    L.novum_hashgrid_create.argtypes = [ci, C.POINTER(vp)]
+    L.novum_hashgrid_destroy.argtypes = [vp]
+    L.novum_hashgrid_table_size.argtypes = [vp]
+    L.novum_hashgrid_build.argtypes = [vp, vp, vp, vp, ci, C.POINTER(cf * 3), cf, vp, vp, vp, vp]
+    L.novum_hashgrid_build_device.argtypes = [vp, vp, vp, vp, ci, C.POINTER(cf * 3), cf, ci]
+    L.novum_hashgrid_query_count.argtypes = [vp, vp, vp, vp, ci, vp]
+    L.novum_hashgrid_last_ms.argtypes = [vp, C.POINTER(cf)]
+    L.novum_vcm_create.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), Shard, C.c_uint64, C.POINTER(vp)]
+    L.novum_vcm_destroy.argtypes = [vp]
+    L.novum_vcm_light_pass.argtypes = [vp, ci, vp]
+    L.novum_vcm_cache_buffer.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.novum_vcm_build_grid.argtypes = [vp, ci]
+    L.novum_vcm_eye_pass.argtypes = [vp, ci, vp]
+    L.novum_vcm_stats.argtypes = [vp, C.POINTER(RenderStats)]
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = lib().novum_error_string(rc).decode()
+        raise NovumError(f"{what} failed: {msg} (code {rc})")
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def device_count():
+    return lib().novum_device_count()
+
+
+def make_scene(name, out_dir, detail=100):
+    _check(lib().novum_make_scene(name.encode(), out_dir.encode(), int(detail)), "novum_make_scene")
+    return os.path.join(out_dir, "configs", "config.rendertron")
+
+
+def load_config(path):
+    cfg = RenderConfig()
+    _check(lib().novum_config_load(path.encode(), C.byref(cfg)), "novum_config_load")
+    return cfg
+
+
+def material_table():
+    m = np.zeros(24, dtype=MAT_DTYPE)
+    _check(lib().novum_material_table(_ptr(m)), "novum_material_table")
+    return m
+
+
+def camera_make(cfg):
+    cam = Camera()
+    _check(lib().novum_camera_make(C.byref(cfg), C.byref(cam)), "novum_camera_make")
+    return cam
+
+
+class Scene:
+    """Opaque NovumScene handle: device geometry + materials + the GPU-built BVH8."""
+
+    def __init__(self, handle, cfg=None):
+        self.h = handle
+        self.cfg = cfg
+
+    @classmethod
+    def from_config(cls, path, render_number=0):
+        h = C.c_void_p()
+        cfg = RenderConfig()
+        _check(lib().novum_scene_load_config(path.encode(), render_number, C.byref(h), C.byref(cfg)), "novum_scene_load_config")
+        return cls(h, cfg)
+
+    @classmethod
+    def from_arrays(cls, positions, normals, uvs, tris, mats, textures=None):
+        positions = np.ascontiguousarray(positions, np.float32).reshape(-1, 4)
+        normals = np.ascontiguousarray(normals, np.float32).reshape(-1, 4)
+        uvs = np.ascontiguousarray(uvs, np.float32).reshape(-1, 2)
+        tris = np.ascontiguousarray(tris, TRI_DTYPE)
+        mats = np.ascontiguousarray(mats, MAT_DTYPE)
+        ntex = 0
+        if textures is not None:
+            textures = np.ascontiguousarray(textures, np.float32).reshape(-1, 4)
+            ntex = len(textures)
+        h = C.c_void_p()
+        _check(lib().novum_scene_create(_ptr(positions), len(positions), _ptr(normals), len(normals), _ptr(uvs), len(uvs), _ptr(tris),
+                                        len(tris), _ptr(mats), len(mats), _ptr(textures), ntex, C.byref(h)), "novum_scene_create")
+        return cls(h)
+
+    def close(self):
+        if self.h:
+            lib().novum_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        nt, nl, nn, r = C.c_int(), C.c_int(), C.c_int(), C.c_float()
+        mn, mx = (C.c_float * 3)(), (C.c_float * 3)()
+        _check(lib().novum_scene_info(self.h, C.byref(nt), C.byref(nl), C.byref(nn), C.byref(mn), C.byref(mx), C.byref(r)), "novum_scene_info")
+        return {"tris": nt.value, "lights": nl.value, "bvh8_nodes": nn.value, "min": list(mn), "max": list(mx), "radius": r.value}
+
+    def download(self):
+        c = [C.c_int() for _ in range(5)]
+        _check(lib().novum_scene_counts(self.h, *[C.byref(x) for x in c]), "novum_scene_counts")
+        npos, nnrm, nuv, ntri, nl = [x.value for x in c]
+        pos = np.zeros((npos, 4), np.float32); nrm = np.zeros((nnrm, 4), np.float32); uv = np.zeros((nuv, 2), np.float32)
+        tris = np.zeros(ntri, TRI_DTYPE); lights = np.zeros(nl, TRI_DTYPE)
+        _check(lib().novum_scene_download(self.h, _ptr(pos), _ptr(nrm), _ptr(uv), _ptr(tris), _ptr(lights)), "novum_scene_download")
+        return pos, nrm, uv, tris, lights
+
+    def trace_closest(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.zeros(len(rays), HIT_DTYPE)
+        _check(lib().novum_trace_closest(self.h, _ptr(rays), len(rays), _ptr(hits)), "novum_trace_closest")
+        return hits
+
+    def trace_shadow(self, rays, max_t, skip=None):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        max_t = np.ascontiguousarray(max_t, np.float32)
+        skip = None if skip is None else np.ascontiguousarray(skip, np.int32)
+        out = np.zeros((len(rays), 4), np.float32)
+        _check(lib().novum_trace_shadow(self.h, _ptr(rays), _ptr(max_t), _ptr(skip), len(rays), _ptr(out)), "novum_trace_shadow")
+        return out
+
+    def trace_closest_device(self, d_rays, n, d_hits, sync=True):
+        _check(lib().novum_trace_closest_device(self.h, C.c_void_p(d_rays), n, C.c_void_p(d_hits), int(sync)), "novum_trace_closest_device")
+
+    def last_trace_ms(self):
+        ms = C.c_float()
+        _check(lib().novum_trace_last_ms(self.h, C.byref(ms)), "novum_trace_last_ms")
+        return ms.value
+
+    def counters(self, enable):
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(lib().novum_trace_counters(self.h, int(enable), C.byref(a), C.byref(b)), "novum_trace_counters")
+        return a.value, b.value
+
+    def set_profile(self, flags):
+        _check(lib().novum_set_profile(self.h, int(flags)), "novum_set_profile")
+
+    def render(self, cfg, cam, first_sample, num_sample, seed=103033, rank=0, world=1):
+        img = np.zeros((cfg.height, cfg.width, 4), np.float32)
+        st = RenderStats()
+        _check(lib().novum_render(self.h, C.byref(cfg), C.byref(cam), first_sample, num_sample, Shard(rank, world), seed, _ptr(img),
+                                  C.byref(st)), "novum_render")
+        return img, st
+
+    def render_device(self, cfg, cam, first_sample, num_sample, d_colors, seed=103033, rank=0, world=1):
+        st = RenderStats()
+        _check(lib().novum_render_device(self.h, C.byref(cfg), C.byref(cam), first_sample, num_sample, Shard(rank, world), seed,
+                                         C.c_void_p(d_colors), C.byref(st)), "novum_render_device")
+        return st
+
+
+class HashGrid:
+    def __init__(self, max_photons):
+        self.h = C.c_void_p()
+        self.max = max_photons
+        _check(lib().novum_hashgrid_create(max_photons, C.byref(self.h)), "novum_hashgrid_create")
+        self.table_size = lib().novum_hashgrid_table_size(self.h)
+
+    def close(self):
+        if self.h:
+            lib().novum_hashgrid_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def build(self, px, py, pz, scene_min, radius):
+        px, py, pz = [np.ascontiguousarray(a, np.float32) for a in (px, py, pz)]
+        n = len(px)
+        idx = np.zeros(n, np.uint32); hsh = np.zeros(n, np.uint32)
+        cs = np.zeros(self.table_size, np.uint32); ce = np.zeros(self.table_size, np.uint32)
+        mn = (C.c_float * 3)(*scene_min)
+        _check(lib().novum_hashgrid_build(self.h, _ptr(px), _ptr(py), _ptr(pz), n, C.byref(mn), radius, _ptr(idx), _ptr(hsh), _ptr(cs),
+                                          _ptr(ce)), "novum_hashgrid_build")
+        return idx, hsh, cs, ce
+
+    def build_device(self, d_px, d_py, d_pz, n, scene_min, radius, sync=True):
+        mn = (C.c_float * 3)(*scene_min)
+        _check(lib().novum_hashgrid_build_device(self.h, C.c_void_p(d_px), C.c_void_p(d_py), C.c_void_p(d_pz), n, C.byref(mn), radius,
+                                                 int(sync)), "novum_hashgrid_build_device")
+
+    def query_count(self, qx, qy, qz):
+        qx, qy, qz = [np.ascontiguousarray(a, np.float32) for a in (qx, qy, qz)]
+        out = np.zeros(len(qx), np.uint32)
+        _check(lib().novum_hashgrid_query_count(self.h, _ptr(qx), _ptr(qy), _ptr(qz), len(qx), _ptr(out)), "novum_hashgrid_query_count")
+        return out
+
+    def last_ms(self):
+        ms = C.c_float()
+        _check(lib().novum_hashgrid_last_ms(self.h, C.byref(ms)), "novum_hashgrid_last_ms")
+        return ms.value

@@ -8,6 +8,15 @@
 
 using namespace nv;
 
+// layouts the reference's main.cu hands over unchanged (sizes printed from its own headers)
+static_assert(sizeof(NovumTriangle) == 80, "Triangle");
+static_assert(sizeof(NovumMaterial) == 176, "Material");
+static_assert(sizeof(NovumCamera) == 112, "Camera");
+static_assert(sizeof(NovumBVHnode) == 48, "BVHnode");
+static_assert(sizeof(NovumVertices) == 32, "Vertices");
+static_assert(sizeof(NovumRay) == 32 && sizeof(NovumHit) == 16, "Ray/Hit");
+static_assert(sizeof(nv::DMat) == 96, "DMat");
+
 namespace nv {
 
 int smCount() {
@@ -312,6 +321,12 @@ int novum_trace_shadow(NovumScene* s, const NovumRay* rays, const float* maxT, c
     cudaError_t e = cudaStreamSynchronize(s->stream);
     if (e == cudaSuccess) cudaEventElapsedTime(&s->lastTraceMs, s->ev0, s->ev1);
     return (int)e;
+}
+
+int novum_set_profile(NovumScene* s, int flags) {
+    if (!s) return NOVUM_E_NOSCENE;
+    s->profileFlags = flags;
+    return 0;
 }
 
 int novum_trace_last_ms(NovumScene* s, float* ms) {

@@ -27,6 +27,7 @@ struct NovumScene {
     float lastTraceMs = 0.f;
     // traversal counters
     bool countersOn = false;
+    int profileFlags = 0;                 // novum_set_profile
     unsigned long long* d_counters = nullptr;   // [0] node visits, [1] tri tests
     int* d_queueCounter = nullptr;              // persistent-kernel work counter
     // staging for the host-pointer trace API (grown on demand)

@@ -54,12 +54,12 @@ __global__ void wfInit(WfState st, int n) {
 }
 
 // ---- extend: closest hit for every queued path, then bin the path by the material class it hit ------------
-__global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st, const int* __restrict__ queue) {
+template <bool COUNT>
+__global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st, const int* __restrict__ queue, TravCounters nocnt) {
     __shared__ uint2 stackMem[kSmemStack * kWfThreads];
     TravStack ts; ts.init(stackMem + threadIdx.x, kWfThreads);
     const int lane = laneId();
     const int n = st.counters[C_EXTEND_COUNT];
-    TravCounters nocnt{nullptr, nullptr};
     unsigned long long traced = 0;
     while (true) {
         int base = 0;
@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st,
         int cls = -1;
         if (valid) {
             float4 o = st.rayO[slot], d = st.rayD[slot];
-            HitRec h = traceClosest<false>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, nocnt);
+            HitRec h = traceClosest<COUNT>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, nocnt);
             ++traced;
             st.hit[slot] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
             st.hitFlags[slot] = h.flags;

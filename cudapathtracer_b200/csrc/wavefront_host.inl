@@ -4,8 +4,9 @@ namespace nv {
 
 struct WfEngine {
     WfState st{};
-    int* pinnedCounters = nullptr;      // host-pinned mirror for the periodic "anything left?" read
-    cudaEvent_t evRead = nullptr;
+    int* pinnedCounters = nullptr;      // host-pinned mirrors (2 slots) for the periodic "anything left?" read
+    cudaEvent_t evRead[2] = {nullptr, nullptr};
+    std::vector<cudaEvent_t> evPool;    // stage-boundary events (profile bit 0), grown on demand and reused
     size_t bytes = 0;
 };
 
@@ -22,8 +23,9 @@ static int wfAlloc(WfEngine& e, int capacity) {
     A((void**)&s.classQ, n * NUM_CLS * sizeof(int)); A((void**)&s.shadowQ, n * sizeof(ShadowRec));
     A((void**)&s.counters, C_TOTAL * sizeof(int)); A((void**)&s.rayCounters, 4 * sizeof(unsigned long long));
     if (err != cudaSuccess) return (int)err;
-    if ((err = cudaHostAlloc((void**)&e.pinnedCounters, C_TOTAL * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
-    cudaEventCreateWithFlags(&e.evRead, cudaEventDisableTiming);
+    if ((err = cudaHostAlloc((void**)&e.pinnedCounters, 2 * C_TOTAL * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    cudaEventCreateWithFlags(&e.evRead[0], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&e.evRead[1], cudaEventDisableTiming);
     return 0;
 }
 
@@ -33,7 +35,8 @@ static void wfFree(WfEngine& e) {
     cudaFree(s.hit); cudaFree(s.hitFlags); cudaFree(s.extendQ[0]); cudaFree(s.extendQ[1]); cudaFree(s.classQ); cudaFree(s.shadowQ);
     cudaFree(s.counters); cudaFree(s.rayCounters);
     if (e.pinnedCounters) cudaFreeHost(e.pinnedCounters);
-    if (e.evRead) cudaEventDestroy(e.evRead);
+    for (int i = 0; i < 2; ++i) if (e.evRead[i]) cudaEventDestroy(e.evRead[i]);
+    for (cudaEvent_t ev : e.evPool) cudaEventDestroy(ev);
     e = WfEngine();
 }
 
@@ -55,7 +58,16 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
     WfState& st = eng.st;
     unsigned long long poolWanted = P.totalIds < (unsigned long long)st.capacity ? P.totalIds : (unsigned long long)st.capacity;
     int pool = (int)poolWanted;
-    unsigned long long launches = 0;
+    unsigned long long launches = 0, stageLaunches[4] = {0, 0, 0, 0};
+    const bool profTime = (scene->profileFlags & 1) != 0, profCount = (scene->profileFlags & 2) != 0;
+    TravCounters cnt{scene->d_counters, scene->d_counters + 1};
+    if (profCount) cudaMemsetAsync(scene->d_counters, 0, 2 * sizeof(unsigned long long), stream);
+    size_t evUsed = 0;
+    auto mark = [&]() {             // stage boundary event (profile bit 0)
+        if (!profTime) return;
+        if (evUsed == eng.evPool.size()) { cudaEvent_t e; cudaEventCreate(&e); eng.evPool.push_back(e); }
+        cudaEventRecord(eng.evPool[evUsed++], stream);
+    };
     cudaEventRecord(scene->ev0, stream);
     if (pool > 0) {
         cudaMemsetAsync(st.rayCounters, 0, 4 * sizeof(unsigned long long), stream);
@@ -63,26 +75,37 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
         ++launches;
         const int grid = smCount() * 8;
         int cur = 0;
-        bool first = true;
+        // Batches of kBatch iterations are enqueued back to back; the "anything left?" counter of batch b is read while
+        // batch b+1 is already queued, so the GPU never waits for the host (one surplus batch of no-op launches at the end).
+        const int kBatch = 4;
+        int pending = -1;           // pinned slot whose copy is in flight
         for (long iter = 0;; ++iter) {
-            if (!first) {
+            mark();
+            if (iter > 0) {
                 wfAdvance<<<1, 32, 0, stream>>>(st.counters);
-                wfExtend<<<grid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur]);
-                launches += 2;
+                if (profCount) wfExtend<true><<<grid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
+                else wfExtend<false><<<grid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
+                launches += 2; stageLaunches[0] += 1; stageLaunches[3] += 1;
             }
+            mark();
             wfShade<<<grid, kWfThreads, 0, stream>>>(sc, st, P, st.extendQ[cur ^ 1]);
+            mark();
             wfShadow<<<grid, kWfThreads, 0, stream>>>(sc, st, d_colors);
-            launches += 2;
+            mark();
+            launches += 2; stageLaunches[1] += 1; stageLaunches[2] += 1;
             cur ^= 1;
-            first = false;
-            if ((iter & 3) == 3) {      // every 4th iteration: is anything still in flight?
-                cudaMemcpyAsync(eng.pinnedCounters, st.counters, C_TOTAL * sizeof(int), cudaMemcpyDeviceToHost, stream);
-                cudaEventRecord(eng.evRead, stream);
-                cudaError_t e = cudaEventSynchronize(eng.evRead);
-                if (e != cudaSuccess) return (int)e;
-                if (eng.pinnedCounters[C_NEXT_COUNT] == 0) break;
+            if ((iter % kBatch) == kBatch - 1) {
+                int slot = (int)((iter / kBatch) & 1);
+                if (pending >= 0) {
+                    cudaError_t e = cudaEventSynchronize(eng.evRead[pending]);
+                    if (e != cudaSuccess) return (int)e;
+                    if (eng.pinnedCounters[pending * C_TOTAL + C_NEXT_COUNT] == 0) break;
+                }
+                cudaMemcpyAsync(eng.pinnedCounters + slot * C_TOTAL, st.counters, C_TOTAL * sizeof(int), cudaMemcpyDeviceToHost, stream);
+                cudaEventRecord(eng.evRead[slot], stream);
+                pending = slot;
             }
-            if (iter > 2000000) return (int)cudaErrorLaunchTimeout;
+            if (iter > 4000000) return (int)cudaErrorLaunchTimeout;
         }
     }
     cudaEventRecord(scene->ev1, stream);
@@ -96,6 +119,17 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
         stats->closestRays = rc[0]; stats->shadowRays = rc[1]; stats->paths = rc[3];
         stats->kernelLaunches = launches;
         cudaEventElapsedTime(&stats->deviceMs, scene->ev0, scene->ev1);
+        for (int k = 0; k < 4; ++k) stats->stageLaunches[k] = stageLaunches[k];
+        if (profTime) {
+            for (size_t i = 0; i + 3 < evUsed; i += 4)
+                for (int k = 0; k < 3; ++k) { float ms = 0; cudaEventElapsedTime(&ms, eng.evPool[i + k], eng.evPool[i + k + 1]); stats->stageMs[k] += ms; }
+            stats->stageMs[3] = stats->deviceMs - stats->stageMs[0] - stats->stageMs[1] - stats->stageMs[2];
+        }
+        if (profCount) {
+            unsigned long long c2[2] = {0, 0};
+            cudaMemcpy(c2, scene->d_counters, sizeof(c2), cudaMemcpyDeviceToHost);
+            stats->bvhNodeVisits = c2[0]; stats->triTests = c2[1];
+        }
     }
     return 0;
 }

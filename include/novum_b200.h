@@ -159,7 +159,9 @@ typedef struct NovumRenderStats {
     uint64_t kernelLaunches;
     float    deviceMs;                 /* CUDA-event time of the sample loop on the launch stream */
     float    _pad;
-    uint64_t bvhNodeVisits, triTests;  /* only filled by the counter build / counter mode */
+    uint64_t bvhNodeVisits, triTests;  /* closest-hit traversal only; filled when profile bit 1 is set */
+    float    stageMs[4];               /* profile bit 0: CUDA-event time of [0] extend (closest hit) [1] shade [2] shadow [3] other */
+    uint64_t stageLaunches[4];
 } NovumRenderStats;
 
 typedef struct NovumScene NovumScene;  /* opaque: device geometry + BVH8 + materials + lights */
@@ -207,6 +209,9 @@ int  novum_trace_shadow(NovumScene* s, const NovumRay* rays, const float* maxT, 
 /* last trace's device time in ms (CUDA events on the library stream) and counters */
 int  novum_trace_last_ms(NovumScene* s, float* ms);
 int  novum_trace_counters(NovumScene* s, int enable, uint64_t* nodeVisits, uint64_t* triTests);
+/* profiling switches for subsequent renders on this scene: bit 0 = per-stage CUDA-event timing (4 events per
+ * wavefront iteration), bit 1 = count BVH8 node visits / triangle tests in the closest-hit stage (slower kernel). */
+int  novum_set_profile(NovumScene* s, int flags);
 
 /* ---- integrators ------------------------------------------------------------------------ */
 int  novum_update_constants(const NovumConstants* c);                 /* deviceCode.cu:38 */

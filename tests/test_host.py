@@ -1,0 +1,100 @@
+"""Host front end kept from the reference: config parser (objects.cuh:844-943), material table (main.cu:397-467),
+camera basis (objects.cuh:221-325), scene generator output. No GPU needed."""
+import math
+import os
+
+import numpy as np
+
+import cudapathtracer_b200 as nb
+from scene_utils import parse_config
+
+
+def test_config_roundtrip(scene_dirs):
+    cfg = nb.load_config(os.path.join(scene_dirs["cornell"], "configs", "config.rendertron"))
+    assert (cfg.width, cfg.height, cfg.sampleCount, cfg.maxDepth, cfg.bvhLeafSize) == (512, 512, 64, 40, 2)
+    assert cfg.integrator == 0 and cfg.pinholeCamera == 1 and cfg.numMeshes == 6
+    assert cfg.bdptEyeDepth == 16 and cfg.bdptLightDepth == 10
+    assert abs(cfg.vcmMergeConst - 0.7) < 1e-7 and abs(cfg.vcmInitialMergeRadiusMultiplier - 0.01) < 1e-9
+    assert list(cfg.camPos) == [0.0, 0.0, 1.0] and cfg.camFov == 60.0
+
+
+def test_config_accepts_both_spellings_of_radius_key(tmp_path):
+    """configs/config.rendertron:27 says 'Multipler', objects.cuh:939 matches 'Multiplier' (SURVEY F10)."""
+    for key in ("VCM Initial Merge Radius Multiplier", "VCM Initial Merge Radius Multipler"):
+        p = tmp_path / "c.rendertron"
+        p.write_text(f"width: 8\nheight: 4\nIntegrator: SPPM\nBDPT_NEE: true\n{key}: 0.25\nMeshes (x):\na.obj; 2.0 * (1.0, 0.5, 0.0); 3\n")
+        cfg = nb.load_config(str(p))
+        assert cfg.vcmInitialMergeRadiusMultiplier == 0.25
+        # SPPM forces the connection strategies off and merging on (main.cu:314-333)
+        assert cfg.integrator == 4 and cfg.doSPPM == 1 and cfg.vcmDoMerge == 1 and cfg.bdptNee == 0 and cfg.bdptDoMis == 0
+        assert cfg.numMeshes == 1
+
+
+def test_config_missing_file_is_an_error():
+    try:
+        nb.load_config("/nonexistent/config.rendertron")
+    except nb.NovumError as e:
+        assert "file" in str(e)
+    else:
+        raise AssertionError("expected NovumError")
+
+
+def test_integrator_names(tmp_path):
+    for name, want in (("UNIDIRECTIONAL", 0), ("BIDIRECTIONAL", 1), ("BDPT", 1), ("NAIVE_UNIDIRECTIONAL", 2), ("VCM", 3), ("SPPM", 4),
+                       ("nope", -1)):
+        p = tmp_path / "c.rendertron"
+        p.write_text(f"Integrator: {name}\n")
+        assert nb.load_config(str(p)).integrator == want
+
+
+def test_material_table_matches_reference_values():
+    m = nb.material_table()
+    assert len(m) == 24
+    assert m["type"][0] == 2 and m["priority"][0] == 99 and m["ior"][0] == 1.0                 # air
+    assert m["type"][5] == 2 and m["ior"][5] == 1.5 and m["priority"][5] == 1 and m["isSpecular"][5] == 1 and m["boundary"][5] == 1
+    assert m["type"][4] == 1 and np.allclose(m["eta"][4][:3], [0.17, 0.35, 1.5]) and np.allclose(m["k"][4][:3], m["eta"][4][:3])
+    assert abs(m["roughness"][4] - 0.05) < 1e-7 and abs(m["roughness"][7] - 0.15) < 1e-7
+    assert np.allclose(m["absorption"][8][:3], [2.5 * 0.18, 2.5 * 1.5, 2.5 * 2.996])            # tea
+    assert m["priority"][9] == 0 and abs(m["ior"][9] - 1.31) < 1e-7 and m["priority"][10] == 2
+    assert m["type"][13] == 4 and abs(m["transmission"][13] - 0.15) < 1e-7 and m["thinWalled"][13] == 1
+    assert m["type"][19] == 6 and m["isSpecular"][19] == 1 and m["boundary"][19] == 0
+    assert np.allclose(m["albedo"][2][:3], 0.9) and np.allclose(m["albedo"][6][:3], [0.9, 0.1, 0.1]) and np.allclose(m["albedo"][23][:3], [0.1, 0.9, 0.1])
+    # fields the reference leaves indeterminate are zero here
+    assert not m["hasTransMap"].any() and m["isSpecular"][[1, 2, 3, 4, 6, 7]].sum() == 0
+
+
+def test_camera_basis_and_pinhole_quirks(scene_dirs):
+    cfg = nb.load_config(os.path.join(scene_dirs["cornell"], "configs", "config.rendertron"))
+    cam = nb.camera_make(cfg)
+    assert abs(cam.fovScale - math.tan(30 * 3.141592 / 180)) < 1e-6
+    assert abs(cam.aperture - 1e-6) < 1e-12 and abs(cam.focalDist - 1.0 / 60.0) < 1e-9     # objects.cuh:235-236
+    assert cam.antiAliasJitterDist == 2.0
+    f = np.array([cam.forward.x, cam.forward.y, cam.forward.z]); r = np.array([cam.right.x, cam.right.y, cam.right.z])
+    u = np.array([cam.up.x, cam.up.y, cam.up.z])
+    assert np.allclose(f, [0, 0, -1]) and np.allclose(r, [1, 0, 0]) and np.allclose(u, [0, 1, 0])
+    cfg.camRot[1] = 90.0
+    cam = nb.camera_make(cfg)
+    f = np.array([cam.forward.x, cam.forward.y, cam.forward.z])
+    assert np.allclose(f, [-1, 0, 0], atol=1e-6)
+
+
+def test_generated_scenes_have_normals_and_uvs(scene_dirs, py_scenes):
+    for name in ("cornell", "dragon", "water"):
+        cfg, pos, nrm, uv, tris, mats = py_scenes[name]
+        assert len(tris) > 0 and (tris["naInd"] >= 0).all() and (tris["uvaInd"] >= 0).all()
+        assert (tris["emission"][:, :3].sum(1) > 0).sum() >= 2            # a quad light = 2 triangles
+        assert np.isfinite(pos).all() and np.isfinite(nrm).all()
+        ln = np.linalg.norm(nrm[:, :3], axis=1)
+        assert (ln > 0.99).all() and (ln < 1.01).all()
+    assert len(py_scenes["cornell"][4]) == 36                              # (5 room + 12 box + 1 light) quads x 2
+    cfgd, meshes = parse_config(os.path.join(scene_dirs["dragon"], "configs", "config.rendertron"))
+    assert cfgd["Integrator"] == "UNIDIRECTIONAL" and cfgd["width"] == "1920" and cfgd["Sample Count"] == "1024"
+    assert meshes[0][0] == "scenedata/dragon_vrip.obj" and meshes[0][2] == 5
+
+
+def test_dragon_full_detail_triangle_count(tmp_path):
+    """The stand-in for dragon_vrip.obj has the reference asset's scale: ~871k triangles."""
+    d = str(tmp_path / "dragon")
+    nb.make_scene("dragon", d, 100)
+    n = sum(1 for l in open(os.path.join(d, "scenedata", "dragon_vrip.obj")) if l.startswith("f "))
+    assert 860_000 <= n <= 880_000, n
