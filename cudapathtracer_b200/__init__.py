@@ -5,6 +5,6 @@ package only loads it for tests and bench.py. There is no CPU fallback: a missin
 raises, loudly.
 """
 from .binding import (  # noqa: F401
-    NovumError, lib, lib_path, Scene, HashGrid, RenderConfig, Camera, RenderStats, Shard, Constants,
+    NovumError, lib, lib_path, Scene, HashGrid, VcmSession, RenderConfig, Camera, RenderStats, Shard, Constants,
     make_scene, load_config, material_table, camera_make, device_count, DECLARED_SYMBOLS,
 )

@@ -135,6 +135,7 @@ def _declare(L):
     L.novum_vcm_build_grid.argtypes = [vp, ci]
     L.novum_vcm_eye_pass.argtypes = [vp, ci, vp]
     L.novum_vcm_stats.argtypes = [vp, C.POINTER(RenderStats)]
+    L.novum_vcm_stream.argtypes = [vp, C.POINTER(vp)]
 
 
 def _check(rc, what):
@@ -317,3 +318,61 @@ class HashGrid:
         ms = C.c_float()
         _check(lib().novum_hashgrid_last_ms(self.h, C.byref(ms)), "novum_hashgrid_last_ms")
         return ms.value
+
+
+class _DevBuf:
+    """Zero-copy view of a device allocation for torch.as_tensor (CUDA array interface v2)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+class VcmSession:
+    """Phase API of the bidirectional engine for one rank of a tile-sharded render (include/novum_b200.h, novum_vcm_*):
+    light_pass -> all-gather of slabs() by the caller -> build_grid -> eye_pass."""
+
+    def __init__(self, scene, cfg, cam, rank=0, world=1, seed=103033):
+        self.h = C.c_void_p()
+        self.scene, self.rank, self.world = scene, rank, world
+        _check(lib().novum_vcm_create(scene.h, C.byref(cfg), C.byref(cam), Shard(rank, world), seed, C.byref(self.h)), "novum_vcm_create")
+        base, slab, total = C.c_void_p(), C.c_uint64(), C.c_uint64()
+        _check(lib().novum_vcm_cache_buffer(self.h, C.byref(base), C.byref(slab), C.byref(total)), "novum_vcm_cache_buffer")
+        self.base, self.slab_bytes, self.total_bytes = base.value, slab.value, total.value
+
+    def close(self):
+        if self.h:
+            lib().novum_vcm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def light_pass(self, it, d_colors):
+        _check(lib().novum_vcm_light_pass(self.h, int(it), C.c_void_p(d_colors)), "novum_vcm_light_pass")
+
+    def build_grid(self, it):
+        _check(lib().novum_vcm_build_grid(self.h, int(it)), "novum_vcm_build_grid")
+
+    def eye_pass(self, it, d_colors):
+        _check(lib().novum_vcm_eye_pass(self.h, int(it), C.c_void_p(d_colors)), "novum_vcm_eye_pass")
+
+    def stats(self):
+        st = RenderStats()
+        _check(lib().novum_vcm_stats(self.h, C.byref(st)), "novum_vcm_stats")
+        return st
+
+    def stream(self):
+        s = C.c_void_p()
+        _check(lib().novum_vcm_stream(self.h, C.byref(s)), "novum_vcm_stream")
+        return s.value
+
+    def slabs_tensor(self):
+        """All ranks' photon slabs as one uint8 torch tensor on the current device (in-place all-gather target)."""
+        import torch
+        return torch.as_tensor(_DevBuf(self.base, self.total_bytes), device="cuda")
+
+    def my_slab_tensor(self):
+        return self.slabs_tensor()[self.rank * self.slab_bytes:(self.rank + 1) * self.slab_bytes]

@@ -75,9 +75,10 @@ struct RaySetup {
 NV_D RaySetup setupRay(V3 o, V3 d) {
     RaySetup r; r.o = o; r.d = d;
     const float tiny = 1e-30f;
-    r.idir.x = 1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
-    r.idir.y = 1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
-    r.idir.z = 1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+    // the sign of the substitute must agree with the `d < 0` tests below and in intersectNode: -0.0f counts as positive
+    r.idir.x = 1.0f / (fabsf(d.x) > tiny ? d.x : (d.x < 0.0f ? -tiny : tiny));
+    r.idir.y = 1.0f / (fabsf(d.y) > tiny ? d.y : (d.y < 0.0f ? -tiny : tiny));
+    r.idir.z = 1.0f / (fabsf(d.z) > tiny ? d.z : (d.z < 0.0f ? -tiny : tiny));
     unsigned oct = (d.x < 0.0f ? 4u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 1u : 0u);
     r.octinv4 = (7u - oct) * 0x01010101u;
     return r;

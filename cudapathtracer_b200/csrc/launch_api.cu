@@ -5,6 +5,8 @@
 #include "scene.h"
 #include <cstring>
 
+namespace nv { const NovumConstants& currentConstants(); }   // wavefront.cu: what novum_update_constants stored
+
 namespace {
 
 int nMatFromTriangles(const NovumTriangle* d_scene, int triNum) {
@@ -24,6 +26,11 @@ int runShim(int integrator, int maxDepth, int eyeDepth, int lightDepth, const No
     cfg.width = w; cfg.height = h; cfg.integrator = integrator; cfg.sampleCount = numSample; cfg.maxDepth = maxDepth;
     cfg.bdptEyeDepth = eyeDepth; cfg.bdptLightDepth = lightDepth;
     cfg.vcmMergeConst = mergePower; cfg.vcmInitialMergeRadiusMultiplier = radiusMult;
+    // the reference's kernels read the strategy toggles from __constant__ memory set by updateConstants (deviceCode.cu:9-51)
+    const NovumConstants& k = nv::currentConstants();
+    cfg.sampleEnvironment = k.sampleEnvironment; cfg.bdptLightTrace = k.bdptLightTrace; cfg.bdptNee = k.bdptNee; cfg.bdptNaive = k.bdptNaive;
+    cfg.bdptConnection = k.bdptConnection; cfg.vcmDoMerge = k.vcmDoMerge; cfg.doSPPM = k.doSPPM; cfg.bdptDrawPath = k.bdptDrawPath;
+    cfg.bdptDoMis = k.bdptDoMis; cfg.bdptPaintWeight = k.bdptPaintWeight;
     NovumShard shard = {0, 1};
     rc = novum_render_device(s, &cfg, &cam, 0, numSample, shard, 103033ull /* deviceCode.cu:215 */, colors, nullptr);
     novum_scene_destroy(s);

@@ -1,15 +1,602 @@
-// vcm.cu — placeholder until the VCM / SPPM / BDPT engine lands (next milestone).
+// vcm.cu — kernels of the bidirectional wavefront engine: VCM, SPPM (= VCM with connections off, one merge per path) and
+// BDPT (no merging, the reference's older weighting). See vcm.cuh for the data layout and the stage list.
+// Bounce-by-bounce semantics follow generateVCMLightPath / doLightPass / connect* / doEyePass (deviceCode.cu:1958-3065) in
+// VCM mode and generateEyePath / generateLightPath / lightPathTracing / connectPath (:751-1765) in BDPT mode, including
+// the quirks results depend on: G clamps 15 (NEE, :681) and 2 (connections, :1753, :2675), the firefly clamp lum > 5
+// (:1637, :2952), the squared NEE ratio in VCM (:2526) vs the plain one in BDPT (:1519), placeholder etaI = etaT = 1
+// (:851, :1177, :2078), un-normalised "to previous vertex" vectors in the VCM connection code (:2493, :2629, :3004),
+// every one of the 27 neighbour cells looked up even when two of them hash to the same slot (:2974-2992).
+#include "vcm.cuh"
 #include "scene.h"
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
 namespace nv {
-int vcmRenderDevice(NovumScene*, const NovumRenderConfig*, const NovumCamera*, int, int, NovumShard, unsigned long long, float4*,
-                    NovumRenderStats*) { return NOVUM_E_UNSUPPORTED; }
+
+constexpr int kBdThreads = 128;
+
+__device__ __forceinline__ int bdLane() { return threadIdx.x & 31; }
+
+__device__ __forceinline__ int bdWarpAppend(int* counter, bool pred) {
+    unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return -1;
+    int leader = __ffs(m) - 1;
+    int base = 0;
+    if (bdLane() == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return pred ? base + __popc(m & ((1u << bdLane()) - 1u)) : -1;
 }
-extern "C" {
-int novum_vcm_create(NovumScene*, const NovumRenderConfig*, const NovumCamera*, NovumShard, uint64_t, NovumVcmState**) { return NOVUM_E_UNSUPPORTED; }
-void novum_vcm_destroy(NovumVcmState*) {}
-int novum_vcm_light_pass(NovumVcmState*, int, NovumFloat4*) { return NOVUM_E_UNSUPPORTED; }
-int novum_vcm_cache_buffer(NovumVcmState*, void**, uint64_t*, uint64_t*) { return NOVUM_E_UNSUPPORTED; }
-int novum_vcm_build_grid(NovumVcmState*, int) { return NOVUM_E_UNSUPPORTED; }
-int novum_vcm_eye_pass(NovumVcmState*, int, NovumFloat4*) { return NOVUM_E_UNSUPPORTED; }
-int novum_vcm_stats(NovumVcmState*, NovumRenderStats*) { return NOVUM_E_UNSUPPORTED; }
+
+// opportunistic aggregation for appends issued from divergent code: the lanes that happen to be converged here share one atomic
+__device__ __forceinline__ int bdAggAppend(int* counter) {
+    unsigned m = __activemask();
+    int leader = __ffs(m) - 1;
+    int base = 0;
+    if (bdLane() == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(m, base, leader);
+    return base + __popc(m & ((1u << bdLane()) - 1u));
 }
+
+NV_D uint32_t packHalf2(float a, float b) { __half2 h = __halves2half2(__float2half(a), __float2half(b)); return *reinterpret_cast<uint32_t*>(&h); }
+NV_D float2 unpackHalf2(uint32_t u) { __half2 h = *reinterpret_cast<__half2*>(&u); return __half22float2(h); }
+
+struct LightVtx { V3 p, n, wo, beta; float2 uv; bool delta, backface; int mat; float d_vc, d_vcm; };
+
+// quantises v in place to what the cache holds and writes the three words
+NV_D void storeLightVtx(const BdState& st, size_t idx, LightVtx& v) {
+    uint32_t pn = packOct(v.n), pw = packOct(v.wo);
+    uint32_t bxy = packHalf2(v.beta.x, v.beta.y), bz = packHalf2(v.beta.z, 0.0f), puv = packHalf2(v.uv.x, v.uv.y);
+    uint32_t info = (v.delta ? 1u : 0u) | (v.backface ? 2u : 0u) | (0xFFFFEu << 2) | (((uint32_t)v.mat & 0x3FFu) << 22);   // objects.cuh:993-1005
+    st.lvA[idx] = make_uint4(__float_as_uint(v.p.x), __float_as_uint(v.p.y), __float_as_uint(v.p.z), pn);
+    st.lvB[idx] = make_uint4(pw, bxy, bz, puv);
+    st.lvC[idx] = make_uint4(info, __float_as_uint(v.d_vc), __float_as_uint(v.d_vcm), 0u);
+    v.n = unpackOct(pn); v.wo = unpackOct(pw);
+    float2 a = unpackHalf2(bxy), b = unpackHalf2(bz), c = unpackHalf2(puv);
+    v.beta = V3(a.x, a.y, b.x); v.uv = c;
+}
+NV_D LightVtx loadLightVtx(const BdState& st, size_t idx) {
+    uint4 A = __ldg(st.lvA + idx), B = __ldg(st.lvB + idx), C = __ldg(st.lvC + idx);
+    LightVtx v;
+    v.p = V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
+    v.n = unpackOct(A.w); v.wo = unpackOct(B.x);
+    float2 a = unpackHalf2(B.y), b = unpackHalf2(B.z);
+    v.beta = V3(a.x, a.y, b.x); v.uv = unpackHalf2(B.w);
+    v.delta = C.x & 1u; v.backface = (C.x >> 1) & 1u; v.mat = (int)((C.x >> 22) & 0x3FFu);
+    v.d_vc = __uint_as_float(C.y); v.d_vcm = __uint_as_float(C.z);
+    return v;
+}
+
+struct BdPath {
+    V3 o, d, beta, prevP;
+    float pdfPrevSA, prevCos, pdfOneBefore, d_vcm, d_vc, d_vm, aux;
+    bool prevDelta;
+    Rng rng;
+};
+NV_D void loadBdPath(const BdState& st, int l, BdPath& p) {
+    float4 a = st.rayO[l], b = st.rayD[l], c = st.beta[l], e = st.prevP[l], f = st.dv[l];
+    p.o = V3(a.x, a.y, a.z); p.pdfPrevSA = a.w;
+    p.d = V3(b.x, b.y, b.z); p.prevCos = b.w;
+    p.beta = V3(c.x, c.y, c.z); p.pdfOneBefore = c.w;
+    p.prevP = V3(e.x, e.y, e.z); p.prevDelta = (__float_as_uint(e.w) & 1u) != 0;
+    p.d_vcm = f.x; p.d_vc = f.y; p.d_vm = f.z; p.aux = f.w;
+    p.rng.state = st.rng[l];
+}
+NV_D void storeBdPath(const BdState& st, int l, const BdPath& p) {
+    st.rayO[l] = make_float4(p.o.x, p.o.y, p.o.z, p.pdfPrevSA);
+    st.rayD[l] = make_float4(p.d.x, p.d.y, p.d.z, p.prevCos);
+    st.beta[l] = make_float4(p.beta.x, p.beta.y, p.beta.z, p.pdfOneBefore);
+    st.prevP[l] = make_float4(p.prevP.x, p.prevP.y, p.prevP.z, __uint_as_float(p.prevDelta ? 1u : 0u));
+    st.dv[l] = make_float4(p.d_vcm, p.d_vc, p.d_vm, p.aux);
+    st.rng[l] = p.rng.state;
+}
+
+enum : unsigned { SR_CLAMP = 1u << 31, SR_NEE = 1u << 30, SR_PIXMASK = (1u << 30) - 1u };
+
+NV_D void pushShadow(const BdState& st, int* cnt, V3 o, V3 d, float maxT, int skip, unsigned pixFlags, V3 contrib) {
+    if (contrib.x == 0.0f && contrib.y == 0.0f && contrib.z == 0.0f) return;
+    int pos = bdAggAppend(&cnt[BC_SHADOW]);
+    if (pos >= st.shadowCap) return;
+    float4* rec = reinterpret_cast<float4*>(st.shadowQ + pos);
+    rec[0] = make_float4(o.x, o.y, o.z, maxT);
+    rec[1] = make_float4(d.x, d.y, d.z, __uint_as_float(pixFlags));
+    rec[2] = make_float4(contrib.x, contrib.y, contrib.z, __int_as_float(skip));
+}
+
+NV_D V3 camFwd(const NovumCamera& c) { return V3(c.forward.x, c.forward.y, c.forward.z); }
+NV_D V3 camOrg(const NovumCamera& c) { return V3(c.cameraOrigin.x, c.cameraOrigin.y, c.cameraOrigin.z); }
+NV_D float imagePlaneArea(const BdParams& P) { return 4.0f * ((float)P.w / (float)P.h) * P.cam.fovScale * P.cam.fovScale; }
+NV_D V3 applyWeight(const BdParams& P, V3 unweighted, float w) {
+    if (P.paintWeight) return V3(w);
+    return P.doMis ? unweighted * w : unweighted;
+}
+NV_D V3 fireflyClamp(V3 c) {
+    float lum = luminance(c);
+    return lum > kMaxFireflyLum ? c * (kMaxFireflyLum / lum) : c;
+}
+NV_D float triArea(const SceneView& sc, const NovumTriangle* t) {
+    int4 idx = __ldg(reinterpret_cast<const int4*>(t));
+    V3 a(__ldg(sc.positions + idx.x)), b(__ldg(sc.positions + idx.y)), c(__ldg(sc.positions + idx.z));
+    return 0.5f * length(cross(b - a, c - a));
+}
+
+// t = 1 strategy: connect a light-path vertex to the camera and splat (deviceCode.cu:1310-1430, :2266-2382).
+// v holds the quantised vertex; f is evaluated here unless the vertex is the point on the light itself (BDPT s = 1).
+NV_D void lightTraceSplat(const SceneView& sc, const BdState& st, const BdParams& P, int* cnt, const LightVtx& v, bool onLight, float pdfSampleY0) {
+    float rx, ry;
+    if (!worldToRaster(P.cam, v.p, rx, ry)) return;
+    int px = (int)rx, py = (int)ry;
+    if (px >= P.w || py >= P.h) return;       // ndc == +1 lands one past the edge in the reference (out-of-range write there)
+    if (v.delta) return;
+    V3 toCam = camOrg(P.cam) - v.p;
+    V3 dirU = normalize(toCam);
+    float cosAtLight = dot(v.n, dirU);
+    float cosAtCamera = fabsf(dot(camFwd(P.cam), -dirU));
+    if (cosAtLight <= kEps) return;
+    float A = imagePlaneArea(P);
+    float We = 1.0f / (A * cosAtCamera * cosAtCamera * cosAtCamera * cosAtCamera);
+    float dSq = fmaxf(lengthSq(toCam), kRayEps);
+    float G = (cosAtLight * cosAtCamera) / dSq;
+    float pdfCurrRevArea = cosAtLight / (dSq * A * cosAtCamera * cosAtCamera * cosAtCamera);
+    V3 f; float wLight;
+    if (onLight) {
+        f = V3(1.0f / kPi);
+        wLight = pdfCurrRevArea / pdfSampleY0;
+    } else {
+        Frame fl(v.n);
+        V3 currToPrevL = fl.toLocal(v.wo), toCamL = fl.toLocal(dirU);
+        Shading sh = resolveShading(sc.mats, v.mat, sc.textures, v.uv);
+        f = bsdfEval(sh, -currToPrevL, toCamL, 1.0f);
+        float pdfOne = bsdfPdf(sh, -toCamL, currToPrevL, 1.0f);
+        wLight = pdfCurrRevArea * (P.etaVcm + v.d_vcm + pdfOne * v.d_vc);
+    }
+    V3 contrib = v.beta * f * (G * We);
+    float w = 1.0f / (1.0f + wLight);
+    pushShadow(st, cnt, v.p + v.n * kRayEps, dirU, length(toCam) - kRayEps, -1, (unsigned)(py * P.w + px), applyWeight(P, contrib, w));
+}
+
+// ---- light pass -----------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBdThreads) bdLightStart(SceneView sc, BdState st, BdParams P) {
+    int l = blockIdx.x * blockDim.x + threadIdx.x;
+    bool active = false;
+    int* cnt = st.counters;
+    if (l < P.nLocal) {
+        int x, y;
+        int pix = localToPixel(P, l, x, y);
+        st.pathLen[l] = 0;
+        BdPath p;
+        p.rng.seed(P.seed, (unsigned long long)pix, (unsigned long long)P.iter, 1);
+        int nl = sc.numLights;
+        int lightInd = P.sampleEnv ? (min((int)(p.rng.uniform() * (nl + 1)), nl) - 1) : min((int)(p.rng.uniform() * nl), nl - 1);
+        float pdfChoose = 1.0f / (float)(P.sampleEnv ? nl + 1 : nl);
+        if (lightInd >= 0) {        // -1 = the (black) environment: the reference returns an empty path (:1982)
+            const NovumTriangle* lt = sc.lights + lightInd;
+            int4 q0 = __ldg(reinterpret_cast<const int4*>(lt)), q1 = __ldg(reinterpret_cast<const int4*>(lt) + 1);
+            float4 em = __ldg(reinterpret_cast<const float4*>(lt) + 3);
+            V3 a(__ldg(sc.positions + q0.x)), b(__ldg(sc.positions + q0.y)), c(__ldg(sc.positions + q0.z));
+            V3 an(__ldg(sc.normals + q0.w)), bn(__ldg(sc.normals + q1.x)), cn(__ldg(sc.normals + q1.y));
+            float area = 0.5f * length(cross(b - a, c - a));
+            float pdfPos = pdfChoose / area;
+            float u = sqrtf(p.rng.uniform()), v = p.rng.uniform();
+            float w0 = 1.0f - u, w1 = u * (1.0f - v), w2 = u * v;
+            V3 y0 = w0 * a + w1 * b + w2 * c;
+            V3 n0 = normalize(w0 * an + w1 * bn + w2 * cn);
+            V3 woL = cosineSample(p.rng);
+            float pdfSA = cosinePdf(woL);
+            V3 dirW = Frame(n0).toWorld(woL);
+            p.o = y0 + n0 * kRayEps; p.d = dirW;
+            p.beta = V3(em.x, em.y, em.z) * kPi / pdfPos;
+            p.prevCos = fabsf(dot(normalize(dirW), n0));
+            p.pdfPrevSA = P.mode == BD_MODE_BDPT ? p.prevCos / kPi : pdfSA;       // :1101 vs :2010
+            p.pdfOneBefore = -1.0f; p.prevP = y0; p.prevDelta = false;
+            p.d_vcm = p.d_vc = p.d_vm = -1.0f; p.aux = pdfPos;
+            storeBdPath(st, l, p);
+            active = true;
+            if (P.mode == BD_MODE_BDPT && P.lightTrace) {      // s = 1, t = 1: the sampled light point seen directly by the camera (:1357-1389)
+                LightVtx v; v.p = y0; v.n = n0; v.wo = V3(0.0f); v.beta = p.beta; v.uv = make_float2(0.f, 0.f); v.delta = false; v.backface = false;
+                v.mat = 0; v.d_vc = 0.f; v.d_vcm = 0.f;
+                lightTraceSplat(sc, st, P, cnt, v, true, pdfPos);
+            }
+        }
+    }
+    int pos = bdWarpAppend(&cnt[BC_QUEUE], active);
+    if (active) st.queue[0][pos] = l;
+}
+
+// closest hit for every queued path of this depth
+__global__ void __launch_bounds__(kBdThreads) bdExtend(SceneView sc, BdState st, const int* __restrict__ queue, int* cnt) {
+    __shared__ uint2 stackMem[kSmemStack * kBdThreads];
+    TravStack ts; ts.init(stackMem + threadIdx.x, kBdThreads);
+    const int lane = bdLane();
+    const int n = cnt[BC_QUEUE];
+    TravCounters nocnt{nullptr, nullptr};
+    unsigned long long traced = 0;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_EXTEND], 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        if (i < n) {
+            int l = __ldg(queue + i);
+            float4 o = st.rayO[l], d = st.rayD[l];
+            HitRec h = traceClosest<false>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, nocnt);
+            st.hit[l] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
+            ++traced;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
+    if (lane == 0 && traced) atomicAdd(&st.stats[0], traced);
+}
+
+// vertex processing shared by both walks: forward area pdf, BSDF sample, reverse pdf, d_vcm / d_vc / d_vm recurrences
+struct StepOut { Surface s; Shading sh; V3 woL, wiL, wiW, currBeta; float d_vcm, d_vc, d_vm; bool delta; };
+
+NV_D bool walkVertex(const SceneView& sc, const BdParams& P, BdPath& p, const float4 hf, bool lightWalk, bool first, StepOut& o) {
+    HitRec h; h.tri = __float_as_int(hf.x); h.t = hf.y; h.u = hf.z; h.v = hf.w; h.flags = 0;
+    o.s = makeSurface(sc, h, p.o, p.d);
+    o.sh = resolveShading(sc.mats, o.s.mat, sc.textures, o.s.uv);
+    o.delta = (o.sh.m.flags & MF_SPECULAR) != 0;
+    Frame fr(o.s.n);
+    o.woL = fr.toLocal(p.d);
+    float distSq = fmaxf(lengthSq(o.s.p - p.prevP), kRayEps);
+    float pdfFwdArea = p.pdfPrevSA * fabsf(o.woL.z) / distSq;
+    V3 f; float pdfFwdSA;
+    bsdfSample(p.rng, o.sh, o.woL, 1.0f, o.s.backface, lightWalk ? MODE_IMPORTANCE : MODE_RADIANCE, o.wiL, f, pdfFwdSA);
+    o.wiW = fr.toWorld(o.wiL);
+    float pdfRevSA = bsdfPdf(o.sh, -o.wiL, -o.woL, 1.0f);
+    if (pdfFwdSA < kEps) return false;
+    o.currBeta = p.beta;
+    p.beta = p.beta * f * (fabsf(o.wiL.z) / pdfFwdSA);
+    const float eta = P.etaVcm;                   // 0 in BDPT mode
+    const bool vm = P.mode == BD_MODE_VCM;
+    float G = p.prevCos / distSq;
+    if (first) {
+        if (lightWalk) {                          // :2111-2142, :1211-1239 (pdf_connect == pdf_trace == spatial pdf of the light sample)
+            float pdfTrace = p.aux;
+            o.d_vcm = pdfTrace / (pdfTrace * pdfFwdArea);
+            o.d_vc = G / (pdfTrace * pdfFwdArea);
+            o.d_vm = vm ? G / (pdfTrace * pdfFwdArea * eta) : 0.0f;
+        } else {                                  // :2802-2819, :876-891
+            o.d_vcm = 1.0f / pdfFwdArea; o.d_vc = 0.0f; o.d_vm = 0.0f;
+        }
+    } else if (p.prevDelta) {                     // :2143-2159
+        o.d_vcm = 0.0f;
+        o.d_vc = (G / pdfFwdArea) * (p.pdfOneBefore * p.d_vc);
+        o.d_vm = vm ? (G / pdfFwdArea) * (p.pdfOneBefore * p.d_vm) : 0.0f;
+    } else {                                      // :2160-2181
+        o.d_vcm = 1.0f / pdfFwdArea;
+        o.d_vc = (G / pdfFwdArea) * (eta + p.d_vcm + p.pdfOneBefore * p.d_vc);
+        o.d_vm = vm ? (G / pdfFwdArea) * (1.0f + p.d_vcm / eta + p.pdfOneBefore * p.d_vm) : 0.0f;
+    }
+    p.d_vcm = o.d_vcm; p.d_vc = o.d_vc; p.d_vm = o.d_vm;
+    p.pdfOneBefore = pdfRevSA;
+    p.pdfPrevSA = pdfFwdSA;
+    p.prevCos = fabsf(o.wiL.z);
+    return true;
+}
+
+__global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState st, BdParams P, int step, int numSteps,
+                                                         const int* __restrict__ queue, int* __restrict__ nextQueue) {
+    const int lane = bdLane();
+    int* cnt = st.counters + step * BC_STRIDE;
+    int* nextCnt = st.counters + (step + 1) * BC_STRIDE;
+    const int n = cnt[BC_QUEUE];
+    unsigned long long nVerts = 0, nPhot = 0;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_STEP], 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        bool cont = false;
+        int l = 0;
+        if (i < n) {
+            l = __ldg(queue + i);
+            float4 hf = st.hit[l];
+            if (__float_as_int(hf.x) >= 0) {
+                BdPath p; loadBdPath(st, l, p);
+                V3 inDir = p.d;
+                StepOut o;
+                if (walkVertex(sc, P, p, hf, true, step == 0, o)) {
+                    LightVtx v;
+                    v.p = o.s.p; v.n = o.s.n; v.wo = normalize(-inDir); v.beta = o.currBeta; v.uv = o.s.uv;
+                    v.delta = o.delta; v.backface = o.s.backface; v.mat = o.s.mat; v.d_vc = o.d_vc; v.d_vcm = o.d_vcm;
+                    storeLightVtx(st, (size_t)step * P.nLocal + l, v);           // v now holds the quantised values
+                    st.pathLen[l] = step + 1;
+                    ++nVerts;
+                    if (!o.delta && P.mode == BD_MODE_VCM && P.doMerge) {        // photon for merging (:2206-2221)
+                        int idx = bdAggAppend(reinterpret_cast<int*>(P.slab));
+                        if (idx < P.slabCap) {
+                            uint4* rec = P.slab + (kSlabHeaderBytes / 16) + (size_t)idx * 2;
+                            rec[0] = make_uint4(__float_as_uint(o.s.p.x), __float_as_uint(o.s.p.y), __float_as_uint(o.s.p.z), packOct(normalize(-inDir)));
+                            rec[1] = make_uint4(packHalf2(o.currBeta.x, o.currBeta.y), packHalf2(o.currBeta.z, 0.0f), __float_as_uint(o.d_vm),
+                                                __float_as_uint(o.d_vcm));
+                            ++nPhot;
+                        }
+                    }
+                    if (P.lightTrace) lightTraceSplat(sc, st, P, cnt, v, false, 0.0f);
+                    bool through = P.mode == BD_MODE_BDPT ? (dot(o.wiW, o.s.n) < 0.0f) : (o.wiL.z < kEps);    // :1274 vs :2229
+                    p.o = through ? o.s.p - o.s.n * kRayEps : o.s.p + o.s.n * kRayEps;
+                    p.d = o.wiW;
+                    p.prevDelta = o.delta; p.prevP = o.s.p;
+                    cont = step + 1 < numSteps;
+                    if (cont) storeBdPath(st, l, p);
+                }
+            }
+        }
+        int pos = bdWarpAppend(&nextCnt[BC_QUEUE], cont);
+        if (cont) nextQueue[pos] = l;
+    }
+    for (int o = 16; o > 0; o >>= 1) { nVerts += __shfl_xor_sync(0xffffffffu, nVerts, o); nPhot += __shfl_xor_sync(0xffffffffu, nPhot, o); }
+    if (lane == 0) { if (nVerts) atomicAdd(&st.stats[3], nVerts); if (nPhot) atomicAdd(&st.stats[2], nPhot); }
+}
+
+// any-hit for every deferred connection of this depth; unoccluded ones add their (already MIS-weighted) contribution
+__global__ void __launch_bounds__(kBdThreads) bdResolve(SceneView sc, BdState st, float4* __restrict__ colors, int* cnt) {
+    __shared__ uint2 stackMem[kSmemStack * kBdThreads];
+    TravStack ts; ts.init(stackMem + threadIdx.x, kBdThreads);
+    const int lane = bdLane();
+    const int n = min(cnt[BC_SHADOW], st.shadowCap);
+    TravCounters nocnt{nullptr, nullptr};
+    unsigned long long traced = 0;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_RESOLVE], 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        if (i < n) {
+            const float4* rp = reinterpret_cast<const float4*>(st.shadowQ + i);
+            float4 a = rp[0], b = rp[1], c = rp[2];
+            V3 thr = traceShadow<false>(sc, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, __float_as_int(c.w), ts, nocnt);
+            ++traced;
+            unsigned pf = __float_as_uint(b.w);
+            if (lengthSq(thr) > ((pf & SR_NEE) ? 0.0f : kEps)) {       // :668 (NEE: > 0) vs :1336, :2304, :2599 (> EPSILON)
+                V3 v = V3(c.x, c.y, c.z) * thr;
+                if (pf & SR_CLAMP) v = fireflyClamp(v);
+                atomicAdd(&colors[pf & SR_PIXMASK], make_float4(v.x, v.y, v.z, 0.f));
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
+    if (lane == 0 && traced) atomicAdd(&st.stats[1], traced);
+}
+
+// ---- eye pass ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBdThreads) bdEyeStart(BdState st, BdParams P) {
+    int l = blockIdx.x * blockDim.x + threadIdx.x;
+    bool active = l < P.nLocal;
+    if (active) {
+        int x, y;
+        int pix = localToPixel(P, l, x, y);
+        BdPath p;
+        p.rng.seed(P.seed, (unsigned long long)pix, (unsigned long long)P.iter, 2);
+        cameraRay(P.cam, p.rng, x, y, p.o, p.d);
+        float cosAtCamera = fabsf(dot(camFwd(P.cam), p.d));
+        p.pdfPrevSA = 1.0f / (imagePlaneArea(P) * cosAtCamera * cosAtCamera * cosAtCamera);      // :2706, :778
+        p.prevCos = cosAtCamera;
+        p.beta = V3(1.0f); p.pdfOneBefore = -1.0f;
+        p.prevP = camOrg(P.cam);
+        p.prevDelta = P.mode == BD_MODE_VCM;        // :2719 (true) vs :792 (false)
+        p.d_vcm = p.d_vc = p.d_vm = -1.0f; p.aux = 0.f;
+        storeBdPath(st, l, p);
+    }
+    int pos = bdWarpAppend(&st.counters[BC_QUEUE], active);
+    if (active) st.queue[0][pos] = l;
+}
+
+__global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st, BdParams P, int step, int numSteps,
+                                                       const int* __restrict__ queue, int* __restrict__ nextQueue) {
+    const int lane = bdLane();
+    int* cnt = st.counters + step * BC_STRIDE;
+    int* nextCnt = st.counters + (step + 1) * BC_STRIDE;
+    const int n = cnt[BC_QUEUE];
+    const bool vcm = P.mode == BD_MODE_VCM;
+    const float eta = P.etaVcm;
+    unsigned long long nMerged = 0;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_STEP], 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        bool cont = false;
+        int l = 0;
+        if (i < n) {
+            l = __ldg(queue + i);
+            float4 hf = st.hit[l];
+            if (__float_as_int(hf.x) >= 0) {
+                BdPath p; loadBdPath(st, l, p);
+                const V3 inDir = p.d, prevP = p.prevP;
+                const bool prevDelta = p.prevDelta;
+                StepOut o;
+                if (walkVertex(sc, P, p, hf, false, step == 0, o)) {
+                    int x, y;
+                    const int pix = localToPixel(P, l, x, y);
+                    const Surface& s = o.s;
+                    Frame fr(s.n);
+                    bool endPath = false;
+                    V3 sum(0.0f);
+                    if (!o.delta) {
+                        const unsigned clampFlag = vcm ? SR_CLAMP : 0u;
+                        const float pdfChoose = 1.0f / (float)(P.sampleEnv ? sc.numLights + 1 : sc.numLights);
+                        // vector from this vertex back to the previous one as the reference hands it to the BSDFs:
+                        // un-normalised position difference in VCM (:2493, :2629, :3004), the stored unit wo in BDPT (:1490, :1708)
+                        const V3 toPrevW = vcm ? (prevP - s.p) : normalize(-inDir);
+                        const V3 toPrevL = fr.toLocal(toPrevW);
+                        // ---- s = 0: the walk hit an emitter from its front side ----
+                        if (P.naive && lengthSq(s.emission) > kEps && !s.backface && s.lightInd >= 0) {
+                            float area = triArea(sc, sc.tris + s.tri);
+                            float w; V3 c = s.emission * o.currBeta;
+                            bool clampIt = true;
+                            if (vcm) {                                                           // connectImplicitHit :2389-2458
+                                float cosLight = dot(s.n, normalize(prevP - s.p));
+                                float pdfConnect = prevDelta ? 0.0f : pdfChoose / area;
+                                w = 1.0f / (1.0f + pdfConnect * o.d_vcm + pdfConnect * (cosLight / kPi) * o.d_vc);
+                            } else if (step == 0) {                                              // t == 2 :1567-1595
+                                V3 lightToPrevU = normalize(-inDir);
+                                float cosThetaLight = fabsf(dot(s.n, lightToPrevU));
+                                float cosAtCamera = fabsf(dot(camFwd(P.cam), -lightToPrevU));
+                                float pdfTraceFromCamera = cosThetaLight / (lengthSq(s.p - prevP) * imagePlaneArea(P) * cosAtCamera * cosAtCamera * cosAtCamera);
+                                w = 1.0f / (1.0f + (pdfChoose / area) / pdfTraceFromCamera);
+                                clampIt = false;
+                            } else {                                                             // :1596-1642
+                                float cosThetaLight = fabsf(dot(s.n, normalize(-inDir)));
+                                float pdfConnect = prevDelta ? 0.0f : pdfChoose / area;
+                                w = 1.0f / (1.0f + pdfConnect * o.d_vcm + pdfConnect * (cosThetaLight / kPi) * o.d_vc);
+                                c = fireflyClamp(c);                                             // clamped before weighting in BDPT
+                                clampIt = false;
+                            }
+                            V3 cw = applyWeight(P, c, w);
+                            sum += clampIt ? fireflyClamp(cw) : cw;
+                        }
+                        // ---- s = 1: next-event estimation (BDPTnextEventEstimation :622-705, connectNEE :2460-2546, connectPath :1479-1546) ----
+                        if (P.nee && sc.numLights > 0) {
+                            int nl = sc.numLights;
+                            int lightInd = P.sampleEnv ? (min((int)(p.rng.uniform() * (nl + 1)), nl) - 1) : min((int)(p.rng.uniform() * nl), nl - 1);
+                            if (lightInd >= 0) {
+                                const NovumTriangle* lt = sc.lights + lightInd;
+                                int4 q0 = __ldg(reinterpret_cast<const int4*>(lt)), q1 = __ldg(reinterpret_cast<const int4*>(lt) + 1);
+                                float4 em = __ldg(reinterpret_cast<const float4*>(lt) + 3);
+                                int lightTri = __ldg(&lt->triInd);
+                                V3 a(__ldg(sc.positions + q0.x)), b(__ldg(sc.positions + q0.y)), c(__ldg(sc.positions + q0.z));
+                                V3 an(__ldg(sc.normals + q0.w)), bn(__ldg(sc.normals + q1.x)), cn(__ldg(sc.normals + q1.y));
+                                float u = sqrtf(p.rng.uniform()), v = p.rng.uniform();
+                                float w0 = 1.0f - u, w1 = u * (1.0f - v), w2 = u * v;
+                                V3 lp = w0 * a + w1 * b + w2 * c;
+                                V3 ln = normalize(w0 * an + w1 * bn + w2 * cn);
+                                V3 toL = lp - s.p;
+                                V3 toLU = normalize(toL);
+                                float dSq = fmaxf(lengthSq(toL), kRayEps);
+                                float cosLight = dot(ln, -toLU);
+                                if (cosLight >= kEps) {
+                                    float cosSurf = fabsf(dot(s.n, toLU));
+                                    float G = fminf(cosLight * cosSurf / dSq, 15.0f);
+                                    float area = 0.5f * length(cross(b - a, c - a));
+                                    float pdfConnect = pdfChoose / area;
+                                    float pdfEmit = cosLight / kPi;
+                                    V3 prevToCurrL = -toPrevL;                   // VCM: toLocal(eyePos - prevPos); BDPT: toLocal(-wo)
+                                    V3 toLL = fr.toLocal(toLU);
+                                    V3 f = bsdfEval(o.sh, prevToCurrL, toLL, 1.0f);
+                                    V3 unweighted = f * V3(em.x, em.y, em.z) * (G / pdfConnect) * o.currBeta;
+                                    float pdfBsdfArea = bsdfPdf(o.sh, prevToCurrL, toLL, 1.0f) * fabsf(cosLight) / dSq;
+                                    float ratio = pdfBsdfArea / pdfConnect;
+                                    float wLight = vcm ? ratio * ratio : ratio;               // :2526 vs :1519
+                                    float pdfCurrRevArea = pdfEmit * fabsf(toLL.z) / dSq;
+                                    float pdfOne = bsdfPdf(o.sh, -toLL, -prevToCurrL, 1.0f);
+                                    float wEye = pdfCurrRevArea * (eta + o.d_vcm + pdfOne * o.d_vc);
+                                    float w = 1.0f / (1.0f + wLight + wEye);
+                                    pushShadow(st, cnt, s.p + s.n * kRayEps, toLU, sqrtf(dSq) - kEps, lightTri, (unsigned)pix | clampFlag | SR_NEE,
+                                               applyWeight(P, unweighted, w));
+                                }
+                            }
+                        }
+                        // ---- s >= 2: connect to every stored vertex of this pixel's light path (connectGeneral :2549-2684, connectPath :1653-1762) ----
+                        if (P.connection) {
+                            const int len = st.pathLen[l];
+                            for (int k = 0; k < len; ++k) {
+                                LightVtx lv = loadLightVtx(st, (size_t)k * P.nLocal + l);
+                                if (lv.delta) continue;
+                                V3 e2l = lv.p - s.p;
+                                float dSq = fmaxf(lengthSq(e2l), kRayEps);
+                                float dist = length(e2l);
+                                V3 e2lU = e2l / dist;
+                                float cosLight = fabsf(dot(lv.n, -e2lU)), cosEye = fabsf(dot(s.n, e2lU));
+                                if (cosLight < kEps || cosEye < kEps) continue;
+                                Frame fl(lv.n);
+                                Shading shL = resolveShading(sc.mats, lv.mat, sc.textures, lv.uv);
+                                V3 l2eAtLight = fl.toLocal(-e2lU), toLightFromPrevAtLight = fl.toLocal(-lv.wo);
+                                float pdfEyeRevArea = bsdfPdf(shL, toLightFromPrevAtLight, l2eAtLight, 1.0f) * cosEye / dSq;
+                                V3 l2eAtEye = fr.toLocal(-e2lU);
+                                float pdfOneBeforeEye = bsdfPdf(o.sh, l2eAtEye, toPrevL, 1.0f);
+                                float pdfLightRevArea = bsdfPdf(o.sh, -toPrevL, -l2eAtEye, 1.0f) * cosLight / dSq;
+                                float pdfOneBeforeLight = bsdfPdf(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
+                                float wEye = pdfEyeRevArea * (eta + o.d_vcm + pdfOneBeforeEye * o.d_vc);
+                                float wLight = pdfLightRevArea * (eta + lv.d_vcm + pdfOneBeforeLight * lv.d_vc);
+                                V3 fEye = bsdfEval(o.sh, l2eAtEye, toPrevL, 1.0f);
+                                V3 fLight = bsdfEval(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
+                                float G = fminf(cosEye * cosLight / dSq, 2.0f);
+                                V3 unweighted = o.currBeta * lv.beta * fEye * fLight * G;
+                                float w = 1.0f / (1.0f + wEye + wLight);
+                                pushShadow(st, cnt, s.p + s.n * kRayEps, e2lU, dist - kRayEps, -1, (unsigned)pix | clampFlag, applyWeight(P, unweighted, w));
+                            }
+                        }
+                        // ---- merging with the photons of the 27 neighbouring cells (:2968-3048) ----
+                        if (vcm && P.doMerge) {
+                          if (P.mergeRadius > 0.0f) {
+                            const float r2 = P.mergeRadius * P.mergeRadius;
+                            const int3 c0 = gridIndex(s.p.x, s.p.y, s.p.z, P.grid);
+                            const float norm = 1.0f / (kPi * r2 * (float)P.w * (float)P.h);
+                            for (int dz = -1; dz <= 1; ++dz) for (int dy = -1; dy <= 1; ++dy) for (int dx = -1; dx <= 1; ++dx) {
+                                unsigned hsh = hashCell(make_int3(c0.x + dx, c0.y + dy, c0.z + dz), P.grid.tableSize);
+                                uint32_t cs = __ldg(P.cellStart + hsh);
+                                if (cs == 0xFFFFFFFFu) continue;
+                                uint32_t ce = __ldg(P.cellEnd + hsh);
+                                for (uint32_t q = cs; q < ce; ++q) {
+                                    uint4 A = __ldg(P.photons + (size_t)q * 2);
+                                    V3 diff = s.p - V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
+                                    if (dot(diff, diff) > r2) continue;
+                                    uint4 B = __ldg(P.photons + (size_t)q * 2 + 1);
+                                    float2 bxy = unpackHalf2(B.x), bz = unpackHalf2(B.y);
+                                    float lightDvm = __uint_as_float(B.z), lightDvcm = __uint_as_float(B.w);
+                                    V3 photonPrevToPhotonL = fr.toLocal(-unpackOct(A.w));
+                                    float eyeRev = bsdfPdf(o.sh, photonPrevToPhotonL, toPrevL, 1.0f);
+                                    float lightRev = bsdfPdf(o.sh, -toPrevL, -photonPrevToPhotonL, 1.0f);
+                                    float wEye = o.d_vcm / eta + eyeRev * o.d_vm;
+                                    float wLight = lightDvcm / eta + lightRev * lightDvm;
+                                    float w = 1.0f / (1.0f + wEye + wLight);
+                                    V3 f = bsdfEval(o.sh, photonPrevToPhotonL, toPrevL, 1.0f);
+                                    V3 unweighted = V3(bxy.x, bxy.y, bz.x) * f * o.currBeta * norm;
+                                    sum += applyWeight(P, unweighted, w);
+                                    ++nMerged;
+                                }
+                            }
+                          }
+                          if (P.doSPPM) endPath = true;              // SPPM gathers density once (:3046)
+                        }
+                    }
+                    if (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) atomicAdd(&P.colors[pix], make_float4(sum.x, sum.y, sum.z, 0.f));
+                    bool through = dot(o.wiW, s.n) < 0.0f;                                       // :3053, :936
+                    p.o = through ? s.p - s.n * kRayEps : s.p + s.n * kRayEps;
+                    p.d = vcm ? o.wiW : normalize(o.wiW);                                        // :3056 vs :944
+                    p.prevDelta = o.delta; p.prevP = s.p;
+                    cont = !endPath && step + 1 < numSteps;
+                    if (cont) storeBdPath(st, l, p);
+                }
+            }
+        }
+        int pos = bdWarpAppend(&nextCnt[BC_QUEUE], cont);
+        if (cont) nextQueue[pos] = l;
+    }
+    for (int o = 16; o > 0; o >>= 1) nMerged += __shfl_xor_sync(0xffffffffu, nMerged, o);
+    if (lane == 0 && nMerged) atomicAdd(&st.stats[4], nMerged);
+}
+
+// ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------
+__global__ void bdSlabCounts(const uint4* __restrict__ slabs, size_t slabWords, int world, int cap, int* __restrict__ counts) {
+    int r = threadIdx.x;
+    if (r < world) counts[r] = min(*reinterpret_cast<const int*>(slabs + (size_t)r * slabWords), cap);
+}
+__global__ void bdCompactSlabs(const uint4* __restrict__ slabs, size_t slabWords, int world, const int* __restrict__ counts,
+                               uint4* __restrict__ out) {
+    // blockIdx.y = slab; records copied word by word (two 16 B words per photon)
+    int r = blockIdx.y;
+    int n = counts[r];
+    int off = 0;
+    for (int k = 0; k < r; ++k) off += counts[k];
+    const uint4* src = slabs + (size_t)r * slabWords + kSlabHeaderBytes / 16;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)n * 2; i += (size_t)gridDim.x * blockDim.x)
+        out[(size_t)off * 2 + i] = src[i];
+}
+__global__ void bdReorderPhotons(const uint4* __restrict__ in, const uint32_t* __restrict__ index, int n, uint4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    size_t s = (size_t)index[i] * 2;
+    uint4 a = __ldg(in + s), b = __ldg(in + s + 1);
+    out[(size_t)i * 2] = a; out[(size_t)i * 2 + 1] = b;
+}
+
+}  // namespace nv
+
+#include "vcm_host.inl"

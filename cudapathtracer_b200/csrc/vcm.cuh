@@ -1,0 +1,84 @@
+// vcm.cuh — data layout of the bidirectional engine (VCM, SPPM and BDPT share it).
+//
+// Replaces the reference's per-pixel megakernels doLightPass / doEyePass (deviceCode.cu:2240-2384, 2686-3065) and
+// lightPathTracing / Li_bidirectional (:1290-1432, :1768-1815) with a depth-synchronous wavefront:
+//   light pass : start -> [extend -> light step -> splat resolve] x lightDepth
+//   exchange   : photon slabs of all ranks are all-gathered by the caller (one slab per rank, fixed capacity)
+//   grid build : hash -> radix sort -> cell table -> gather of the 32 B photon records into cell order
+//   eye pass   : start -> [extend -> eye step (implicit hit, NEE, connections, merging) -> connection resolve] x eyeDepth
+// Every shadow ray (t=1 splats, NEE, vertex connections) is deferred into a queue and traced by an any-hit kernel.
+//
+// Light-vertex cache (what the reference keeps in VCMPathVertices, objects.cuh:958-991, 42 B/vertex in 12 arrays):
+// three 16 B words per vertex, indexed [depth * nLocal + localPath], same quantisation as the reference —
+// octahedral 2 x snorm16 normal / wo (util.cuh:342-391), fp16 beta, fp16 uv, packed info word:
+//   A = { pos.x, pos.y, pos.z, oct(normal) }
+//   B = { oct(wo), half2(beta.x, beta.y), half2(beta.z, 0), half2(uv) }
+//   C = { info (bit0 delta, bit1 backface, bits 22..31 material), d_vc, d_vcm, 0 }
+// Photon record (reference Photons, objects.cuh:1162-1179, 34 B in 10 arrays; its packedNormal is never read): 32 B
+//   A = { pos.x, pos.y, pos.z, oct(wi) }     B = { half2(beta.x, beta.y), half2(beta.z, 0), d_vm, d_vcm }
+// Photon slab of rank r: [32 B header: int count, int capacity, ...][capacity x 32 B records]; slabs of all ranks are
+// contiguous, so one all-gather on the whole buffer exchanges an iteration's photons.
+#pragma once
+#include <cuda_fp16.h>
+#include "scene_dev.cuh"
+#include "camera.cuh"
+#include "hashgrid.cuh"
+
+namespace nv {
+
+enum : int { BD_MODE_VCM = 0, BD_MODE_BDPT = 1 };
+constexpr int kMaxBdDepth = 32;          // eye / light depth limit of the wavefront counters
+constexpr int kSlabHeaderBytes = 32;
+
+// per (pass, depth) counters; one memset per pass clears them all
+enum : int { BC_QUEUE = 0, BC_SHADOW = 1, BC_FETCH_EXTEND = 2, BC_FETCH_STEP = 3, BC_FETCH_RESOLVE = 4, BC_STRIDE = 8 };
+
+struct __align__(16) BdShadowRec { float4 o_maxT; float4 d_pix; float4 contrib_skip; };   // 48 B
+
+struct BdState {
+    // per local path (shared by the light pass and the eye pass, which run one after the other)
+    float4* rayO;      // xyz origin,    w = pdf (solid angle) of the last sampled direction
+    float4* rayD;      // xyz direction, w = |cos| at the previous vertex
+    float4* beta;      // xyz throughput, w = reverse pdf (solid angle) at the previous vertex
+    float4* prevP;     // xyz previous vertex, w = bits: 1 = previous vertex was delta
+    float4* dv;        // d_vcm, d_vc, d_vm of the previous vertex, w = spatial pdf of the light sample (light pass)
+    unsigned long long* rng;
+    float4* hit;       // bits tri, t, u, v
+    int* queue[2];
+    int* pathLen;      // surface vertices stored per light path
+    uint4 *lvA, *lvB, *lvC;
+    BdShadowRec* shadowQ;
+    int* counters;     // (kMaxBdDepth + 1) * BC_STRIDE
+    unsigned long long* stats;   // [0] closest rays [1] shadow rays [2] photons stored [3] light vertices stored [4] merges accepted
+    int nLocal;
+    int shadowCap;
+};
+
+struct BdParams {
+    NovumCamera cam;
+    int w, h;
+    int eyeDepth, lightDepth;
+    int mode;                          // BD_MODE_*
+    int lightTrace, nee, naive, connection, doMis, paintWeight, doMerge, doSPPM, sampleEnv;
+    float mergeRadius, etaVcm;
+    unsigned long long seed;
+    int iter;
+    int rank, world;                   // pixel rows y with y % world == rank belong to this rank
+    int nLocal;
+    float4* colors;                    // full-frame sum accumulator of this rank
+    // photons
+    uint4* slab;                       // this rank's slab (header + records), append target of the light pass
+    int slabCap;
+    const uint4* photons;              // records in cell order (eye pass)
+    const uint32_t* cellStart; const uint32_t* cellEnd;
+    GridParams grid;
+};
+
+NV_D int localToPixel(const BdParams& P, int l, int& x, int& y) {
+    int row = l / P.w;
+    x = l - row * P.w;
+    y = P.rank + row * P.world;
+    return y * P.w + x;
+}
+
+}  // namespace nv

@@ -1,0 +1,336 @@
+// vcm_host.inl — host side of the bidirectional engine: buffers, the per-iteration pass sequence, the multi-GPU phase API
+// (light pass -> caller all-gathers the photon slabs -> grid build -> eye pass) and the single-call render entry.
+// launch_VCM's host loop (deviceCode.cu:3256-3497) is the reference for what one iteration does: radius schedule,
+// photon counter reset, light pass, hash grid, eye pass.
+
+namespace nv {
+
+struct BdEngine {
+    BdState st{};
+    NovumScene* scene = nullptr;
+    NovumCamera cam{};
+    int w = 0, h = 0, eyeDepth = 0, lightDepth = 0, mode = BD_MODE_VCM;
+    int rank = 0, world = 1, nLocal = 0;
+    unsigned long long seed = 0;
+    NovumRenderConfig cfg{};
+    // photons: `world` slabs (this rank appends into slab `rank`), compacted copy, cell-ordered copy
+    uint4* slabs = nullptr; size_t slabWords = 0; int slabCap = 0;
+    uint4* photonsAll = nullptr; uint4* photonsSorted = nullptr;
+    int maxPhotons = 0, photonCount = 0;
+    HashGridDevice grid;
+    bool gridAllocated = false;
+    int* d_counts = nullptr; int* h_counts = nullptr;
+    float mergeRadius = 0.f;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    unsigned long long launches = 0, iterations = 0;
+    float deviceMs = 0.f;
+    float stageMs[4] = {0, 0, 0, 0};      // light pass, grid build, eye pass, (unused)
+    size_t bytes = 0;
+};
+
+static void bdFree(BdEngine& e) {
+    BdState& s = e.st;
+    cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.dv); cudaFree(s.rng); cudaFree(s.hit);
+    cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
+    cudaFree(s.shadowQ); cudaFree(s.counters); cudaFree(s.stats);
+    cudaFree(e.slabs); cudaFree(e.photonsAll); cudaFree(e.photonsSorted); cudaFree(e.d_counts);
+    if (e.h_counts) cudaFreeHost(e.h_counts);
+    if (e.gridAllocated) hashGridFree(e.grid);
+    if (e.ev0) { cudaEventDestroy(e.ev0); cudaEventDestroy(e.ev1); }
+    e = BdEngine();
+}
+
+static int bdModeOf(int integrator) { return integrator == NOVUM_BIDIRECTIONAL ? BD_MODE_BDPT : BD_MODE_VCM; }
+
+static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg, const NovumCamera& cam, NovumShard shard,
+                   unsigned long long seed) {
+    e.scene = scene; e.cam = cam; e.cfg = cfg; e.seed = seed;
+    e.w = cfg.width; e.h = cfg.height; e.eyeDepth = cfg.bdptEyeDepth; e.lightDepth = cfg.bdptLightDepth;
+    e.mode = bdModeOf(cfg.integrator);
+    e.rank = shard.rank; e.world = shard.world;
+    if (e.eyeDepth < 1 || e.lightDepth < 1 || e.eyeDepth > kMaxBdDepth || e.lightDepth > kMaxBdDepth) return NOVUM_E_ARG;
+    if ((long long)e.w * e.h >= (1ll << 30)) return NOVUM_E_ARG;
+    int rows = 0;
+    for (int y = e.rank; y < e.h; y += e.world) ++rows;
+    e.nLocal = rows * e.w;
+    BdState& s = e.st;
+    s.nLocal = e.nLocal;
+    size_t n = (size_t)(e.nLocal > 0 ? e.nLocal : 1);
+    cudaError_t err = cudaSuccess;
+    auto A = [&](void** p, size_t b) { if (err == cudaSuccess) { err = cudaMalloc(p, b ? b : 16); e.bytes += b; } };
+    A((void**)&s.rayO, n * 16); A((void**)&s.rayD, n * 16); A((void**)&s.beta, n * 16); A((void**)&s.prevP, n * 16); A((void**)&s.dv, n * 16);
+    A((void**)&s.rng, n * 8); A((void**)&s.hit, n * 16);
+    A((void**)&s.queue[0], n * 4); A((void**)&s.queue[1], n * 4); A((void**)&s.pathLen, n * 4);
+    size_t nv = n * (size_t)e.lightDepth;
+    A((void**)&s.lvA, nv * 16); A((void**)&s.lvB, nv * 16); A((void**)&s.lvC, nv * 16);
+    size_t cap = n * (size_t)(e.lightDepth + 1);
+    if (cap < 2 * n) cap = 2 * n;
+    if (cap > 0x7fffffffull) cap = 0x7fffffffull;
+    s.shadowCap = (int)cap;
+    A((void**)&s.shadowQ, cap * sizeof(BdShadowRec));
+    A((void**)&s.counters, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int));
+    A((void**)&s.stats, 8 * sizeof(unsigned long long));
+    // photon storage: one slab per rank, sized for that rank's worst case (every vertex of every light path)
+    int rowsMax = (e.h + e.world - 1) / e.world;
+    e.slabCap = rowsMax * e.w * e.lightDepth;
+    e.slabWords = (size_t)kSlabHeaderBytes / 16 + (size_t)e.slabCap * 2;
+    e.maxPhotons = e.w * e.h * e.lightDepth;                 // deviceCode.cu:3276
+    A((void**)&e.slabs, e.slabWords * 16 * e.world);
+    if (e.mode == BD_MODE_VCM) {
+        if (e.world > 1) A((void**)&e.photonsAll, (size_t)e.maxPhotons * 32);
+        A((void**)&e.photonsSorted, (size_t)e.maxPhotons * 32);
+    }
+    A((void**)&e.d_counts, 16 * sizeof(int));
+    if (err != cudaSuccess) return (int)err;
+    if ((err = cudaHostAlloc((void**)&e.h_counts, 16 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    if (e.mode == BD_MODE_VCM) {
+        int rc = hashGridAlloc(e.grid, e.maxPhotons);
+        if (rc) return rc;
+        e.gridAllocated = true;
+    }
+    cudaMemsetAsync(s.stats, 0, 8 * sizeof(unsigned long long), scene->stream);
+    cudaMemsetAsync(e.slabs, 0, e.slabWords * 16 * e.world, scene->stream);
+    cudaEventCreate(&e.ev0); cudaEventCreate(&e.ev1);
+    return 0;
+}
+
+static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
+    BdParams P;
+    memset(&P, 0, sizeof(P));
+    const NovumRenderConfig& c = e.cfg;
+    P.cam = e.cam; P.w = e.w; P.h = e.h; P.eyeDepth = e.eyeDepth; P.lightDepth = e.lightDepth; P.mode = e.mode;
+    P.lightTrace = c.bdptLightTrace; P.nee = c.bdptNee; P.naive = c.bdptNaive; P.connection = c.bdptConnection;
+    P.doMis = c.bdptDoMis; P.paintWeight = c.bdptPaintWeight; P.doMerge = c.vcmDoMerge; P.doSPPM = c.doSPPM; P.sampleEnv = c.sampleEnvironment;
+    if (c.integrator == NOVUM_SPPM) {           // main.cu:314-333
+        P.connection = 0; P.naive = 0; P.nee = 0; P.lightTrace = 0; P.doMis = 0; P.doMerge = 1; P.doSPPM = 1;
+    }
+    if (e.mode == BD_MODE_BDPT) { P.doMerge = 0; P.doSPPM = 0; }
+    float r = e.mode == BD_MODE_VCM ? mergeRadiusAt(e.scene->sceneRadius * c.vcmInitialMergeRadiusMultiplier, c.vcmMergeConst, iter) : 0.0f;
+    P.mergeRadius = r;
+    P.etaVcm = e.mode == BD_MODE_VCM ? (float)(e.w * e.h) * kPi * r * r : 0.0f;      // deviceCode.cu:1962
+    P.seed = e.seed; P.iter = iter; P.rank = e.rank; P.world = e.world; P.nLocal = e.nLocal;
+    P.colors = colors;
+    P.slab = e.slabs + (size_t)e.rank * e.slabWords; P.slabCap = e.slabCap;
+    P.photons = e.photonsSorted; P.cellStart = e.grid.cellStart; P.cellEnd = e.grid.cellEnd; P.grid = e.grid.params;
+    return P;
+}
+
+}  // namespace nv
+
+namespace nv {
+
+static inline int bdGrid() { return smCount() * 8; }
+
+// light pass of iteration `iter` for this rank's rows: fills the light-vertex cache, appends photons to this rank's slab,
+// splats the t = 1 connections into `colors`
+static int bdLightPass(BdEngine& e, int iter, float4* colors) {
+    cudaStream_t s = e.scene->stream;
+    BdState& st = e.st;
+    BdParams P = bdParams(e, iter, colors);
+    SceneView sc = e.scene->view();
+    e.mergeRadius = P.mergeRadius;
+    cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
+    cudaMemsetAsync(P.slab, 0, kSlabHeaderBytes, s);                      // photon counter of this rank (deviceCode.cu:3330)
+    if (e.nLocal == 0 || sc.numLights == 0) return 0;
+    const int numSteps = e.mode == BD_MODE_BDPT ? e.lightDepth - 1 : e.lightDepth;      // :1116 (depth 1..max-1) vs :2029 (0..max-1)
+    bdLightStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(sc, st, P);
+    ++e.launches;
+    const int grid = bdGrid();
+    for (int step = 0; step < numSteps; ++step) {
+        int* cnt = st.counters + step * BC_STRIDE;
+        bdExtend<<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt);
+        bdLightStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
+        if (P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; }
+        e.launches += 2;
+    }
+    if (numSteps == 0 && P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, st.counters); ++e.launches; }
+    return (int)cudaGetLastError();
+}
+
+// after the slabs of all ranks are in place: count, compact, hash, sort, cell table, reorder into cell order
+static int bdBuildGrid(BdEngine& e, int iter) {
+    if (e.mode != BD_MODE_VCM) return 0;
+    cudaStream_t s = e.scene->stream;
+    BdParams P = bdParams(e, iter, nullptr);
+    if (!P.doMerge || P.mergeRadius <= 0.0f) { e.photonCount = 0; return 0; }
+    bdSlabCounts<<<1, 32, 0, s>>>(e.slabs, e.slabWords, e.world, e.slabCap, e.d_counts);
+    ++e.launches;
+    cudaMemcpyAsync(e.h_counts, e.d_counts, 16 * sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaError_t err = cudaStreamSynchronize(s);           // the reference blocks on the same counter (deviceCode.cu:3352)
+    if (err != cudaSuccess) return (int)err;
+    long long total = 0;
+    for (int r = 0; r < e.world; ++r) total += e.h_counts[r];
+    if (total > e.maxPhotons) total = e.maxPhotons;
+    e.photonCount = (int)total;
+    const uint4* src = e.slabs + kSlabHeaderBytes / 16;
+    if (e.world > 1) {
+        dim3 g(256, e.world);
+        bdCompactSlabs<<<g, 256, 0, s>>>(e.slabs, e.slabWords, e.world, e.d_counts, e.photonsAll);
+        ++e.launches;
+        src = e.photonsAll;
+    }
+    int rc = hashGridBuildAoS(e.grid, reinterpret_cast<const float*>(src), 8, e.photonCount, e.scene->sceneMin, P.mergeRadius, s);
+    if (rc) return rc;
+    e.launches += e.grid.launches;
+    if (e.photonCount > 0) {
+        bdReorderPhotons<<<(e.photonCount + 255) / 256, 256, 0, s>>>(src, e.grid.index, e.photonCount, e.photonsSorted);
+        ++e.launches;
+    }
+    return (int)cudaGetLastError();
+}
+
+static int bdEyePass(BdEngine& e, int iter, float4* colors) {
+    cudaStream_t s = e.scene->stream;
+    BdState& st = e.st;
+    BdParams P = bdParams(e, iter, colors);
+    SceneView sc = e.scene->view();
+    if (e.nLocal == 0) return 0;
+    cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
+    const int numSteps = e.mode == BD_MODE_BDPT ? e.eyeDepth - 1 : e.eyeDepth;          // :794 vs :2723
+    bdEyeStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(st, P);
+    ++e.launches;
+    const int grid = bdGrid();
+    const bool shadows = P.nee || P.connection;
+    for (int step = 0; step < numSteps; ++step) {
+        int* cnt = st.counters + step * BC_STRIDE;
+        bdExtend<<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt);
+        bdEyeStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
+        if (shadows) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; }
+        e.launches += 2;
+    }
+    ++e.iterations;
+    return (int)cudaGetLastError();
+}
+
+static void bdFillStats(BdEngine& e, NovumRenderStats* stats) {
+    if (!stats) return;
+    unsigned long long h[8] = {0};
+    cudaMemcpy(h, e.st.stats, sizeof(h), cudaMemcpyDeviceToHost);
+    memset(stats, 0, sizeof(*stats));
+    stats->closestRays = h[0]; stats->shadowRays = h[1]; stats->photons = h[2]; stats->lightVertices = h[3];
+    stats->triTests = h[4];                           // merges accepted (photons within the radius), reported in the spare counter
+    stats->paths = 2ull * (unsigned long long)e.nLocal * e.iterations;      // one light + one eye path per pixel per iteration
+    stats->kernelLaunches = e.launches;
+    stats->deviceMs = e.deviceMs;
+    for (int k = 0; k < 4; ++k) stats->stageMs[k] = e.stageMs[k];
+}
+
+static void bdResetStats(BdEngine& e) {
+    cudaMemsetAsync(e.st.stats, 0, 8 * sizeof(unsigned long long), e.scene->stream);
+    e.launches = 0; e.iterations = 0; e.deviceMs = 0.f;
+    for (int k = 0; k < 4; ++k) e.stageMs[k] = 0.f;
+}
+
+static void bdEngineFree(void* p) { BdEngine* e = (BdEngine*)p; bdFree(*e); delete e; }
+
+static bool bdMatches(const BdEngine& e, const NovumRenderConfig& cfg, NovumShard shard) {
+    return e.w == cfg.width && e.h == cfg.height && e.eyeDepth == cfg.bdptEyeDepth && e.lightDepth == cfg.bdptLightDepth &&
+           e.mode == bdModeOf(cfg.integrator) && e.rank == shard.rank && e.world == shard.world;
+}
+
+// Single-call form (novum_render_device): whole iterations are striped over the ranks of `shard` — iteration i runs all
+// light and eye paths on rank i % world, so no exchange is needed and the caller only sums the framebuffers at the end.
+int vcmRenderDevice(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                    NovumShard shard, unsigned long long seed, float4* d_colors, NovumRenderStats* stats) {
+    NovumShard whole = {0, 1};
+    BdEngine* e = (BdEngine*)s->vcmEngine;
+    if (e && !bdMatches(*e, *cfg, whole)) { bdEngineFree(e); s->vcmEngine = nullptr; e = nullptr; }
+    if (!e) {
+        e = new BdEngine();
+        int rc = bdAlloc(*e, s, *cfg, *cam, whole, seed);
+        if (rc) { bdFree(*e); delete e; return rc; }
+        s->vcmEngine = e; s->vcmEngineFree = bdEngineFree;
+    }
+    e->cam = *cam; e->cfg = *cfg; e->seed = seed;
+    bdResetStats(*e);
+    const bool prof = (s->profileFlags & 1) != 0;
+    std::vector<cudaEvent_t> evs;
+    cudaEventRecord(e->ev0, s->stream);
+    for (int k = shard.rank; k < numSample; k += shard.world) {
+        int iter = firstSample + k;
+        auto mark = [&]() { if (prof) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, s->stream); evs.push_back(ev); } };
+        mark();
+        int rc = bdLightPass(*e, iter, d_colors);
+        mark();
+        if (!rc) rc = bdBuildGrid(*e, iter);
+        mark();
+        if (!rc) rc = bdEyePass(*e, iter, d_colors);
+        mark();
+        if (rc) return rc;
+    }
+    cudaEventRecord(e->ev1, s->stream);
+    cudaError_t err = cudaStreamSynchronize(s->stream);
+    if (err != cudaSuccess) return (int)err;
+    if ((err = cudaGetLastError()) != cudaSuccess) return (int)err;
+    cudaEventElapsedTime(&e->deviceMs, e->ev0, e->ev1);
+    for (size_t i = 0; i + 3 < evs.size(); i += 4)
+        for (int k = 0; k < 3; ++k) { float ms = 0; cudaEventElapsedTime(&ms, evs[i + k], evs[i + k + 1]); e->stageMs[k] += ms; }
+    for (cudaEvent_t ev : evs) cudaEventDestroy(ev);
+    bdFillStats(*e, stats);
+    return 0;
+}
+
+}  // namespace nv
+
+// ---- C ABI: multi-GPU phase API (tile-sharded: rank r owns pixel rows y % world == r for BOTH walks) -----------------------
+struct NovumVcmState { nv::BdEngine e; };
+
+extern "C" {
+
+int novum_vcm_create(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, NovumShard shard, uint64_t seed,
+                     NovumVcmState** out) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (!cfg || !cam || !out || shard.world < 1 || shard.world > 16 || shard.rank < 0 || shard.rank >= shard.world) return NOVUM_E_ARG;
+    if (cfg->integrator != NOVUM_VCM && cfg->integrator != NOVUM_SPPM && cfg->integrator != NOVUM_BIDIRECTIONAL) return NOVUM_E_ARG;
+    NovumVcmState* v = new NovumVcmState();
+    int rc = nv::bdAlloc(v->e, s, *cfg, *cam, shard, seed);
+    if (rc) { nv::bdFree(v->e); delete v; return rc; }
+    *out = v;
+    return 0;
+}
+
+void novum_vcm_destroy(NovumVcmState* v) {
+    if (!v) return;
+    nv::bdFree(v->e);
+    delete v;
+}
+
+int novum_vcm_light_pass(NovumVcmState* v, int iter, NovumFloat4* d_splat) {
+    if (!v || !d_splat) return NOVUM_E_ARG;
+    return nv::bdLightPass(v->e, iter, (float4*)d_splat);
+}
+
+int novum_vcm_cache_buffer(NovumVcmState* v, void** d_cacheBase, uint64_t* slabBytes, uint64_t* totalBytes) {
+    if (!v) return NOVUM_E_ARG;
+    if (d_cacheBase) *d_cacheBase = v->e.slabs;
+    if (slabBytes) *slabBytes = v->e.slabWords * 16;
+    if (totalBytes) *totalBytes = v->e.slabWords * 16 * v->e.world;
+    return 0;
+}
+
+int novum_vcm_build_grid(NovumVcmState* v, int iter) {
+    if (!v) return NOVUM_E_ARG;
+    return nv::bdBuildGrid(v->e, iter);
+}
+
+int novum_vcm_eye_pass(NovumVcmState* v, int iter, NovumFloat4* d_colors) {
+    if (!v || !d_colors) return NOVUM_E_ARG;
+    return nv::bdEyePass(v->e, iter, (float4*)d_colors);
+}
+
+int novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats) {
+    if (!v || !stats) return NOVUM_E_ARG;
+    cudaError_t err = cudaStreamSynchronize(v->e.scene->stream);
+    if (err != cudaSuccess) return (int)err;
+    nv::bdFillStats(v->e, stats);
+    stats->photons = (uint64_t)v->e.photonCount;      // photons in the last grid (all ranks)
+    return 0;
+}
+
+int novum_vcm_stream(NovumVcmState* v, void** stream) {
+    if (!v || !stream) return NOVUM_E_ARG;
+    *stream = (void*)v->e.scene->stream;
+    return 0;
+}
+
+}  // extern "C"

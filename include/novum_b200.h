@@ -267,7 +267,13 @@ int  novum_hashgrid_query_count(NovumHashGrid* g, const float* qx, const float* 
 int  novum_hashgrid_last_ms(NovumHashGrid* g, float* ms);
 
 /* ---- multi-GPU phase API (one process per GPU; the exchange itself is done by the caller with
- *      NCCL / torch.distributed on the device pointers returned here) -------------------------- */
+ *      NCCL / torch.distributed on the device pointers returned here) --------------------------
+ * Tile sharding: rank r owns pixel rows y % world == r for the light walk AND the eye walk of an iteration, so vertex
+ * connections (paired by pixel in the reference, deviceCode.cu:2866-2942) stay local; what every rank needs from every
+ * other rank is the photons (merging looks at all of them, :2968-3048). They live in `world` fixed-capacity slabs
+ * ([32 B header: int count][32 B records]) laid out back to back: one in-place all-gather per iteration exchanges them.
+ * The t=1 splats land on arbitrary pixels: every rank accumulates into its own full-frame buffer and the frames are summed
+ * once at the end. (novum_render_device instead stripes whole iterations over ranks and needs no exchange at all.) */
 typedef struct NovumVcmState NovumVcmState;
 int  novum_vcm_create(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, NovumShard shard,
                       uint64_t seed, NovumVcmState** out);
@@ -282,6 +288,8 @@ int  novum_vcm_cache_buffer(NovumVcmState* v, void** d_cacheBase, uint64_t* slab
 int  novum_vcm_build_grid(NovumVcmState* v, int iter);
 int  novum_vcm_eye_pass(NovumVcmState* v, int iter, NovumFloat4* d_colors);
 int  novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats);
+/* the CUDA stream (cudaStream_t) the passes are enqueued on, so the caller can order its collective after the light pass */
+int  novum_vcm_stream(NovumVcmState* v, void** stream);
 int  novum_sync(void);
 
 /* ---- synthetic scene generator (stand-ins for the reference's LFS-pointer OBJ files) ----- */
