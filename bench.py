@@ -1,13 +1,21 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the B200-native Novum core.
 
-A "step" is one pass of the hot path over one batch of work: `--spp-per-step` sample passes of the full frame per GPU
-(weak scaling: N GPUs render N x as many sample passes per step, sharded by sample index, framebuffers summed at the end).
-Workloads (BASELINE.json configs): dragon_nee = configs[1] (glass dragon stand-in, ~871k tris, 1920x1080, NEE+MIS),
-cornell = configs[0]. metric = Mrays/s (closest-hit + shadow rays actually traced, device counters).
+A "step" is one pass of the hot path over one batch of work: `--spp-per-step` sample passes (unidirectional) or whole
+VCM / BDPT / SPPM iterations of the full frame per GPU. Weak scaling: N GPUs render N x as many passes per step, striped by
+pass index (`--sharding striped`, default) or — bidirectional integrators only — by pixel rows with a per-iteration NCCL
+all-gather of the photon slabs (`--sharding tiles`); the full-frame accumulators are summed with one NCCL reduce.
+
+Workloads = BASELINE.json configs on the generated stand-in scenes (the reference's OBJ files are LFS pointers):
+  dragon_nee   configs[1]  glass dragon stand-in (~871k tris) 1920x1080, NEE+MIS          (north_star's >=5x target)
+  rainbow_vcm  configs[4]  rainbow dragon, VCM, 3840x2160                                 (the metric's headline config)
+  water_bdpt   configs[2]  water caustic, BDPT, 1920x1080
+  water_sppm   configs[3]  water caustic, SPPM, 1024x1024 light paths (~1M photons / iteration)
+  cornell      configs[0]  Cornell box 512x512 NEE+MIS
+metric = Mrays/s: closest-hit + shadow rays actually traced (device counters); paths/s is reported beside it.
 
   python bench.py --gpus N --steps K --warmup W            our arm (torchrun for N > 1)
-  python bench.py --impl reference ...                      the reference's own CUDA build (oracle/_ref/novum_ref)
+  python bench.py --impl reference ...                      the reference's own CUDA build (oracle/_ref/novum_ref), 1 GPU
 """
 import argparse
 import json
@@ -23,10 +31,13 @@ REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
 sys.path.insert(0, os.path.join(REPO, "tests"))
 
+UNI, BDPT, NAIVE, VCM, SPPM = 0, 1, 2, 3, 4
 WORKLOADS = {
-    # name: (scene generator, integrator override, width, height, what BASELINE.json calls it)
-    "dragon_nee": ("dragon", None, 1920, 1080, "configs[1]: dragon stand-in (~871k tris, glass) 1920x1080 NEE+MIS"),
-    "cornell": ("cornell", None, 512, 512, "configs[0]: Cornell box 512x512 NEE+MIS"),
+    "dragon_nee": dict(gen="dragon", integ=UNI, w=1920, h=1080, spp=32, desc="configs[1]: dragon stand-in (~871k tris, glass) 1920x1080 NEE+MIS"),
+    "rainbow_vcm": dict(gen="rainbow", integ=VCM, w=3840, h=2160, spp=1, desc="configs[4]: rainbow dragon stand-in (~871k tris) 3840x2160 VCM, eye 16 / light 10"),
+    "water_bdpt": dict(gen="water", integ=BDPT, w=1920, h=1080, spp=2, desc="configs[2]: water caustic stand-in 1920x1080 BDPT, all strategies + MIS"),
+    "water_sppm": dict(gen="water_sppm", integ=SPPM, w=1024, h=1024, spp=4, desc="configs[3]: water caustic stand-in SPPM, 1024x1024 light paths per iteration"),
+    "cornell": dict(gen="cornell", integ=UNI, w=512, h=512, spp=64, desc="configs[0]: Cornell box 512x512 NEE+MIS"),
 }
 
 
@@ -73,7 +84,7 @@ class ClockSampler:
 
 def scene_dir_for(workload, detail, rank, dist):
     """Rank 0 generates the stand-in scene once per box; other ranks wait for it."""
-    gen = WORKLOADS[workload][0]
+    gen = WORKLOADS[workload]["gen"]
     d = os.path.join(tempfile.gettempdir(), f"novum_bench_{gen}_{detail}")
     import cudapathtracer_b200 as nb
     marker = os.path.join(d, ".done")
@@ -85,10 +96,43 @@ def scene_dir_for(workload, detail, rank, dist):
     return d
 
 
+def cpu_oracle_baseline(sdir, workload, target_s=12.0):
+    """The CPU restatement of the reference's path (oracle/, kind "port") on the host cores, on a bounded sample: the same
+    scene and camera at reduced resolution through the oracle's NEE+MIS walk (closest-hit + shadow rays of the reference's
+    BVHSceneIntersect / BVHShadowRay restatement), sized for ~10-20 s. For the bidirectional workloads the ray mix differs
+    (no CPU VCM exists); the figure is the host's Mrays/s on this scene's geometry."""
+    import cudapathtracer_b200 as nb
+    from oracle.oracle_binding import OracleScene
+    scene = nb.Scene.from_config(os.path.join(sdir, "configs", "config.rendertron"))
+    pos, nrm, uv, tris, lights = scene.download()
+    cfg = scene.cfg
+    scene.close()
+    ora = OracleScene(pos, nrm, uv, tris, nb.material_table(), None, 2)
+    wl = WORKLOADS[workload]
+    sw, sh, spp = max(16, wl["w"] // 16), max(9, wl["h"] // 16), 1
+    cfg.width, cfg.height = sw, sh
+    if cfg.maxDepth <= 0:
+        cfg.maxDepth = 40
+    cam = nb.camera_make(cfg)
+    t0 = time.time()
+    img, counts = ora.render_unidirectional(bytes(cam), sw, sh, cfg.maxDepth, 0, spp)
+    dt = time.time() - t0
+    if dt < target_s / 4:          # grow the sample towards the target duration
+        spp = int(min(256, max(1, target_s / max(dt, 1e-3))))
+        t0 = time.time()
+        img, counts = ora.render_unidirectional(bytes(cam), sw, sh, cfg.maxDepth, 1, spp)
+        dt = time.time() - t0
+    rays = float(counts[0] + counts[1])
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{sw}x{sh} px x {spp} spp of the same scene/camera through the oracle's NEE+MIS walk, OpenMP on all host cores ({dt:.1f} s)",
+            "paths_per_s": sw * sh * spp / dt, "rays_per_path": rays / (sw * sh * spp)}
+
+
 def run_ours(args):
     import numpy as np
     import torch
     import cudapathtracer_b200 as nb
+    from cudapathtracer_b200 import distributed as nd
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -103,24 +147,38 @@ def run_ours(args):
     nb.lib().novum_set_device(local)
     dev = torch.device("cuda", local)
 
+    wl = WORKLOADS[args.workload]
     sdir = scene_dir_for(args.workload, args.detail, rank, dist)
     t0 = time.time()
     scene = nb.Scene.from_config(os.path.join(sdir, "configs", "config.rendertron"))
     load_s = time.time() - t0
     cfg = scene.cfg
-    _, integ, w, h, wl_name = WORKLOADS[args.workload]
-    cfg.width, cfg.height = w, h
+    w, h, integ = wl["w"], wl["h"], wl["integ"]
+    cfg.width, cfg.height, cfg.integrator = w, h, integ
+    bidir = integ in (BDPT, VCM, SPPM)
+    tiles = bidir and args.sharding == "tiles"
     cam = nb.camera_make(cfg)
     info = scene.info()
-    S = args.spp_per_step
+    S = args.spp_per_step or wl["spp"]
     colors = torch.zeros((h, w, 4), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > L2 (126 MB)
+    tiler = nd.TileRenderer(scene, cfg, cam, dist) if tiles else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def step(i, profile=0):
+        """One step: S passes per GPU. Returns (stats, device ms)."""
         scene.set_profile(profile)
-        flush.fill_(i & 0xff)          # evict L2 between steps (the path pool alone, ~0.3 GB, also exceeds L2)
+        flush.fill_(i & 0xff)          # evict L2 between steps (the working set of a step, >0.4 GB, also exceeds L2)
         torch.cuda.synchronize()
-        return scene.render_device(cfg, cam, i * S * world, S * world, colors.data_ptr(), rank=rank, world=world)
+        if tiles:                      # all ranks work on the same S*world iterations, each on its pixel rows
+            ext = tiler.ext_stream
+            ev0.record(ext)
+            st = tiler.render(i * S * world, S * world, colors)
+            ev1.record(ext)
+            torch.cuda.synchronize()
+            return st, ev0.elapsed_time(ev1)
+        st = scene.render_device(cfg, cam, i * S * world, S * world, colors.data_ptr(), rank=rank, world=world)
+        return st, st.deviceMs          # CUDA events on the library's own stream around the whole call
 
     for i in range(args.warmup):
         step(i)
@@ -131,13 +189,21 @@ def run_ours(args):
     if rank == 0:
         clocks.start()
     wall0 = time.time()
-    dev_ms, rays, paths, launches, stage_ms, closest = 0.0, 0, 0, 0, [0.0] * 4, 0
+    dev_ms, rays, paths, launches, stage_ms, closest, photons = 0.0, 0, 0, 0, [0.0] * 4, 0, 0
+    merge_cand, merge_acc = 0, 0
+    before = tiler.session.stats() if tiles else None       # the session's counters are cumulative
     for i in range(args.steps):
-        st = step(args.warmup + i, profile=1)
-        dev_ms += st.deviceMs; rays += st.closestRays + st.shadowRays; paths += st.paths; launches += st.kernelLaunches
-        closest += st.closestRays
-        for k in range(4):
-            stage_ms[k] += st.stageMs[k]
+        st, ms = step(args.warmup + i, profile=0 if tiles else 1)
+        dev_ms += ms
+        photons = st.photons
+        if not tiles:
+            rays += st.closestRays + st.shadowRays; closest += st.closestRays; paths += st.paths; launches += st.kernelLaunches
+            merge_cand += st.bvhNodeVisits; merge_acc += st.triTests
+            for k in range(4):
+                stage_ms[k] += st.stageMs[k]
+    if tiles:
+        rays = (st.closestRays + st.shadowRays) - (before.closestRays + before.shadowRays)
+        closest = st.closestRays - before.closestRays; paths = st.paths - before.paths; launches = st.kernelLaunches - before.kernelLaunches
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -152,23 +218,30 @@ def run_ours(args):
     max_dev_ms, max_wall_ms, max_extend_ms = [float(x) for x in mx.tolist()]
 
     # ---- end-to-end through the host-facing call: render + D2H of the framebuffer (+ NCCL reduce for N > 1) ----
-    e2e_rays, e2e_wall = 0, 0.0
+    e2e_rays = 0
     host_img = None
     scene.set_profile(0)
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     e0 = time.time()
+    base_i = args.warmup + args.steps
     for i in range(args.steps):
-        if world == 1:
-            host_img, st = scene.render(cfg, cam, (args.warmup + args.steps + i) * S, S)      # allocs, renders, copies w*h*16 B to host
+        if world == 1 and not tiles:
+            host_img, st = scene.render(cfg, cam, (base_i + i) * S, S)      # allocates, renders, copies w*h*16 B to host
+            e2e_rays += st.closestRays + st.shadowRays
         else:
             colors.zero_()
-            st = scene.render_device(cfg, cam, (args.warmup + args.steps + i) * S * world, S * world, colors.data_ptr(), rank=rank, world=world)
-            dist.reduce(colors, 0)
+            if tiles:
+                before = tiler.session.stats()
+                st = tiler.render((base_i + i) * S * world, S * world, colors)
+                e2e_rays += (st.closestRays + st.shadowRays) - (before.closestRays + before.shadowRays)
+            else:
+                st = scene.render_device(cfg, cam, (base_i + i) * S * world, S * world, colors.data_ptr(), rank=rank, world=world)
+                e2e_rays += st.closestRays + st.shadowRays
+            nd.reduce_frames(colors, dist, 0)
             if rank == 0:
                 host_img = colors.cpu().numpy()
-        e2e_rays += st.closestRays + st.shadowRays
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -177,22 +250,33 @@ def run_ours(args):
     if dist is not None:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.SUM)
 
-    # ---- roofline of the dominant kernel (wfExtend: BVH8 closest-hit traversal) ----
-    st = step(10_000, profile=3)       # one counted step (slower kernel, not timed): nodes / triangles per ray
-    vn = st.bvhNodeVisits / max(1, st.closestRays); vt = st.triTests / max(1, st.closestRays)
-    bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt            # ray in + hit out + 80 B nodes + 48 B triangles
-    peak, peak_src = peaks()
-    achieved = (closest * bytes_per_ray) / (stage_ms[0] * 1e-3) / 1e9 if stage_ms[0] > 0 else 0.0
+    # ---- roofline of the dominant kernel class: BVH8 closest-hit traversal (wfExtend / bdExtend) ----
+    roof = None
+    if not tiles:
+        st, _ = step(10_000, profile=3)       # one counted step (slower kernel, not timed): nodes / triangles per ray
+        vn = st.bvhNodeVisits / max(1, st.closestRays); vt = st.triTests / max(1, st.closestRays)
+        bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt            # ray in + hit out + 80 B nodes + 48 B triangles
+        peak, peak_src = peaks()
+        achieved = (closest * bytes_per_ray) / (stage_ms[0] * 1e-3) / 1e9 if stage_ms[0] > 0 else 0.0
+        names = ({"extend": 0, "step": 1, "resolve": 2, "grid+other": 3} if bidir else {"extend": 0, "shade": 1, "shadow": 2, "other": 3})
+        roof = {"bound": "hbm", "kernel": "bdExtend (BVH8 closest hit)" if bidir else "wfExtend (BVH8 closest hit)", "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
+                "closest_rays_per_s": closest / (stage_ms[0] * 1e-3) if stage_ms[0] > 0 else None,
+                "extend_ms_share": stage_ms[0] / dev_ms if dev_ms else None,
+                "stage_ms": {k: stage_ms[v] for k, v in names.items()}}
 
     if rank == 0:
         line = {
             "metric": "Mrays/s", "value": tot_rays / (max_dev_ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": max_dev_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl_name, "scene": args.workload, "tris": info["tris"], "bvh8_nodes": info["bvh8_nodes"],
-                       "width": w, "height": h, "spp_per_step_per_gpu": S, "max_depth": cfg.maxDepth,
-                       "sharding": "sample passes striped over ranks, framebuffer sum-reduced (NCCL) at the end",
-                       "l2": "256 MB flush between steps; path pool + queues (~0.4 GB) exceed the 126 MB L2",
+            "config": {"workload": wl["desc"], "scene": args.workload, "tris": info["tris"], "bvh8_nodes": info["bvh8_nodes"],
+                       "width": w, "height": h, "passes_per_step_per_gpu": S, "max_depth": cfg.maxDepth,
+                       "eye_depth": cfg.bdptEyeDepth, "light_depth": cfg.bdptLightDepth,
+                       "sharding": ("pixel rows striped over ranks, photon slabs all-gathered (NCCL) every iteration, frames sum-reduced at the end"
+                                    if tiles else "sample passes / iterations striped over ranks, frames sum-reduced (NCCL) at the end"),
+                       "l2": "256 MB flush between steps; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
                        "scene_load_s": round(load_s, 3)},
             "paths_per_s": tot_paths / (max_dev_ms * 1e-3), "rays_per_path": tot_rays / max(1.0, tot_paths),
             "wall_ms_per_step": max_wall_ms / args.steps,
@@ -201,90 +285,79 @@ def run_ours(args):
                     "note": "novum_render: camera/config in, render, framebuffer (w*h float4) copied to host every step"},
             "gpu_launches": int(tot_launch),
             "clocks": clk,
-            "roofline": {"bound": "hbm", "kernel": "wfExtend (BVH8 closest hit)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
-                         "extend_ms_share": stage_ms[0] / dev_ms if dev_ms else None,
-                         "stage_ms": {"extend": stage_ms[0], "shade": stage_ms[1], "shadow": stage_ms[2], "other": stage_ms[3]}},
         }
+        if roof:
+            line["roofline"] = roof
+        if bidir:
+            line["photons_per_iteration"] = int(photons) if tiles else int(photons // max(1, S))
+            line["merge"] = {"candidates_per_step": merge_cand // max(1, args.steps), "merged_per_step": merge_acc // max(1, args.steps)}
+        if tiles:
+            line["exchange_bytes_per_iteration_per_gpu"] = int(tiler.slabs.numel())
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_oracle_baseline(sdir, args.workload)
         if host_img is not None:
-            line["image_mean"] = float(host_img[..., :3].mean())
+            line["image_mean"] = float(host_img[..., :3].mean() / max(1, S * world))
         print(json.dumps(line))
+    if tiler:
+        tiler.close()
     scene.close()
     if dist is not None:
         dist.destroy_process_group()
 
 
-def cpu_oracle_baseline(sdir, workload, target_s=12.0):
-    """The CPU restatement of the reference's path (oracle/, kind "port") on the host cores, on a bounded sample:
-    the same scene and camera at reduced resolution, sized for ~10-20 s."""
-    import numpy as np
-    import cudapathtracer_b200 as nb
-    from oracle.oracle_binding import OracleScene
-    scene = nb.Scene.from_config(os.path.join(sdir, "configs", "config.rendertron"))
-    pos, nrm, uv, tris, lights = scene.download()
-    cfg = scene.cfg
-    scene.close()
-    ora = OracleScene(pos, nrm, uv, tris, nb.material_table(), None, 2)
-    _, _, w, h, _ = WORKLOADS[workload]
-    sw, sh, spp = max(16, w // 16), max(9, h // 16), 1
-    cfg.width, cfg.height = sw, sh
-    cam = nb.camera_make(cfg)
-    t0 = time.time()
-    img, counts = ora.render_unidirectional(bytes(cam), sw, sh, cfg.maxDepth, 0, spp)
-    dt = time.time() - t0
-    if dt < target_s / 4:          # grow the sample towards the target duration
-        spp = int(min(64, max(1, target_s / max(dt, 1e-3))))
-        t0 = time.time()
-        img, counts = ora.render_unidirectional(bytes(cam), sw, sh, cfg.maxDepth, 1, spp)
-        dt = time.time() - t0
-    rays = float(counts[0] + counts[1])
-    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": f"{sw}x{sh} px x {spp} spp of the same scene/camera, OpenMP on all host cores ({dt:.1f} s)",
-            "paths_per_s": sw * sh * spp / dt, "rays_per_path": rays / (sw * sh * spp)}
-
-
 def run_reference(args):
     """The reference's own CUDA build (unmodified sources, oracle/_ref/novum_ref) on ONE B200 of this box: it is GPU-only,
-    so this is the baseline north_star names. Rays are not counted by the reference; its ray count per path is taken from
-    the CPU restatement of its algorithm on a sample of the same workload."""
+    so this is the baseline north_star names. Its rays per pass come from the counting build of the same sources
+    (oracle/_ref/novum_ref_count, run once on one pass, never timed)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import cudapathtracer_b200 as nb
     ref = os.path.join(REPO, "oracle", "_ref", "novum_ref")
+    refc = os.path.join(REPO, "oracle", "_ref", "novum_ref_count")
+    wl = WORKLOADS[args.workload]
     sdir = scene_dir_for(args.workload, args.detail, 0, None)
-    _, _, w, h, wl_name = WORKLOADS[args.workload]
-    S = args.spp_per_step
-    base = cpu_oracle_baseline(sdir, args.workload, target_s=8.0)
+    w, h = wl["w"], wl["h"]
+    S = args.spp_per_step or wl["spp"]
     if not os.path.exists(ref):
+        base = cpu_oracle_baseline(sdir, args.workload, target_s=8.0)
         line = {"impl": "reference", "metric": "Mrays/s", "value": base["value"], "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps,
-                "warmup": args.warmup, "higher_is_better": True, "config": {"workload": wl_name}, "cpu_baseline": base,
+                "warmup": args.warmup, "higher_is_better": True, "config": {"workload": wl["desc"]}, "cpu_baseline": base,
                 "e2e": {"value": base["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "note": "oracle/_ref/novum_ref not built on this box: CPU port of the reference's algorithm instead"}
         print(json.dumps(line))
         return
 
-    def run(spp):
-        out = subprocess.check_output([ref, "render", sdir, "--spp", str(spp), "--out", os.path.join(tempfile.gettempdir(), "ref.raw")],
+    def run(binary, spp):
+        out = subprocess.check_output([binary, "render", sdir, "--spp", str(spp), "--out", os.path.join(tempfile.gettempdir(), "ref.raw")],
                                       stderr=subprocess.STDOUT).decode()
         return json.loads(re.search(r"NOVUM_REF_JSON (\{.*\})", out).group(1))
 
-    a = run(max(1, args.warmup * S))                     # includes curand_init, allocations: subtracted out below
-    b = run((args.warmup + args.steps) * S)
+    a = run(ref, max(1, args.warmup * S))                     # includes curand_init, allocations: subtracted out below
+    b = run(ref, (args.warmup + args.steps) * S)
     ms = b["launch_ms"] - a["launch_ms"]
-    paths = w * h * args.steps * S
-    rays = paths * base["rays_per_path"]
+    bidir = wl["integ"] in (BDPT, VCM, SPPM)
+    passes = args.steps * S
+    paths = w * h * passes * (2 if bidir else 1)
+    rays_per_pass, how = None, None
+    if os.path.exists(refc):
+        nc = 1 if bidir else min(4, S)
+        c = run(refc, nc)
+        rays_per_pass = (c["closest_rays"] + c["shadow_rays"]) / nc
+        how = f"device counters of the counting build of the same sources over {nc} pass(es)"
+    else:
+        base = cpu_oracle_baseline(sdir, args.workload, target_s=8.0)
+        rays_per_pass = base["rays_per_path"] * w * h
+        how = "rays per path of the CPU restatement"
+    rays = rays_per_pass * passes
     val = rays / (ms * 1e-3) / 1e6
     line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl_name, "scene": args.workload, "tris": b["tris"], "width": w, "height": h, "spp_per_step_per_gpu": S,
-                       "timing": "launch_unidirectional CUDA-event time at (W+K)*S spp minus at W*S spp (drops curand_init + allocation)"},
-            "paths_per_s": paths / (ms * 1e-3), "rays_per_path": base["rays_per_path"],
+            "config": {"workload": wl["desc"], "scene": args.workload, "tris": b["tris"], "width": w, "height": h, "passes_per_step_per_gpu": S,
+                       "timing": "launch_* CUDA-event time at (W+K)*S passes minus at W*S passes (drops curand_init + allocation)",
+                       "rays": how},
+            "paths_per_s": paths / (ms * 1e-3), "rays_per_path": rays / paths,
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference",
-                             "sample": f"whole workload: {args.steps} steps x {S} spp at {w}x{h} on one B200 (the reference has no CPU path)"},
+                             "sample": f"whole workload: {args.steps} steps x {S} passes at {w}x{h} on one B200 (the reference has no CPU path)"},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "reference_bvh_build_s": b["bvh_build_s"]}
     print(json.dumps(line))
@@ -297,7 +370,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="dragon_nee", choices=sorted(WORKLOADS))
-    ap.add_argument("--spp-per-step", type=int, default=32)
+    ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
+    ap.add_argument("--sharding", default="striped", choices=["striped", "tiles"])
     ap.add_argument("--detail", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

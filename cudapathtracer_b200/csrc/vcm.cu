@@ -95,6 +95,7 @@ enum : unsigned { SR_CLAMP = 1u << 31, SR_NEE = 1u << 30, SR_PIXMASK = (1u << 30
 
 NV_D void pushShadow(const BdState& st, int* cnt, V3 o, V3 d, float maxT, int skip, unsigned pixFlags, V3 contrib) {
     if (contrib.x == 0.0f && contrib.y == 0.0f && contrib.z == 0.0f) return;
+    if (!(isfinite(contrib.x) && isfinite(contrib.y) && isfinite(contrib.z))) return;     // a non-finite sample is dropped, not accumulated
     int pos = bdAggAppend(&cnt[BC_SHADOW]);
     if (pos >= st.shadowCap) return;
     float4* rec = reinterpret_cast<float4*>(st.shadowQ + pos);
@@ -204,12 +205,12 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStart(SceneView sc, BdState
 }
 
 // closest hit for every queued path of this depth
-__global__ void __launch_bounds__(kBdThreads) bdExtend(SceneView sc, BdState st, const int* __restrict__ queue, int* cnt) {
+template <bool COUNT>
+__global__ void __launch_bounds__(kBdThreads) bdExtend(SceneView sc, BdState st, const int* __restrict__ queue, int* cnt, TravCounters tc) {
     __shared__ uint2 stackMem[kSmemStack * kBdThreads];
     TravStack ts; ts.init(stackMem + threadIdx.x, kBdThreads);
     const int lane = bdLane();
     const int n = cnt[BC_QUEUE];
-    TravCounters nocnt{nullptr, nullptr};
     unsigned long long traced = 0;
     while (true) {
         int base = 0;
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(kBdThreads) bdExtend(SceneView sc, BdState st,
         if (i < n) {
             int l = __ldg(queue + i);
             float4 o = st.rayO[l], d = st.rayD[l];
-            HitRec h = traceClosest<false>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, nocnt);
+            HitRec h = traceClosest<COUNT>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, tc);
             st.hit[l] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
             ++traced;
         }
@@ -394,7 +395,6 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
     const int n = cnt[BC_QUEUE];
     const bool vcm = P.mode == BD_MODE_VCM;
     const float eta = P.etaVcm;
-    unsigned long long nMerged = 0;
     while (true) {
         int base = 0;
         if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_STEP], 32);
@@ -525,38 +525,19 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                         // ---- merging with the photons of the 27 neighbouring cells (:2968-3048) ----
                         if (vcm && P.doMerge) {
                           if (P.mergeRadius > 0.0f) {
-                            const float r2 = P.mergeRadius * P.mergeRadius;
-                            const int3 c0 = gridIndex(s.p.x, s.p.y, s.p.z, P.grid);
-                            const float norm = 1.0f / (kPi * r2 * (float)P.w * (float)P.h);
-                            for (int dz = -1; dz <= 1; ++dz) for (int dy = -1; dy <= 1; ++dy) for (int dx = -1; dx <= 1; ++dx) {
-                                unsigned hsh = hashCell(make_int3(c0.x + dx, c0.y + dy, c0.z + dz), P.grid.tableSize);
-                                uint32_t cs = __ldg(P.cellStart + hsh);
-                                if (cs == 0xFFFFFFFFu) continue;
-                                uint32_t ce = __ldg(P.cellEnd + hsh);
-                                for (uint32_t q = cs; q < ce; ++q) {
-                                    uint4 A = __ldg(P.photons + (size_t)q * 2);
-                                    V3 diff = s.p - V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
-                                    if (dot(diff, diff) > r2) continue;
-                                    uint4 B = __ldg(P.photons + (size_t)q * 2 + 1);
-                                    float2 bxy = unpackHalf2(B.x), bz = unpackHalf2(B.y);
-                                    float lightDvm = __uint_as_float(B.z), lightDvcm = __uint_as_float(B.w);
-                                    V3 photonPrevToPhotonL = fr.toLocal(-unpackOct(A.w));
-                                    float eyeRev = bsdfPdf(o.sh, photonPrevToPhotonL, toPrevL, 1.0f);
-                                    float lightRev = bsdfPdf(o.sh, -toPrevL, -photonPrevToPhotonL, 1.0f);
-                                    float wEye = o.d_vcm / eta + eyeRev * o.d_vm;
-                                    float wLight = lightDvcm / eta + lightRev * lightDvm;
-                                    float w = 1.0f / (1.0f + wEye + wLight);
-                                    V3 f = bsdfEval(o.sh, photonPrevToPhotonL, toPrevL, 1.0f);
-                                    V3 unweighted = V3(bxy.x, bxy.y, bz.x) * f * o.currBeta * norm;
-                                    sum += applyWeight(P, unweighted, w);
-                                    ++nMerged;
-                                }
-                            }
+                            // deferred: the photon gather runs warp-cooperatively in bdMerge on this record
+                            int pos = bdAggAppend(&cnt[BC_MERGE]);
+                            float4* rec = reinterpret_cast<float4*>(st.mergeQ + pos);
+                            rec[0] = make_float4(s.p.x, s.p.y, s.p.z, __int_as_float(pix));
+                            rec[1] = make_float4(s.n.x, s.n.y, s.n.z, __int_as_float(s.mat));
+                            rec[2] = make_float4(toPrevL.x, toPrevL.y, toPrevL.z, o.d_vcm);
+                            rec[3] = make_float4(o.currBeta.x, o.currBeta.y, o.currBeta.z, o.d_vm);
+                            rec[4] = make_float4(s.uv.x, s.uv.y, 0.f, 0.f);
                           }
                           if (P.doSPPM) endPath = true;              // SPPM gathers density once (:3046)
                         }
                     }
-                    if (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) atomicAdd(&P.colors[pix], make_float4(sum.x, sum.y, sum.z, 0.f));
+                    if ((sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) && isfinite(sum.x) && isfinite(sum.y) && isfinite(sum.z)) atomicAdd(&P.colors[pix], make_float4(sum.x, sum.y, sum.z, 0.f));
                     bool through = dot(o.wiW, s.n) < 0.0f;                                       // :3053, :936
                     p.o = through ? s.p - s.n * kRayEps : s.p + s.n * kRayEps;
                     p.d = vcm ? o.wiW : normalize(o.wiW);                                        // :3056 vs :944
@@ -569,8 +550,110 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
         int pos = bdWarpAppend(&nextCnt[BC_QUEUE], cont);
         if (cont) nextQueue[pos] = l;
     }
-    for (int o = 16; o > 0; o >>= 1) nMerged += __shfl_xor_sync(0xffffffffu, nMerged, o);
-    if (lane == 0 && nMerged) atomicAdd(&st.stats[4], nMerged);
+}
+
+// ---- merging (deviceCode.cu:2968-3048), one warp per eye vertex ----------------------------------------------------------------
+// Lanes 0..26 look up the 27 neighbour cells (same z, y, x order and the same per-cell lookups as the reference, so a table
+// slot shared by two neighbours is visited twice there and here); the cells' photon ranges are concatenated with a warp scan
+// and swept 32 candidates at a time (coalesced reads of the cell-ordered records). Candidates inside the radius are compacted
+// into a per-warp buffer so that the expensive part — two reverse pdfs, the BSDF value, the VM MIS weight — always runs on
+// full warps. The BSDF dispatch is uniform across the warp (one eye vertex = one material).
+constexpr int kMergeWarps = kBdThreads / 32;
+
+NV_D V3 mergeOne(const BdParams& P, const Shading& sh, const Frame& fr, V3 eyeP, V3 toPrevL, V3 currBeta, float eyeDvcm, float eyeDvm,
+                 float norm, uint32_t q) {
+    uint4 A = __ldg(P.photons + (size_t)q * 2), B = __ldg(P.photons + (size_t)q * 2 + 1);
+    float2 bxy = unpackHalf2(B.x), bz = unpackHalf2(B.y);
+    float lightDvm = __uint_as_float(B.z), lightDvcm = __uint_as_float(B.w);
+    V3 photonPrevToPhotonL = fr.toLocal(-unpackOct(A.w));
+    float eyeRev = bsdfPdf(sh, photonPrevToPhotonL, toPrevL, 1.0f);
+    float lightRev = bsdfPdf(sh, -toPrevL, -photonPrevToPhotonL, 1.0f);
+    float wEye = eyeDvcm / P.etaVcm + eyeRev * eyeDvm;
+    float wLight = lightDvcm / P.etaVcm + lightRev * lightDvm;
+    float w = 1.0f / (1.0f + wEye + wLight);
+    V3 f = bsdfEval(sh, photonPrevToPhotonL, toPrevL, 1.0f);
+    return applyWeight(P, V3(bxy.x, bxy.y, bz.x) * f * currBeta * norm, w);
+}
+
+__global__ void __launch_bounds__(kBdThreads) bdMerge(SceneView sc, BdState st, BdParams P, int* cnt) {
+    __shared__ uint32_t accBuf[kMergeWarps][64];
+    const int lane = bdLane(), warp = threadIdx.x >> 5;
+    const int n = cnt[BC_MERGE];
+    const float r2 = P.mergeRadius * P.mergeRadius;
+    const float norm = 1.0f / (kPi * r2 * (float)P.w * (float)P.h);
+    const unsigned ltMask = (1u << lane) - 1u;
+    unsigned long long nMerged = 0, nCand = 0;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], 4);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const int end = min(base + 4, n);
+        for (int r = base; r < end; ++r) {
+            const float4* rp = reinterpret_cast<const float4*>(st.mergeQ + r);
+            const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2q = __ldg(rp + 2), r3 = __ldg(rp + 3), r4 = __ldg(rp + 4);
+            const V3 eyeP(r0.x, r0.y, r0.z), toPrevL(r2q.x, r2q.y, r2q.z), currBeta(r3.x, r3.y, r3.z);
+            const int pix = __float_as_int(r0.w);
+            const Frame fr(V3(r1.x, r1.y, r1.z));
+            const Shading sh = resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y));
+            const int3 c0 = gridIndex(eyeP.x, eyeP.y, eyeP.z, P.grid);
+            uint32_t cs = 0, cc = 0;
+            if (lane < 27) {
+                int dz = lane / 9 - 1, dy = (lane / 3) % 3 - 1, dx = lane % 3 - 1;
+                unsigned hsh = hashCell(make_int3(c0.x + dx, c0.y + dy, c0.z + dz), P.grid.tableSize);
+                uint32_t s0 = __ldg(P.cellStart + hsh);
+                if (s0 != 0xFFFFFFFFu) { cs = s0; cc = __ldg(P.cellEnd + hsh) - s0; }
+            }
+            uint32_t incl = cc;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+            const uint32_t excl = incl - cc;
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+            nCand += (lane == 0) ? total : 0;
+            int count = 0;
+            V3 sum(0.0f);
+            for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+                const uint32_t j = j0 + lane;
+                // cell of candidate j: the largest c with excl[c] <= j (binary search over the lanes' prefix values)
+                int c = 0;
+#pragma unroll
+                for (int stp = 16; stp >= 1; stp >>= 1) {
+                    int t = c + stp;
+                    uint32_t e = __shfl_sync(0xffffffffu, excl, t & 31);
+                    if (t < 27 && e <= j) c = t;
+                }
+                const uint32_t q = __shfl_sync(0xffffffffu, cs, c) + (j - __shfl_sync(0xffffffffu, excl, c));
+                bool accept = false;
+                if (j < total) {
+                    uint4 A = __ldg(P.photons + (size_t)q * 2);
+                    V3 diff = eyeP - V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
+                    accept = dot(diff, diff) <= r2;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, accept);
+                if (accept) accBuf[warp][count + __popc(m & ltMask)] = q;
+                count += __popc(m);
+                __syncwarp();
+                if (count >= 32) {
+                    sum += mergeOne(P, sh, fr, eyeP, toPrevL, currBeta, r2q.w, r3.w, norm, accBuf[warp][lane]);
+                    uint32_t carry = accBuf[warp][32 + lane];
+                    __syncwarp();
+                    accBuf[warp][lane] = carry;
+                    count -= 32; nMerged += 32;
+                    __syncwarp();
+                }
+            }
+            if (lane < count) sum += mergeOne(P, sh, fr, eyeP, toPrevL, currBeta, r2q.w, r3.w, norm, accBuf[warp][lane]);
+            nMerged += count;
+            __syncwarp();
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                sum.x += __shfl_xor_sync(0xffffffffu, sum.x, o); sum.y += __shfl_xor_sync(0xffffffffu, sum.y, o); sum.z += __shfl_xor_sync(0xffffffffu, sum.z, o);
+            }
+            if (lane == 0 && (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) && isfinite(sum.x) && isfinite(sum.y) && isfinite(sum.z))
+                atomicAdd(&P.colors[pix], make_float4(sum.x, sum.y, sum.z, 0.f));
+        }
+    }
+    if (lane == 0) { if (nMerged) atomicAdd(&st.stats[4], nMerged); if (nCand) atomicAdd(&st.stats[5], nCand); }
 }
 
 // ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------

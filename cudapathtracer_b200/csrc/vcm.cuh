@@ -31,9 +31,11 @@ constexpr int kMaxBdDepth = 32;          // eye / light depth limit of the wavef
 constexpr int kSlabHeaderBytes = 32;
 
 // per (pass, depth) counters; one memset per pass clears them all
-enum : int { BC_QUEUE = 0, BC_SHADOW = 1, BC_FETCH_EXTEND = 2, BC_FETCH_STEP = 3, BC_FETCH_RESOLVE = 4, BC_STRIDE = 8 };
+enum : int { BC_QUEUE = 0, BC_SHADOW = 1, BC_FETCH_EXTEND = 2, BC_FETCH_STEP = 3, BC_FETCH_RESOLVE = 4, BC_MERGE = 5, BC_FETCH_MERGE = 6, BC_STRIDE = 8 };
 
 struct __align__(16) BdShadowRec { float4 o_maxT; float4 d_pix; float4 contrib_skip; };   // 48 B
+// eye vertex waiting for its photon gather: {p, pixel} {n, material} {toPrev (local frame), d_vcm} {beta, d_vm} {uv}
+struct __align__(16) BdMergeRec { float4 p_pix, n_mat, toPrev_dvcm, beta_dvm, uv; };      // 80 B
 
 struct BdState {
     // per local path (shared by the light pass and the eye pass, which run one after the other)
@@ -48,8 +50,9 @@ struct BdState {
     int* pathLen;      // surface vertices stored per light path
     uint4 *lvA, *lvB, *lvC;
     BdShadowRec* shadowQ;
+    BdMergeRec* mergeQ;         // at most one record per path and depth
     int* counters;     // (kMaxBdDepth + 1) * BC_STRIDE
-    unsigned long long* stats;   // [0] closest rays [1] shadow rays [2] photons stored [3] light vertices stored [4] merges accepted
+    unsigned long long* stats;   // [0] closest rays [1] shadow rays [2] photons stored [3] light vertices stored [4] merges accepted [5] merge candidates (photons in the 27 cells)
     int nLocal;
     int shadowCap;
 };

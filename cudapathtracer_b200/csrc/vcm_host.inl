@@ -24,19 +24,32 @@ struct BdEngine {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     unsigned long long launches = 0, iterations = 0;
     float deviceMs = 0.f;
-    float stageMs[4] = {0, 0, 0, 0};      // light pass, grid build, eye pass, (unused)
+    float stageMs[4] = {0, 0, 0, 0};      // profile bit 0: [0] closest-hit extends [1] light/eye step kernels [2] shadow resolves [3] photon grid build + merge kernels + rest
+    unsigned long long stageLaunches[4] = {0, 0, 0, 0};
+    bool prof = false, profCount = false;
+    std::vector<cudaEvent_t> evs; std::vector<int> evCls; size_t evUsed = 0;
     size_t bytes = 0;
 };
+
+// profile bit 0: an event after every launch, tagged with the launch's class; the gap to the previous event is charged to it
+static void bdTick(BdEngine& e, int cls) {
+    e.stageLaunches[cls]++;
+    if (!e.prof) return;
+    if (e.evUsed == e.evs.size()) { cudaEvent_t ev; cudaEventCreate(&ev); e.evs.push_back(ev); e.evCls.push_back(0); }
+    e.evCls[e.evUsed] = cls;
+    cudaEventRecord(e.evs[e.evUsed++], e.scene->stream);
+}
 
 static void bdFree(BdEngine& e) {
     BdState& s = e.st;
     cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.dv); cudaFree(s.rng); cudaFree(s.hit);
     cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
-    cudaFree(s.shadowQ); cudaFree(s.counters); cudaFree(s.stats);
+    cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.counters); cudaFree(s.stats);
     cudaFree(e.slabs); cudaFree(e.photonsAll); cudaFree(e.photonsSorted); cudaFree(e.d_counts);
     if (e.h_counts) cudaFreeHost(e.h_counts);
     if (e.gridAllocated) hashGridFree(e.grid);
     if (e.ev0) { cudaEventDestroy(e.ev0); cudaEventDestroy(e.ev1); }
+    for (cudaEvent_t ev : e.evs) cudaEventDestroy(ev);
     e = BdEngine();
 }
 
@@ -68,6 +81,7 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     if (cap > 0x7fffffffull) cap = 0x7fffffffull;
     s.shadowCap = (int)cap;
     A((void**)&s.shadowQ, cap * sizeof(BdShadowRec));
+    if (e.mode == BD_MODE_VCM) A((void**)&s.mergeQ, n * sizeof(BdMergeRec));
     A((void**)&s.counters, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int));
     A((void**)&s.stats, 8 * sizeof(unsigned long long));
     // photon storage: one slab per rank, sized for that rank's worst case (every vertex of every light path)
@@ -133,17 +147,22 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
     cudaMemsetAsync(P.slab, 0, kSlabHeaderBytes, s);                      // photon counter of this rank (deviceCode.cu:3330)
     if (e.nLocal == 0 || sc.numLights == 0) return 0;
     const int numSteps = e.mode == BD_MODE_BDPT ? e.lightDepth - 1 : e.lightDepth;      // :1116 (depth 1..max-1) vs :2029 (0..max-1)
+    bdTick(e, 3);
     bdLightStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(sc, st, P);
-    ++e.launches;
+    ++e.launches; bdTick(e, 1);
     const int grid = bdGrid();
+    TravCounters tc{e.scene->d_counters, e.scene->d_counters + 1};
     for (int step = 0; step < numSteps; ++step) {
         int* cnt = st.counters + step * BC_STRIDE;
-        bdExtend<<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt);
+        if (e.profCount) bdExtend<true><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
+        else bdExtend<false><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
+        bdTick(e, 0);
         bdLightStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
-        if (P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; }
+        bdTick(e, 1);
+        if (P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; bdTick(e, 2); }
         e.launches += 2;
     }
-    if (numSteps == 0 && P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, st.counters); ++e.launches; }
+    if (numSteps == 0 && P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, st.counters); ++e.launches; bdTick(e, 2); }
     return (int)cudaGetLastError();
 }
 
@@ -176,6 +195,7 @@ static int bdBuildGrid(BdEngine& e, int iter) {
         bdReorderPhotons<<<(e.photonCount + 255) / 256, 256, 0, s>>>(src, e.grid.index, e.photonCount, e.photonsSorted);
         ++e.launches;
     }
+    bdTick(e, 3);
     return (int)cudaGetLastError();
 }
 
@@ -187,15 +207,22 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
     if (e.nLocal == 0) return 0;
     cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
     const int numSteps = e.mode == BD_MODE_BDPT ? e.eyeDepth - 1 : e.eyeDepth;          // :794 vs :2723
+    bdTick(e, 3);
     bdEyeStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(st, P);
-    ++e.launches;
+    ++e.launches; bdTick(e, 1);
     const int grid = bdGrid();
     const bool shadows = P.nee || P.connection;
+    const bool merging = e.mode == BD_MODE_VCM && P.doMerge && P.mergeRadius > 0.0f;
+    TravCounters tc{e.scene->d_counters, e.scene->d_counters + 1};
     for (int step = 0; step < numSteps; ++step) {
         int* cnt = st.counters + step * BC_STRIDE;
-        bdExtend<<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt);
+        if (e.profCount) bdExtend<true><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
+        else bdExtend<false><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
+        bdTick(e, 0);
         bdEyeStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
-        if (shadows) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; }
+        bdTick(e, 1);
+        if (shadows) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; bdTick(e, 2); }
+        if (merging) { bdMerge<<<grid, kBdThreads, 0, s>>>(sc, st, P, cnt); ++e.launches; bdTick(e, 3); }
         e.launches += 2;
     }
     ++e.iterations;
@@ -208,17 +235,26 @@ static void bdFillStats(BdEngine& e, NovumRenderStats* stats) {
     cudaMemcpy(h, e.st.stats, sizeof(h), cudaMemcpyDeviceToHost);
     memset(stats, 0, sizeof(*stats));
     stats->closestRays = h[0]; stats->shadowRays = h[1]; stats->photons = h[2]; stats->lightVertices = h[3];
-    stats->triTests = h[4];                           // merges accepted (photons within the radius), reported in the spare counter
+    stats->triTests = h[4];                           // bidirectional renders: photons merged (inside the radius) ...
+    stats->bvhNodeVisits = h[5];                      // ... and merge candidates (photons in the 27 cells), in the two spare counters
     stats->paths = 2ull * (unsigned long long)e.nLocal * e.iterations;      // one light + one eye path per pixel per iteration
     stats->kernelLaunches = e.launches;
     stats->deviceMs = e.deviceMs;
-    for (int k = 0; k < 4; ++k) stats->stageMs[k] = e.stageMs[k];
+    for (int k = 0; k < 4; ++k) { stats->stageMs[k] = e.stageMs[k]; stats->stageLaunches[k] = e.stageLaunches[k]; }
+    if (e.profCount) {
+        unsigned long long c2[2] = {0, 0};
+        cudaMemcpy(c2, e.scene->d_counters, sizeof(c2), cudaMemcpyDeviceToHost);
+        stats->bvhNodeVisits = c2[0];
+        stats->triTests = c2[1];                      // (replaces the merge count in the counted run)
+    }
 }
 
 static void bdResetStats(BdEngine& e) {
     cudaMemsetAsync(e.st.stats, 0, 8 * sizeof(unsigned long long), e.scene->stream);
-    e.launches = 0; e.iterations = 0; e.deviceMs = 0.f;
-    for (int k = 0; k < 4; ++k) e.stageMs[k] = 0.f;
+    e.launches = 0; e.iterations = 0; e.deviceMs = 0.f; e.evUsed = 0;
+    for (int k = 0; k < 4; ++k) { e.stageMs[k] = 0.f; e.stageLaunches[k] = 0; }
+    e.prof = (e.scene->profileFlags & 1) != 0; e.profCount = (e.scene->profileFlags & 2) != 0;
+    if (e.profCount) cudaMemsetAsync(e.scene->d_counters, 0, 2 * sizeof(unsigned long long), e.scene->stream);
 }
 
 static void bdEngineFree(void* p) { BdEngine* e = (BdEngine*)p; bdFree(*e); delete e; }
@@ -243,19 +279,12 @@ int vcmRenderDevice(NovumScene* s, const NovumRenderConfig* cfg, const NovumCame
     }
     e->cam = *cam; e->cfg = *cfg; e->seed = seed;
     bdResetStats(*e);
-    const bool prof = (s->profileFlags & 1) != 0;
-    std::vector<cudaEvent_t> evs;
     cudaEventRecord(e->ev0, s->stream);
     for (int k = shard.rank; k < numSample; k += shard.world) {
         int iter = firstSample + k;
-        auto mark = [&]() { if (prof) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, s->stream); evs.push_back(ev); } };
-        mark();
         int rc = bdLightPass(*e, iter, d_colors);
-        mark();
         if (!rc) rc = bdBuildGrid(*e, iter);
-        mark();
         if (!rc) rc = bdEyePass(*e, iter, d_colors);
-        mark();
         if (rc) return rc;
     }
     cudaEventRecord(e->ev1, s->stream);
@@ -263,9 +292,7 @@ int vcmRenderDevice(NovumScene* s, const NovumRenderConfig* cfg, const NovumCame
     if (err != cudaSuccess) return (int)err;
     if ((err = cudaGetLastError()) != cudaSuccess) return (int)err;
     cudaEventElapsedTime(&e->deviceMs, e->ev0, e->ev1);
-    for (size_t i = 0; i + 3 < evs.size(); i += 4)
-        for (int k = 0; k < 3; ++k) { float ms = 0; cudaEventElapsedTime(&ms, evs[i + k], evs[i + k + 1]); e->stageMs[k] += ms; }
-    for (cudaEvent_t ev : evs) cudaEventDestroy(ev);
+    for (size_t i = 1; i < e->evUsed; ++i) { float ms = 0; cudaEventElapsedTime(&ms, e->evs[i - 1], e->evs[i]); e->stageMs[e->evCls[i]] += ms; }
     bdFillStats(*e, stats);
     return 0;
 }

@@ -59,7 +59,11 @@ NV_D void storePath(const WfState& st, int slot, const PathRegs& p) {
     st.rng[slot] = p.rng.state;
 }
 
+// A non-finite sample (e.g. the NEE weight inf/inf when the shading point lies exactly in the light's plane, deviceCode.cu:468-471)
+// poisons the pixel for good in the reference, which paints such pixels magenta at the end (main.cu:863-868); here the one
+// sample is dropped instead so the accumulator stays usable.
 NV_D void addColor(float4* colors, int pix, V3 c) {
+    if (!(isfinite(c.x) && isfinite(c.y) && isfinite(c.z))) return;
     if (c.x != 0.0f || c.y != 0.0f || c.z != 0.0f) atomicAdd(&colors[pix], make_float4(c.x, c.y, c.z, 0.f));
 }
 
@@ -148,7 +152,7 @@ NV_D bool shadeMIS(const SceneView& sc, const WfState& st, const WfParams& P, Pa
                 float bp = bsdfPdf(sh, wiLocal, toLight, etaI);
                 float wgt = lightPdf * lightPdf / (bp * bp + lightPdf * lightPdf);
                 V3 contrib = p.beta * (f * V3(em.x, em.y, em.z) * cosS / lightPdf) * wgt;
-                bool push = contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f;
+                bool push = (contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f) && isfinite(contrib.x) && isfinite(contrib.y) && isfinite(contrib.z);
                 // (no warp aggregation: lanes reach this point divergently inside a class only via lightPdf)
                 if (push) {
                     int pos = atomicAdd(&st.counters[C_SHADOW_COUNT], 1);

@@ -159,7 +159,8 @@ typedef struct NovumRenderStats {
     uint64_t kernelLaunches;
     float    deviceMs;                 /* CUDA-event time of the sample loop on the launch stream */
     float    _pad;
-    uint64_t bvhNodeVisits, triTests;  /* closest-hit traversal only; filled when profile bit 1 is set */
+    uint64_t bvhNodeVisits, triTests;  /* closest-hit traversal only; filled when profile bit 1 is set. VCM / SPPM renders
+                                          without bit 1 report merge candidates / photons merged here instead */
     float    stageMs[4];               /* profile bit 0: CUDA-event time of [0] extend (closest hit) [1] shade [2] shadow [3] other */
     uint64_t stageLaunches[4];
 } NovumRenderStats;

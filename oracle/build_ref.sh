@@ -17,5 +17,8 @@ fi
 NVCC="${NVCC:-nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -w -I$REF"
 # default nvcc flags otherwise (-fmad=true, -prec-div=true): the reference ships no build file
-$NVCC $FLAGS -o "$OUT/novum_ref" "$HERE/ref/ref_all.cu" -lcudart
+$NVCC $FLAGS -o "$OUT/novum_ref" "$HERE/ref/ref_all.cu" -lcudart &
+$NVCC $FLAGS -DNOVUM_REF_COUNT_RAYS -o "$OUT/novum_ref_count" "$HERE/ref/ref_all.cu" -lcudart &
+wait
+[ -x "$OUT/novum_ref" ] && [ -x "$OUT/novum_ref_count" ]
 echo "build_ref.sh: built $OUT/novum_ref"

@@ -38,6 +38,27 @@
 #include <utility>
 #undef __forceinline__
 #define __forceinline__ __attribute__((always_inline))
+#ifdef NOVUM_REF_COUNT_RAYS
+// Counting build (novum_ref_count, never the timed one): the reference's two intersection routines are compiled under other
+// names and re-exported through wrappers that bump device counters, so every call site in deviceCode.cu is counted without
+// touching a line of the reference. Gives the reference's OWN rays per path for the Mrays/s conversion in bench.py.
+__device__ unsigned long long g_refRayCounters[2];
+#define BVHSceneIntersect BVHSceneIntersect_refimpl
+#define BVHShadowRay BVHShadowRay_refimpl
+#include "integratorUtilities.cuh"
+#undef BVHSceneIntersect
+#undef BVHShadowRay
+__device__ inline void BVHSceneIntersect(const Ray& r, BVHnode* BVH, int* BVHindices, Vertices* verts, Triangle* scene, Intersection& intersect,
+                                         float max_t = 999999.0f, int skipTri = -1) {
+    atomicAdd(&g_refRayCounters[0], 1ull);
+    BVHSceneIntersect_refimpl(r, BVH, BVHindices, verts, scene, intersect, max_t, skipTri);
+}
+__device__ inline void BVHShadowRay(const Ray& r, BVHnode* BVH, int* BVHindices, Vertices* verts, Triangle* scene, Material* materials,
+                                    float4& throughputScale, float max_t, int skip_tri) {
+    atomicAdd(&g_refRayCounters[1], 1ull);
+    BVHShadowRay_refimpl(r, BVH, BVHindices, verts, scene, materials, throughputScale, max_t, skip_tri);
+}
+#endif
 #include "deviceCode.cu"
 #define main novum_reference_main_unused
 #include "main.cu"

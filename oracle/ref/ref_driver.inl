@@ -79,9 +79,13 @@ static int cmdRender(int argc, char** argv) {
     cudaMemcpy(host.data(), out_colors, host.size() * sizeof(float4), cudaMemcpyDeviceToHost);
     FILE* f = fopen(outAbs.c_str(), "wb");
     if (f) { fwrite(host.data(), sizeof(float4), host.size(), f); fclose(f); }
+    unsigned long long rayCnt[2] = {0, 0};
+#ifdef NOVUM_REF_COUNT_RAYS
+    cudaMemcpyFromSymbol(rayCnt, g_refRayCounters, sizeof(rayCnt));
+#endif
     printf("\nNOVUM_REF_JSON {\"integrator\": \"%s\", \"w\": %d, \"h\": %d, \"spp\": %d, \"tris\": %d, \"lights\": %d, \"bvh_nodes\": %d, "
-           "\"launch_ms\": %.3f, \"launch_wall_s\": %.4f, \"bvh_build_s\": %.4f, \"cuda_error\": %d}\n",
-           config.integratorType.c_str(), w, h, config.sampleCount, nt, nl, (int)S.bvh.size(), ms, wall, S.buildSeconds, (int)err);
+           "\"launch_ms\": %.3f, \"launch_wall_s\": %.4f, \"bvh_build_s\": %.4f, \"closest_rays\": %llu, \"shadow_rays\": %llu, \"cuda_error\": %d}\n",
+           config.integratorType.c_str(), w, h, config.sampleCount, nt, nl, (int)S.bvh.size(), ms, wall, S.buildSeconds, rayCnt[0], rayCnt[1], (int)err);
     return err == cudaSuccess ? 0 : 2;
 }
 

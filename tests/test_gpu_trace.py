@@ -70,7 +70,9 @@ def test_closest_hit_vs_reference_golden(name, gpu_scenes):
     ref = np.rec.fromarrays([g["tri"], g["t"], g["u"], g["v"]], names="tri,t,u,v")
     cls = classify(ours, ref)
     assert cls["mismatch"] == 0, cls                       # every non-tie, non-superset ray: same id, bit-equal t/u/v
-    assert cls["tie"] <= 2e-3 * cls["n"], cls              # first-found (reference) vs lowest-id (ours) on bit-equal t
+    # first-found (reference) vs lowest-id (ours) on bit-equal t. A quarter of the fixture's rays are aimed exactly at shared
+    # vertices and edge midpoints, where two or more triangles report the same t by construction.
+    assert cls["tie"] <= 2e-2 * cls["n"], cls
 
 
 @pytest.mark.parametrize("name", ["cornell", "dragon"])
