@@ -560,19 +560,37 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
 // full warps. The BSDF dispatch is uniform across the warp (one eye vertex = one material).
 constexpr int kMergeWarps = kBdThreads / 32;
 
-NV_D V3 mergeOne(const BdParams& P, const Shading& sh, const Frame& fr, V3 eyeP, V3 toPrevL, V3 currBeta, float eyeDvcm, float eyeDvm,
-                 float norm, uint32_t q) {
+// per-eye-vertex constants of the merge, hoisted out of the photon loop
+struct MergeCtx {
+    Shading sh; Frame fr; V3 eyeP, toPrevL, scale;     // scale = currBeta * 1/(pi r^2 w h)
+    float wEye;        // d_vcm / eta + eyeRev * d_vm for a diffuse surface (eyeRev does not depend on the photon there)
+    float eyeDvcmOverEta, eyeDvm, invEta;
+    bool diffuse;
+    NV_D MergeCtx(const Shading& s, V3 n) : sh(s), fr(n) {}
+};
+
+NV_D V3 mergeOne(const BdParams& P, const MergeCtx& c, uint32_t q) {
     uint4 A = __ldg(P.photons + (size_t)q * 2), B = __ldg(P.photons + (size_t)q * 2 + 1);
     float2 bxy = unpackHalf2(B.x), bz = unpackHalf2(B.y);
     float lightDvm = __uint_as_float(B.z), lightDvcm = __uint_as_float(B.w);
-    V3 photonPrevToPhotonL = fr.toLocal(-unpackOct(A.w));
-    float eyeRev = bsdfPdf(sh, photonPrevToPhotonL, toPrevL, 1.0f);
-    float lightRev = bsdfPdf(sh, -toPrevL, -photonPrevToPhotonL, 1.0f);
-    float wEye = eyeDvcm / P.etaVcm + eyeRev * eyeDvm;
-    float wLight = lightDvcm / P.etaVcm + lightRev * lightDvm;
-    float w = 1.0f / (1.0f + wEye + wLight);
-    V3 f = bsdfEval(sh, photonPrevToPhotonL, toPrevL, 1.0f);
-    return applyWeight(P, V3(bxy.x, bxy.y, bz.x) * f * currBeta * norm, w);
+    V3 wiPhoton = unpackOct(A.w);                          // photon -> its previous vertex, world space
+    V3 beta(bxy.x, bxy.y, bz.x);
+    if (c.diffuse) {
+        // Lambert: pdf_eval = max(cos, eps)/pi of the outgoing argument only, f_eval = albedo/pi (reflectors.cuh:10-18, :566, :644):
+        // the photon's direction enters through its cosine with the normal alone
+        float lightRev = fmaxf(dot(wiPhoton, c.fr.n), kEps) * (1.0f / kPi);      // pdf_eval(.., wo = -photonPrevToPhoton_local)
+        float wLight = lightDvcm * c.invEta + lightRev * lightDvm;
+        float w = __fdividef(1.0f, 1.0f + c.wEye + wLight);
+        return applyWeight(P, beta * c.scale * (c.sh.m.albedo * (1.0f / kPi)), w);
+    }
+    V3 photonPrevToPhotonL = c.fr.toLocal(-wiPhoton);
+    float eyeRev = bsdfPdf(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
+    float lightRev = bsdfPdf(c.sh, -c.toPrevL, -photonPrevToPhotonL, 1.0f);
+    float wEye = c.eyeDvcmOverEta + eyeRev * c.eyeDvm;
+    float wLight = lightDvcm * c.invEta + lightRev * lightDvm;
+    float w = __fdividef(1.0f, 1.0f + wEye + wLight);
+    V3 f = bsdfEval(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
+    return applyWeight(P, beta * f * c.scale, w);
 }
 
 __global__ void __launch_bounds__(kBdThreads) bdMerge(SceneView sc, BdState st, BdParams P, int* cnt) {
@@ -592,10 +610,13 @@ __global__ void __launch_bounds__(kBdThreads) bdMerge(SceneView sc, BdState st, 
         for (int r = base; r < end; ++r) {
             const float4* rp = reinterpret_cast<const float4*>(st.mergeQ + r);
             const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2q = __ldg(rp + 2), r3 = __ldg(rp + 3), r4 = __ldg(rp + 4);
-            const V3 eyeP(r0.x, r0.y, r0.z), toPrevL(r2q.x, r2q.y, r2q.z), currBeta(r3.x, r3.y, r3.z);
+            const V3 eyeP(r0.x, r0.y, r0.z);
             const int pix = __float_as_int(r0.w);
-            const Frame fr(V3(r1.x, r1.y, r1.z));
-            const Shading sh = resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y));
+            MergeCtx ctx(resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y)), V3(r1.x, r1.y, r1.z));
+            ctx.eyeP = eyeP; ctx.toPrevL = V3(r2q.x, r2q.y, r2q.z); ctx.scale = V3(r3.x, r3.y, r3.z) * norm;
+            ctx.invEta = 1.0f / P.etaVcm; ctx.eyeDvcmOverEta = r2q.w / P.etaVcm; ctx.eyeDvm = r3.w;
+            ctx.diffuse = ctx.sh.m.type == MAT_DIFFUSE;
+            ctx.wEye = ctx.eyeDvcmOverEta + cosinePdf(ctx.toPrevL) * ctx.eyeDvm;
             const int3 c0 = gridIndex(eyeP.x, eyeP.y, eyeP.z, P.grid);
             uint32_t cs = 0, cc = 0;
             if (lane < 27) {
@@ -612,19 +633,10 @@ __global__ void __launch_bounds__(kBdThreads) bdMerge(SceneView sc, BdState st, 
             nCand += (lane == 0) ? total : 0;
             int count = 0;
             V3 sum(0.0f);
-            for (uint32_t j0 = 0; j0 < total; j0 += 32) {
-                const uint32_t j = j0 + lane;
-                // cell of candidate j: the largest c with excl[c] <= j (binary search over the lanes' prefix values)
-                int c = 0;
-#pragma unroll
-                for (int stp = 16; stp >= 1; stp >>= 1) {
-                    int t = c + stp;
-                    uint32_t e = __shfl_sync(0xffffffffu, excl, t & 31);
-                    if (t < 27 && e <= j) c = t;
-                }
-                const uint32_t q = __shfl_sync(0xffffffffu, cs, c) + (j - __shfl_sync(0xffffffffu, excl, c));
+            // one sweep step: test candidate q (if live), compact the accepted ones, flush a full warp of them
+            auto sweep = [&](bool live, uint32_t q) {
                 bool accept = false;
-                if (j < total) {
+                if (live) {
                     uint4 A = __ldg(P.photons + (size_t)q * 2);
                     V3 diff = eyeP - V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
                     accept = dot(diff, diff) <= r2;
@@ -634,15 +646,37 @@ __global__ void __launch_bounds__(kBdThreads) bdMerge(SceneView sc, BdState st, 
                 count += __popc(m);
                 __syncwarp();
                 if (count >= 32) {
-                    sum += mergeOne(P, sh, fr, eyeP, toPrevL, currBeta, r2q.w, r3.w, norm, accBuf[warp][lane]);
+                    sum += mergeOne(P, ctx, accBuf[warp][lane]);
                     uint32_t carry = accBuf[warp][32 + lane];
                     __syncwarp();
                     accBuf[warp][lane] = carry;
                     count -= 32; nMerged += 32;
                     __syncwarp();
                 }
+            };
+            if (total >= 27u * 24u) {
+                // dense neighbourhood: cell by cell, lanes strided over the cell's photons (no per-candidate search)
+                for (int c = 0; c < 27; ++c) {
+                    const uint32_t ccount = __shfl_sync(0xffffffffu, cc, c);
+                    if (ccount == 0) continue;
+                    const uint32_t cstart = __shfl_sync(0xffffffffu, cs, c);
+                    for (uint32_t j0 = 0; j0 < ccount; j0 += 32) sweep(j0 + lane < ccount, cstart + j0 + lane);
+                }
+            } else {
+                // sparse: the 27 ranges concatenated; the cell of candidate j is the largest c with excl[c] <= j
+                for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+                    const uint32_t j = j0 + lane;
+                    int c = 0;
+#pragma unroll
+                    for (int stp = 16; stp >= 1; stp >>= 1) {
+                        int t = c + stp;
+                        uint32_t e = __shfl_sync(0xffffffffu, excl, t & 31);
+                        if (t < 27 && e <= j) c = t;
+                    }
+                    sweep(j < total, __shfl_sync(0xffffffffu, cs, c) + (j - __shfl_sync(0xffffffffu, excl, c)));
+                }
             }
-            if (lane < count) sum += mergeOne(P, sh, fr, eyeP, toPrevL, currBeta, r2q.w, r3.w, norm, accBuf[warp][lane]);
+            if (lane < count) sum += mergeOne(P, ctx, accBuf[warp][lane]);
             nMerged += count;
             __syncwarp();
 #pragma unroll
