@@ -146,17 +146,28 @@ struct TravStack {
     }
 };
 
-// Closest hit. tmaxIn mirrors the reference's max_t argument (999999 by default), skipTri its skipTri.
+// Closest hit as a resumable state machine, so that a persistent warp can refill finished lanes with new rays between
+// steps (trav_stream.cuh). tmaxIn mirrors the reference's max_t argument (999999 by default), skipTri its skipTri.
 template <bool COUNT>
-NV_D HitRec traceClosest(const Bvh8View& bvh, V3 o, V3 d, float tmaxIn, int skipTri, TravStack& st, TravCounters cnt) {
-    RaySetup r = setupRay(o, d);
-    HitRec best; best.tri = -1; best.t = 3.402823466e+38f; best.u = 0.f; best.v = 0.f; best.flags = 0;
-    float tlimit = tmaxIn;                 // strict: t < max_t and t < min_t
-    st.top = 0;
-    uint2 ngroup = make_uint2(0u, 0x80000000u);
-    uint2 tgroup = make_uint2(0u, 0u);
-    unsigned long long nv = 0, tt = 0;
-    while (true) {
+struct ClosestTrav {
+    RaySetup r;
+    HitRec best;
+    float tlimit;                          // strict: t < max_t and t < min_t
+    int skipTri;
+    uint2 ngroup, tgroup;
+    unsigned nv, tt;                       // node visits / triangle tests of this ray (COUNT builds)
+
+    NV_D void begin(V3 o, V3 d, float tmaxIn, int skip, TravStack& st) {
+        r = setupRay(o, d);
+        best.tri = -1; best.t = 3.402823466e+38f; best.u = 0.f; best.v = 0.f; best.flags = 0;
+        tlimit = tmaxIn; skipTri = skip;
+        st.top = 0;
+        ngroup = make_uint2(0u, 0x80000000u);
+        tgroup = make_uint2(0u, 0u);
+        nv = 0; tt = 0;
+    }
+    // One step: at most one node fetch + 8 box tests, then every triangle of the current leaf group. Returns true when done.
+    NV_D bool step(const Bvh8View& bvh, TravStack& st) {
         if (ngroup.y > 0x00ffffffu) {
             unsigned hits = ngroup.y;
             unsigned bit = 31u - __clz(hits);
@@ -193,11 +204,22 @@ NV_D HitRec traceClosest(const Bvh8View& bvh, V3 o, V3 d, float tmaxIn, int skip
         }
         if (ngroup.y <= 0x00ffffffu) {
             if (st.top > 0) ngroup = st.pop();
-            else break;
+            else return true;
         }
+        return false;
     }
-    if (COUNT) { atomicAdd(cnt.nodeVisits, nv); atomicAdd(cnt.triTests, tt); }
-    return best;
+    NV_D void flushCounters(TravCounters cnt) const {
+        if (COUNT) { atomicAdd(cnt.nodeVisits, (unsigned long long)nv); atomicAdd(cnt.triTests, (unsigned long long)tt); }
+    }
+};
+
+template <bool COUNT>
+NV_D HitRec traceClosest(const Bvh8View& bvh, V3 o, V3 d, float tmaxIn, int skipTri, TravStack& st, TravCounters cnt) {
+    ClosestTrav<COUNT> tr;
+    tr.begin(o, d, tmaxIn, skipTri, st);
+    while (!tr.step(bvh, st)) {}
+    tr.flushCounters(cnt);
+    return tr.best;
 }
 
 }  // namespace nv

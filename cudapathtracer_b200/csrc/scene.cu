@@ -2,6 +2,7 @@
 // (novum_trace_closest / novum_trace_shadow) that mirror BVHSceneIntersect / BVHShadowRay
 // (integratorUtilities.cuh:84, :188) on whole batches.
 #include "scene.h"
+#include "trav_stream.cuh"
 #include <cstdio>
 #include <cstring>
 #include <cmath>
@@ -79,27 +80,23 @@ int sceneFinalize(NovumScene* s) {
 // ---- ray-batch kernels -----------------------------------------------------------------------------
 constexpr int kTraceThreads = 128;
 
-// Persistent warps pull 32-ray packets from a global counter; stack lives in shared memory.
+// Persistent warps stream the batch through their lanes with per-lane refill (trav_stream.cuh); stack in shared memory.
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceThreads) closestBatchKernel(SceneView sc, const NovumRay* __restrict__ rays, int n,
                                                                      NovumHit* __restrict__ hits, int* __restrict__ counter,
                                                                      TravCounters cnt) {
     __shared__ uint2 stackMem[kSmemStack * kTraceThreads];
     TravStack st; st.init(stackMem + threadIdx.x, kTraceThreads);
-    const int lane = threadIdx.x & 31;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(counter, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
+    streamClosest<COUNT>(sc.bvh, st, n, counter, cnt,
+        [&](int i, V3& o, V3& d) {
             const float4* rp = reinterpret_cast<const float4*>(rays + i);
-            float4 o = __ldg(rp), d = __ldg(rp + 1);
-            HitRec h = traceClosest<COUNT>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, st, cnt);
+            float4 ro = __ldg(rp), rd = __ldg(rp + 1);
+            o = V3(ro.x, ro.y, ro.z); d = V3(rd.x, rd.y, rd.z);
+        },
+        [&](int i, const HitRec& h) {
             reinterpret_cast<float4*>(hits)[i] = make_float4(__int_as_float(h.tri), h.tri >= 0 ? h.t : 0.f, h.u, h.v);
-        }
-    }
+        },
+        [](bool) {});
 }
 
 template <bool COUNT>
@@ -108,20 +105,13 @@ __global__ void __launch_bounds__(kTraceThreads) shadowBatchKernel(SceneView sc,
                                                                     float4* __restrict__ out, int* __restrict__ counter, TravCounters cnt) {
     __shared__ uint2 stackMem[kSmemStack * kTraceThreads];
     TravStack st; st.init(stackMem + threadIdx.x, kTraceThreads);
-    const int lane = threadIdx.x & 31;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(counter, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
+    streamShadow<COUNT>(sc, st, n, counter, cnt,
+        [&](int i, V3& o, V3& d, float& mt, int& sk) {
             const float4* rp = reinterpret_cast<const float4*>(rays + i);
-            float4 o = __ldg(rp), d = __ldg(rp + 1);
-            V3 t = traceShadow<COUNT>(sc, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), maxT[i], skip ? skip[i] : -1, st, cnt);
-            out[i] = make_float4(t.x, t.y, t.z, 0.f);
-        }
-    }
+            float4 ro = __ldg(rp), rd = __ldg(rp + 1);
+            o = V3(ro.x, ro.y, ro.z); d = V3(rd.x, rd.y, rd.z); mt = maxT[i]; sk = skip ? skip[i] : -1;
+        },
+        [&](int i, V3 t) { out[i] = make_float4(t.x, t.y, t.z, 0.f); });
 }
 
 }  // namespace nv

@@ -69,17 +69,26 @@ NV_D Surface makeSurface(const SceneView& sc, const HitRec& h, V3 o, V3 d) {
 // attenuate by albedo*transmission*(1-Schlick) and let it continue; below 1 % it is black.
 // Traversal order is irrelevant to the result (every factor is <= 1), so the nearest-first ordering
 // the reference pays for is dropped and the first blocking hit ends the lane immediately.
+// Resumable like ClosestTrav so persistent warps can refill finished lanes (trav_stream.cuh).
 template <bool COUNT>
-NV_D V3 traceShadow(const SceneView& sc, V3 o, V3 d, float maxT, int skipTri, TravStack& st, TravCounters cnt) {
-    const Bvh8View& bvh = sc.bvh;
-    RaySetup r = setupRay(o, d);
-    V3 thr(1.0f);
-    st.top = 0;
-    uint2 ngroup = make_uint2(0u, 0x80000000u);
-    uint2 tgroup = make_uint2(0u, 0u);
-    unsigned long long nv = 0, tt = 0;
-    bool done = false;
-    while (!done) {
+struct ShadowTrav {
+    RaySetup r;
+    V3 thr;
+    float maxT;
+    int skipTri;
+    uint2 ngroup, tgroup;
+    unsigned nv, tt;
+
+    NV_D void begin(V3 o, V3 d, float maxT_, int skip, TravStack& st) {
+        r = setupRay(o, d);
+        thr = V3(1.0f); maxT = maxT_; skipTri = skip;
+        st.top = 0;
+        ngroup = make_uint2(0u, 0x80000000u);
+        tgroup = make_uint2(0u, 0u);
+        nv = 0; tt = 0;
+    }
+    NV_D bool step(const SceneView& sc, TravStack& st) {
+        const Bvh8View& bvh = sc.bvh;
         if (ngroup.y > 0x00ffffffu) {
             unsigned hits = ngroup.y;
             unsigned bit = 31u - __clz(hits);
@@ -117,19 +126,30 @@ NV_D V3 traceShadow(const SceneView& sc, V3 o, V3 d, float maxT, int skipTri, Tr
                     float cosT = fabsf(dot(r.d, normalize(n)));
                     float F = schlick(cosT, 1.0f, m.ior);
                     thr *= m.albedo * (m.transmission * (1.0f - F));
-                    if (maxComp(thr) < 0.01f) { thr = V3(0.0f); done = true; break; }
+                    if (maxComp(thr) < 0.01f) { thr = V3(0.0f); return true; }
                 } else {
-                    thr = V3(0.0f); done = true; break;
+                    thr = V3(0.0f); return true;
                 }
             }
         }
-        if (!done && ngroup.y <= 0x00ffffffu) {
+        if (ngroup.y <= 0x00ffffffu) {
             if (st.top > 0) ngroup = st.pop();
-            else break;
+            else return true;
         }
+        return false;
     }
-    if (COUNT) { atomicAdd(cnt.nodeVisits, nv); atomicAdd(cnt.triTests, tt); }
-    return thr;
+    NV_D void flushCounters(TravCounters cnt) const {
+        if (COUNT) { atomicAdd(cnt.nodeVisits, (unsigned long long)nv); atomicAdd(cnt.triTests, (unsigned long long)tt); }
+    }
+};
+
+template <bool COUNT>
+NV_D V3 traceShadow(const SceneView& sc, V3 o, V3 d, float maxT, int skipTri, TravStack& st, TravCounters cnt) {
+    ShadowTrav<COUNT> tr;
+    tr.begin(o, d, maxT, skipTri, st);
+    while (!tr.step(sc, st)) {}
+    tr.flushCounters(cnt);
+    return tr.thr;
 }
 
 }  // namespace nv

@@ -204,30 +204,24 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStart(SceneView sc, BdState
     if (active) st.queue[0][pos] = l;
 }
 
-// closest hit for every queued path of this depth
+// closest hit for every queued path of this depth (rays streamed through the lanes with per-lane refill, trav_stream.cuh)
 template <bool COUNT>
 __global__ void __launch_bounds__(kBdThreads) bdExtend(SceneView sc, BdState st, const int* __restrict__ queue, int* cnt, TravCounters tc) {
     __shared__ uint2 stackMem[kSmemStack * kBdThreads];
     TravStack ts; ts.init(stackMem + threadIdx.x, kBdThreads);
     const int lane = bdLane();
     const int n = cnt[BC_QUEUE];
-    unsigned long long traced = 0;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_EXTEND], 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
+    unsigned traced = streamClosest<COUNT>(sc.bvh, ts, n, &cnt[BC_FETCH_EXTEND], tc,
+        [&](int i, V3& o, V3& d) {
             int l = __ldg(queue + i);
-            float4 o = st.rayO[l], d = st.rayD[l];
-            HitRec h = traceClosest<COUNT>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, tc);
-            st.hit[l] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
-            ++traced;
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
-    if (lane == 0 && traced) atomicAdd(&st.stats[0], traced);
+            float4 ro = st.rayO[l], rd = st.rayD[l];
+            o = V3(ro.x, ro.y, ro.z); d = V3(rd.x, rd.y, rd.z);
+        },
+        [&](int i, const HitRec& h) { st.hit[__ldg(queue + i)] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v); },
+        [](bool) {});
+    unsigned long long tr64 = traced;
+    for (int o = 16; o > 0; o >>= 1) tr64 += __shfl_xor_sync(0xffffffffu, tr64, o);
+    if (lane == 0 && tr64) atomicAdd(&st.stats[0], tr64);
 }
 
 // vertex processing shared by both walks: forward area pdf, BSDF sample, reverse pdf, d_vcm / d_vc / d_vm recurrences
@@ -340,28 +334,25 @@ __global__ void __launch_bounds__(kBdThreads) bdResolve(SceneView sc, BdState st
     const int lane = bdLane();
     const int n = min(cnt[BC_SHADOW], st.shadowCap);
     TravCounters nocnt{nullptr, nullptr};
-    unsigned long long traced = 0;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_RESOLVE], 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
+    unsigned traced = streamShadow<false>(sc, ts, n, &cnt[BC_FETCH_RESOLVE], nocnt,
+        [&](int i, V3& o, V3& d, float& maxT, int& skip) {
             const float4* rp = reinterpret_cast<const float4*>(st.shadowQ + i);
-            float4 a = rp[0], b = rp[1], c = rp[2];
-            V3 thr = traceShadow<false>(sc, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, __float_as_int(c.w), ts, nocnt);
-            ++traced;
+            float4 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
+            o = V3(a.x, a.y, a.z); d = V3(b.x, b.y, b.z); maxT = a.w; skip = __float_as_int(c.w);
+        },
+        [&](int i, V3 thr) {
+            const float4* rp = reinterpret_cast<const float4*>(st.shadowQ + i);
+            float4 b = __ldg(rp + 1), c = __ldg(rp + 2);
             unsigned pf = __float_as_uint(b.w);
             if (lengthSq(thr) > ((pf & SR_NEE) ? 0.0f : kEps)) {       // :668 (NEE: > 0) vs :1336, :2304, :2599 (> EPSILON)
                 V3 v = V3(c.x, c.y, c.z) * thr;
                 if (pf & SR_CLAMP) v = fireflyClamp(v);
                 atomicAdd(&colors[pf & SR_PIXMASK], make_float4(v.x, v.y, v.z, 0.f));
             }
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
-    if (lane == 0 && traced) atomicAdd(&st.stats[1], traced);
+        });
+    unsigned long long tr64 = traced;
+    for (int o = 16; o > 0; o >>= 1) tr64 += __shfl_xor_sync(0xffffffffu, tr64, o);
+    if (lane == 0 && tr64) atomicAdd(&st.stats[1], tr64);
 }
 
 // ---- eye pass ---------------------------------------------------------------------------------------------------------------

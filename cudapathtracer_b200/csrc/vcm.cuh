@@ -21,6 +21,7 @@
 #pragma once
 #include <cuda_fp16.h>
 #include "scene_dev.cuh"
+#include "trav_stream.cuh"
 #include "camera.cuh"
 #include "hashgrid.cuh"
 

@@ -54,40 +54,58 @@ __global__ void wfInit(WfState st, int n) {
 }
 
 // ---- extend: closest hit for every queued path, then bin the path by the material class it hit ------------
+// Rays stream through the warp's lanes with per-lane refill (trav_stream.cuh). Finished paths are staged in a per-warp
+// shared buffer and binned 32 at a time with one ballot-aggregated atomic per class present, as before.
 template <bool COUNT>
-__global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st, const int* __restrict__ queue, TravCounters nocnt) {
+__global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st, const int* __restrict__ queue, TravCounters cnt) {
     __shared__ uint2 stackMem[kSmemStack * kWfThreads];
+    __shared__ int2 stage[kWfThreads / 32][64];
+    __shared__ int stageCnt[kWfThreads / 32];
     TravStack ts; ts.init(stackMem + threadIdx.x, kWfThreads);
-    const int lane = laneId();
+    const int lane = laneId(), warp = threadIdx.x >> 5;
+    if (lane == 0) stageCnt[warp] = 0;
+    __syncwarp();
     const int n = st.counters[C_EXTEND_COUNT];
-    unsigned long long traced = 0;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&st.counters[C_FETCH_EXTEND], 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        bool valid = i < n;
-        int slot = valid ? __ldg(queue + i) : 0;
-        int cls = -1;
-        if (valid) {
-            float4 o = st.rayO[slot], d = st.rayD[slot];
-            HitRec h = traceClosest<COUNT>(sc.bvh, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), 999999.0f, -1, ts, nocnt);
-            ++traced;
-            st.hit[slot] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
-            st.hitFlags[slot] = h.flags;
-            cls = h.tri < 0 ? CLS_REGEN : classOfMaterial(sc.mats, h.flags & 0xffff);
-        }
-        // bin by class: one aggregated atomic per class present in the warp
+    auto binStaged = [&](int first, int count) {           // whole warp converged
+        int2 e = lane < count ? stage[warp][first + lane] : make_int2(0, -1);
 #pragma unroll
         for (int c = 0; c < NUM_CLS; ++c) {
-            int pos = warpAppend(&st.counters[C_CLASS_COUNT + c], cls == c);
-            if (cls == c) st.classQ[c * st.capacity + pos] = slot;
+            int pos = warpAppend(&st.counters[C_CLASS_COUNT + c], e.y == c);
+            if (e.y == c) st.classQ[c * st.capacity + pos] = e.x;
         }
-    }
+    };
+    unsigned traced = streamClosest<COUNT>(sc.bvh, ts, n, &st.counters[C_FETCH_EXTEND], cnt,
+        [&](int i, V3& o, V3& d) {
+            int slot = __ldg(queue + i);
+            float4 ro = st.rayO[slot], rd = st.rayD[slot];
+            o = V3(ro.x, ro.y, ro.z); d = V3(rd.x, rd.y, rd.z);
+        },
+        [&](int i, const HitRec& h) {
+            int slot = __ldg(queue + i);
+            st.hit[slot] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
+            st.hitFlags[slot] = h.flags;
+            int cls = h.tri < 0 ? CLS_REGEN : classOfMaterial(sc.mats, h.flags & 0xffff);
+            stage[warp][atomicAdd(&stageCnt[warp], 1)] = make_int2(slot, cls);
+        },
+        [&](bool final) {
+            __syncwarp();
+            int c = stageCnt[warp];
+            __syncwarp();
+            if (c >= 32) {
+                binStaged(0, 32);
+                int2 carry = lane < c - 32 ? stage[warp][32 + lane] : make_int2(0, -1);
+                __syncwarp();
+                if (lane < c - 32) stage[warp][lane] = carry;
+                c -= 32;
+                if (lane == 0) stageCnt[warp] = c;
+                __syncwarp();
+            }
+            if (final && c > 0) { binStaged(0, c); if (lane == 0) stageCnt[warp] = 0; __syncwarp(); }
+        });
     // one atomic per warp for the ray counter
-    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
-    if (lane == 0 && traced) atomicAdd(&st.rayCounters[0], traced);
+    unsigned long long tr64 = traced;
+    for (int o = 16; o > 0; o >>= 1) tr64 += __shfl_xor_sync(0xffffffffu, tr64, o);
+    if (lane == 0 && tr64) atomicAdd(&st.rayCounters[0], tr64);
 }
 
 // ---- shadow: any-hit for every queued NEE connection; unoccluded ones add their contribution --------------
@@ -97,26 +115,22 @@ __global__ void __launch_bounds__(kWfThreads) wfShadow(SceneView sc, WfState st,
     const int lane = laneId();
     const int n = st.counters[C_SHADOW_COUNT];
     TravCounters nocnt{nullptr, nullptr};
-    unsigned long long traced = 0;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&st.counters[C_FETCH_SHADOW], 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
+    unsigned traced = streamShadow<false>(sc, ts, n, &st.counters[C_FETCH_SHADOW], nocnt,
+        [&](int i, V3& o, V3& d, float& maxT, int& skip) {
             const float4* rp = reinterpret_cast<const float4*>(st.shadowQ + i);
-            float4 a = rp[0], b = rp[1], c = rp[2];
-            V3 thr = traceShadow<false>(sc, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, -1, ts, nocnt);
-            ++traced;
+            float4 a = __ldg(rp), b = __ldg(rp + 1);
+            o = V3(a.x, a.y, a.z); d = V3(b.x, b.y, b.z); maxT = a.w; skip = -1;
+        },
+        [&](int i, V3 thr) {
             if (lengthSq(thr) > 0.0f) {     // deviceCode.cu:131
-                int pix = __float_as_int(b.w);
-                atomicAdd(&colors[pix], make_float4(c.x * thr.x, c.y * thr.y, c.z * thr.z, 0.f));
+                const float4* rp = reinterpret_cast<const float4*>(st.shadowQ + i);
+                float4 b = __ldg(rp + 1), c = __ldg(rp + 2);
+                atomicAdd(&colors[__float_as_int(b.w)], make_float4(c.x * thr.x, c.y * thr.y, c.z * thr.z, 0.f));
             }
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
-    if (lane == 0 && traced) atomicAdd(&st.rayCounters[1], traced);
+        });
+    unsigned long long tr64 = traced;
+    for (int o = 16; o > 0; o >>= 1) tr64 += __shfl_xor_sync(0xffffffffu, tr64, o);
+    if (lane == 0 && tr64) atomicAdd(&st.rayCounters[1], tr64);
 }
 
 }  // namespace nv

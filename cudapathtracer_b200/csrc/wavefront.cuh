@@ -8,6 +8,7 @@
 // path counter, so the pool stays full until the last samples drain.
 #pragma once
 #include "scene_dev.cuh"
+#include "trav_stream.cuh"
 #include "camera.cuh"
 
 namespace nv {
