@@ -7,8 +7,8 @@ pass index (`--sharding striped`, default) or — bidirectional integrators only
 all-gather of the photon slabs (`--sharding tiles`); the full-frame accumulators are summed with one NCCL reduce.
 
 Workloads = BASELINE.json configs on the generated stand-in scenes (the reference's OBJ files are LFS pointers):
+  rainbow_vcm  configs[4]  rainbow dragon, VCM, 3840x2160         (DEFAULT: the config BASELINE.json's metric is quoted on)
   dragon_nee   configs[1]  glass dragon stand-in (~871k tris) 1920x1080, NEE+MIS          (north_star's >=5x target)
-  rainbow_vcm  configs[4]  rainbow dragon, VCM, 3840x2160                                 (the metric's headline config)
   water_bdpt   configs[2]  water caustic, BDPT, 1920x1080
   water_sppm   configs[3]  water caustic, SPPM, 1024x1024 light paths (~1M photons / iteration)
   cornell      configs[0]  Cornell box 512x512 NEE+MIS
@@ -190,7 +190,7 @@ def run_ours(args):
         clocks.start()
     wall0 = time.time()
     dev_ms, rays, paths, launches, stage_ms, closest, photons = 0.0, 0, 0, 0, [0.0] * 4, 0, 0
-    merge_cand, merge_acc = 0, 0
+    merge_cand, merge_acc, merge_q = 0, 0, 0
     before = tiler.session.stats() if tiles else None       # the session's counters are cumulative
     for i in range(args.steps):
         st, ms = step(args.warmup + i, profile=0 if tiles else 1)
@@ -198,7 +198,7 @@ def run_ours(args):
         photons = st.photons
         if not tiles:
             rays += st.closestRays + st.shadowRays; closest += st.closestRays; paths += st.paths; launches += st.kernelLaunches
-            merge_cand += st.bvhNodeVisits; merge_acc += st.triTests
+            merge_cand += st.mergeCandidates; merge_acc += st.mergeAccepted; merge_q += st.mergeQueries
             for k in range(4):
                 stage_ms[k] += st.stageMs[k]
     if tiles:
@@ -250,21 +250,35 @@ def run_ours(args):
     if dist is not None:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.SUM)
 
-    # ---- roofline of the dominant kernel class: BVH8 closest-hit traversal (wfExtend / bdExtend) ----
+    # ---- roofline of the dominant kernel class (by live CUDA-event stage time) ----
+    # closest-hit traversal (wfExtend / bdExtend): per ray 32 B ray + 16 B hit + 80 B x nodes + 48 B x triangles;
+    # photon merge (bdMergeLambert / bdMerge): per query 80 B record + 27 x 8 B cell ranges + 16 B pixel RMW, 16 B per photon
+    # scanned (position word) + 16 B per photon inside the radius (second word) — SURVEY 8d's "27 x 8 B + record x scanned".
     roof = None
     if not tiles:
         st, _ = step(10_000, profile=3)       # one counted step (slower kernel, not timed): nodes / triangles per ray
         vn = st.bvhNodeVisits / max(1, st.closestRays); vt = st.triTests / max(1, st.closestRays)
-        bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt            # ray in + hit out + 80 B nodes + 48 B triangles
+        bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt
         peak, peak_src = peaks()
-        achieved = (closest * bytes_per_ray) / (stage_ms[0] * 1e-3) / 1e9 if stage_ms[0] > 0 else 0.0
-        names = ({"extend": 0, "step": 1, "resolve": 2, "grid+other": 3} if bidir else {"extend": 0, "shade": 1, "shadow": 2, "other": 3})
-        roof = {"bound": "hbm", "kernel": "bdExtend (BVH8 closest hit)" if bidir else "wfExtend (BVH8 closest hit)", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
-                "closest_rays_per_s": closest / (stage_ms[0] * 1e-3) if stage_ms[0] > 0 else None,
-                "extend_ms_share": stage_ms[0] / dev_ms if dev_ms else None,
+        names = ({"extend": 0, "step+grid": 1, "resolve": 2, "merge": 3} if bidir else {"extend": 0, "shade": 1, "shadow": 2, "other": 3})
+        ext = {"kernel": "bdExtend (BVH8 closest hit)" if bidir else "wfExtend (BVH8 closest hit)",
+               "achieved": (closest * bytes_per_ray) / (stage_ms[0] * 1e-3) / 1e9 if stage_ms[0] > 0 else 0.0,
+               "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
+               "closest_rays_per_s": closest / (stage_ms[0] * 1e-3) if stage_ms[0] > 0 else None,
+               "ms_share": stage_ms[0] / dev_ms if dev_ms else None}
+        dom = ext
+        if bidir and stage_ms[3] > stage_ms[0] and merge_q > 0:
+            mbytes = merge_q * (80 + 27 * 8 + 16) + 16 * merge_cand + 16 * merge_acc
+            dom = {"kernel": "bdMergeLambert + bdMerge (photon gather over 27 hash-grid cells)",
+                   "achieved": mbytes / (stage_ms[3] * 1e-3) / 1e9, "bytes_per_query": mbytes / merge_q,
+                   "photons_scanned_per_query": merge_cand / merge_q, "photons_merged_per_query": merge_acc / merge_q,
+                   "photons_scanned_per_s": merge_cand / (stage_ms[3] * 1e-3), "ms_share": stage_ms[3] / dev_ms if dev_ms else None,
+                   "note": "every photon record is re-read by ~10^3 queries, so these bytes are served by L1/L2, not HBM: achieved/peak can "
+                           "exceed 1; the kernel is instruction-issue bound (profiles/)"}
+        roof = {"bound": "hbm", **dom, "peak": peak, "unit": "GB/s", "frac": dom["achieved"] / peak, "traffic": None, "peak_source": peak_src,
                 "stage_ms": {k: stage_ms[v] for k, v in names.items()}}
+        if dom is not ext:
+            roof["extend"] = {**ext, "frac": ext["achieved"] / peak}
 
     if rank == 0:
         line = {
@@ -290,9 +304,10 @@ def run_ours(args):
             line["roofline"] = roof
         if bidir:
             line["photons_per_iteration"] = int(photons) if tiles else int(photons // max(1, S))
-            line["merge"] = {"candidates_per_step": merge_cand // max(1, args.steps), "merged_per_step": merge_acc // max(1, args.steps)}
+            line["merge"] = {"queries_per_step": merge_q // max(1, args.steps), "candidates_per_step": merge_cand // max(1, args.steps),
+                             "merged_per_step": merge_acc // max(1, args.steps)}
         if tiles:
-            line["exchange_bytes_per_iteration_per_gpu"] = int(tiler.slabs.numel())
+            line["exchange_bytes_per_iteration_per_gpu"] = int(tiler.last_exchange_bytes)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_oracle_baseline(sdir, args.workload)
         if host_img is not None:
@@ -366,10 +381,10 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="dragon_nee", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS))
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
     ap.add_argument("--sharding", default="striped", choices=["striped", "tiles"])
     ap.add_argument("--detail", type=int, default=100)

@@ -64,7 +64,8 @@ class Shard(C.Structure):
 class RenderStats(C.Structure):
     _fields_ = [("closestRays", C.c_uint64), ("shadowRays", C.c_uint64), ("paths", C.c_uint64), ("photons", C.c_uint64),
                 ("lightVertices", C.c_uint64), ("kernelLaunches", C.c_uint64), ("deviceMs", C.c_float), ("_pad", C.c_float),
-                ("bvhNodeVisits", C.c_uint64), ("triTests", C.c_uint64), ("stageMs", C.c_float * 4), ("stageLaunches", C.c_uint64 * 4)]
+                ("bvhNodeVisits", C.c_uint64), ("triTests", C.c_uint64), ("stageMs", C.c_float * 4), ("stageLaunches", C.c_uint64 * 4),
+                ("mergeQueries", C.c_uint64), ("mergeCandidates", C.c_uint64), ("mergeAccepted", C.c_uint64)]
 
 
 # numpy dtypes with the reference's struct layouts (objects.cuh Triangle 80 B, Material 176 B)

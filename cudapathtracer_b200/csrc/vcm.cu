@@ -38,6 +38,7 @@ __device__ __forceinline__ int bdAggAppend(int* counter) {
     return base + __popc(m & ((1u << bdLane()) - 1u));
 }
 
+NV_D float rcpApprox(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 NV_D uint32_t packHalf2(float a, float b) { __half2 h = __halves2half2(__float2half(a), __float2half(b)); return *reinterpret_cast<uint32_t*>(&h); }
 NV_D float2 unpackHalf2(uint32_t u) { __half2 h = *reinterpret_cast<__half2*>(&u); return __half22float2(h); }
 
@@ -379,7 +380,7 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStart(BdState st, BdParams P)
 }
 
 __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st, BdParams P, int step, int numSteps,
-                                                       const int* __restrict__ queue, int* __restrict__ nextQueue) {
+                                                       const int* __restrict__ queue, int* __restrict__ nextQueue, MergeQueue mq) {
     const int lane = bdLane();
     int* cnt = st.counters + step * BC_STRIDE;
     int* nextCnt = st.counters + (step + 1) * BC_STRIDE;
@@ -517,8 +518,10 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                         if (vcm && P.doMerge) {
                           if (P.mergeRadius > 0.0f) {
                             // deferred: the photon gather runs warp-cooperatively in bdMerge on this record
-                            int pos = bdAggAppend(&cnt[BC_MERGE]);
-                            float4* rec = reinterpret_cast<float4*>(st.mergeQ + pos);
+                            // Lambert vertices fill mergeQ from the front (bdMergeLambert), every other material from the back (bdMerge)
+                            const bool lambert = o.sh.m.type == MAT_DIFFUSE && !P.paintWeight;
+                            int pos = lambert ? bdAggAppend(&mq.cnt[BC_MERGE]) : mq.cap - 1 - bdAggAppend(&mq.cnt[BC_MERGE_GEN]);
+                            float4* rec = reinterpret_cast<float4*>(mq.recs + pos);
                             rec[0] = make_float4(s.p.x, s.p.y, s.p.z, __int_as_float(pix));
                             rec[1] = make_float4(s.n.x, s.n.y, s.n.z, __int_as_float(s.mat));
                             rec[2] = make_float4(toPrevL.x, toPrevL.y, toPrevL.z, o.d_vcm);
@@ -545,140 +548,258 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
 
 // ---- merging (deviceCode.cu:2968-3048), one warp per eye vertex ----------------------------------------------------------------
 // Lanes 0..26 look up the 27 neighbour cells (same z, y, x order and the same per-cell lookups as the reference, so a table
-// slot shared by two neighbours is visited twice there and here); the cells' photon ranges are concatenated with a warp scan
-// and swept 32 candidates at a time (coalesced reads of the cell-ordered records). Candidates inside the radius are compacted
-// into a per-warp buffer so that the expensive part — two reverse pdfs, the BSDF value, the VM MIS weight — always runs on
-// full warps. The BSDF dispatch is uniform across the warp (one eye vertex = one material).
-constexpr int kMergeWarps = kBdThreads / 32;
+// slot shared by two neighbours is visited twice there and here). Photon records are read in the merge-ready form written by
+// bdReorderPhotons. Two kernels, because the eye vertex's material decides how much work one accepted photon is:
+//   bdMergeLambert  Lambert vertices (front of mergeQ): the reverse pdfs and the BSDF value reduce to one cosine, so the
+//                   accept path is ~20 instructions and is run in place, predicated, with no compaction;
+//   bdMerge         everything else (back of mergeQ): accepted candidates are compacted into a per-warp buffer so that the
+//                   expensive part - two reverse pdfs, the BSDF value, the VM MIS weight - always runs on full warps.
+constexpr int kMergeThreads = 128;
+constexpr int kMergeWarps = kMergeThreads / 32;
 
-// per-eye-vertex constants of the merge, hoisted out of the photon loop
+struct MergeCells { uint32_t cs, cc; };     // per lane (< 27): first photon and photon count of its neighbour cell
+
+NV_D MergeCells mergeCells(const BdParams& P, V3 eyeP, int lane) {
+    const int3 c0 = gridIndex(eyeP.x, eyeP.y, eyeP.z, P.grid);
+    MergeCells m{0u, 0u};
+    if (lane < 27) {
+        int dz = lane / 9 - 1, dy = (lane / 3) % 3 - 1, dx = lane % 3 - 1;
+        unsigned hsh = hashCell(make_int3(c0.x + dx, c0.y + dy, c0.z + dz), P.grid.tableSize);
+        uint32_t s0 = __ldg(P.cellStart + hsh);
+        if (s0 != 0xFFFFFFFFu) { m.cs = s0; m.cc = __ldg(P.cellEnd + hsh) - s0; }
+    }
+    return m;
+}
+
+NV_D void mergeSplat(const BdParams& P, int pix, V3 sum, int lane) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum.x += __shfl_xor_sync(0xffffffffu, sum.x, o); sum.y += __shfl_xor_sync(0xffffffffu, sum.y, o); sum.z += __shfl_xor_sync(0xffffffffu, sum.z, o);
+    }
+    if (lane == 0 && (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) && isfinite(sum.x) && isfinite(sum.y) && isfinite(sum.z))
+        atomicAdd(&P.colors[pix], make_float4(sum.x, sum.y, sum.z, 0.f));
+}
+
+// Lambert eye vertex: pdf_eval = max(cos, eps)/pi of the outgoing argument only, f_eval = albedo/pi (reflectors.cuh:10-18, :566,
+// :644), so per photon   w = 1 / (1 + wEye + d_vcm/eta + max(cos(wi, n), eps)/pi * d_vm)   and the vertex's contribution is
+// (currBeta * albedo/pi / (pi r^2 w h)) * sum(beta_photon * w).
+//
+// One warp gathers G consecutive records TOGETHER: the union of their neighbour cells is swept once, every lane loads one
+// candidate photon (two coalesced 16 B words) and tests it against all G vertices, whose constants live in registers. With
+// G = 4 on the primary-hit queue (consecutive records = adjacent pixels, whose 27-cell neighbourhoods nearly coincide) each
+// photon load and its address arithmetic are shared by four (vertex, photon) pairs, which takes the kernel off the L1 / L2
+// bandwidth limit the one-vertex-per-warp form sits on. A photon within r of a vertex always lies in one of that vertex's own
+// 27 cells, so testing a vertex against the cells of its neighbours adds only rejected candidates; table slots are de-duplicated
+// across the union (the reference visits a slot twice when two of a vertex's neighbour cells collide in the table, p ~ 1e-6).
+template <bool MIS, int G>
+__global__ void __launch_bounds__(kMergeThreads) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
+    int* cnt = mq.cnt;
+    const int lane = bdLane();
+    const int n = min(cnt[BC_MERGE], mq.cap);
+    const float r2 = P.mergeRadius * P.mergeRadius;
+    const float norm = 1.0f / (kPi * r2 * (float)P.w * (float)P.h);
+    const float invEta = 1.0f / P.etaVcm;
+    const PhotonSoA ph = P.photons;
+    const unsigned ltMask = (1u << lane) - 1u;
+    unsigned long long nCand = 0;
+    unsigned nAcc = 0;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], G);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        V3 eyeP[G], nPi[G], sum[G];
+        float C[G];
+        uint32_t cs[G], cc[G], key[G];
+        int recIdx[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            // a short last group repeats its last record (its result is dropped below)
+            const int r = min(base + g, n - 1);
+            recIdx[g] = mq.order ? __ldg(mq.order + r) : r;
+            const float4* rp = reinterpret_cast<const float4*>(mq.recs + recIdx[g]);
+            const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2q = __ldg(rp + 2), r3 = __ldg(rp + 3);
+            eyeP[g] = V3(r0.x, r0.y, r0.z);
+            nPi[g] = V3(r1.x, r1.y, r1.z) * (1.0f / kPi);                                        // cos/pi = dot(wi, n/pi)
+            C[g] = 1.0f + r2q.w * invEta + cosinePdf(V3(r2q.x, r2q.y, r2q.z)) * r3.w;           // 1 + d_vcm/eta + eyeRev * d_vm
+            sum[g] = V3(0.0f);
+            const MergeCells mc = mergeCells(P, eyeP[g], lane);
+            cs[g] = mc.cs; cc[g] = mc.cc;
+            // drop table slots already listed: by an earlier lane of this vertex, or by an earlier vertex of the group
+            // (key = first photon of the slot; empty slots get keys no photon index can take)
+            key[g] = mc.cc ? mc.cs : 0xFFFFFF00u + (unsigned)lane;
+            if (G > 1) {
+                const unsigned same = __match_any_sync(0xffffffffu, key[g]);
+                if (same & ltMask) cc[g] = 0u;
+#pragma unroll
+                for (int k = 0; k < g; ++k) {
+                    if (__all_sync(0xffffffffu, key[k] == key[g])) { cc[g] = 0u; continue; }     // same centre cell: identical lists
+                    for (int j = 0; j < 27; ++j) if (__shfl_sync(0xffffffffu, key[k], j) == key[g]) cc[g] = 0u;
+                }
+            }
+            if (base + g >= n) cc[g] = 0u;
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            nCand += (unsigned long long)cc[g] * (unsigned)min(G, n - base);
+            unsigned nonEmpty = __ballot_sync(0xffffffffu, cc[g] != 0u);
+            while (nonEmpty) {
+                const int c = __ffs(nonEmpty) - 1;
+                nonEmpty &= nonEmpty - 1;
+                const uint32_t cend = __shfl_sync(0xffffffffu, cs[g] + cc[g], c);
+                uint32_t q = __shfl_sync(0xffffffffu, cs[g], c) + lane;
+                // lanes strided over the cell's photons; the next trip's two words are requested before this trip's tests
+                float4 A = make_float4(0.f, 0.f, 0.f, 0.f); uint4 B = make_uint4(0u, 0u, 0u, 0u);
+                if (q < cend) { A = __ldg(ph.a + q); B = __ldg(ph.b + q); }
+                for (; q < cend; q += 32) {
+                    const float4 Ac = A; const uint4 Bc = B;
+                    if (q + 32 < cend) { A = __ldg(ph.a + q + 32); B = __ldg(ph.b + q + 32); }
+                    const float2 wxy = unpackHalf2(__float_as_uint(Ac.w)), wzb = unpackHalf2(Bc.x), byz = unpackHalf2(Bc.y);
+#pragma unroll
+                    for (int k = 0; k < G; ++k) {
+                        const float dx = eyeP[k].x - Ac.x, dy = eyeP[k].y - Ac.y, dz = eyeP[k].z - Ac.z;
+                        if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= r2) {
+                            float w = 1.0f;
+                            if (MIS) {
+                                const float rev = fmaxf(fmaf(wxy.x, nPi[k].x, fmaf(wxy.y, nPi[k].y, wzb.x * nPi[k].z)), kEps * (1.0f / kPi));
+                                w = rcpApprox(fmaf(rev, __uint_as_float(Bc.z), C[k] + __uint_as_float(Bc.w)));      // the argument is >= 1
+                            }
+                            sum[k].x = fmaf(wzb.y, w, sum[k].x); sum[k].y = fmaf(byz.x, w, sum[k].y); sum[k].z = fmaf(byz.y, w, sum[k].z);
+                            ++nAcc;
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            if (base + g >= n) break;
+            const float4* rp = reinterpret_cast<const float4*>(mq.recs + recIdx[g]);
+            const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r3 = __ldg(rp + 3), r4 = __ldg(rp + 4);
+            const Shading sh = resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y));
+            const V3 K = V3(r3.x, r3.y, r3.z) * sh.m.albedo * (norm * (1.0f / kPi));
+            mergeSplat(P, __float_as_int(r0.w), sum[g] * K, lane);
+        }
+    }
+    unsigned long long acc = nAcc;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, o); nCand += __shfl_xor_sync(0xffffffffu, nCand, o); }
+    if (lane == 0) { if (acc) atomicAdd(&st.stats[4], acc); if (nCand) atomicAdd(&st.stats[5], nCand); }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0) atomicAdd(&st.stats[6], (unsigned long long)n);
+}
+
+// per-eye-vertex constants of the general merge, hoisted out of the photon loop
 struct MergeCtx {
-    Shading sh; Frame fr; V3 eyeP, toPrevL, scale;     // scale = currBeta * 1/(pi r^2 w h)
-    float wEye;        // d_vcm / eta + eyeRev * d_vm for a diffuse surface (eyeRev does not depend on the photon there)
-    float eyeDvcmOverEta, eyeDvm, invEta;
-    bool diffuse;
+    Shading sh; Frame fr; V3 toPrevL, scale;     // scale = currBeta * 1/(pi r^2 w h)
+    float eyeDvcmOverEta, eyeDvm;
     NV_D MergeCtx(const Shading& s, V3 n) : sh(s), fr(n) {}
 };
 
 NV_D V3 mergeOne(const BdParams& P, const MergeCtx& c, uint32_t q) {
-    uint4 A = __ldg(P.photons + (size_t)q * 2), B = __ldg(P.photons + (size_t)q * 2 + 1);
-    float2 bxy = unpackHalf2(B.x), bz = unpackHalf2(B.y);
-    float lightDvm = __uint_as_float(B.z), lightDvcm = __uint_as_float(B.w);
-    V3 wiPhoton = unpackOct(A.w);                          // photon -> its previous vertex, world space
-    V3 beta(bxy.x, bxy.y, bz.x);
-    if (c.diffuse) {
-        // Lambert: pdf_eval = max(cos, eps)/pi of the outgoing argument only, f_eval = albedo/pi (reflectors.cuh:10-18, :566, :644):
-        // the photon's direction enters through its cosine with the normal alone
-        float lightRev = fmaxf(dot(wiPhoton, c.fr.n), kEps) * (1.0f / kPi);      // pdf_eval(.., wo = -photonPrevToPhoton_local)
-        float wLight = lightDvcm * c.invEta + lightRev * lightDvm;
-        float w = __fdividef(1.0f, 1.0f + c.wEye + wLight);
-        return applyWeight(P, beta * c.scale * (c.sh.m.albedo * (1.0f / kPi)), w);
-    }
+    const uint4 B = __ldg(P.photons.b + q);
+    const float2 wxy = unpackHalf2(__float_as_uint(__ldg(&P.photons.a[q].w))), wzb = unpackHalf2(B.x), byz = unpackHalf2(B.y);
+    const float lightDvm = __uint_as_float(B.z), lightDvcmOverEta = __uint_as_float(B.w);
+    const V3 wiPhoton(wxy.x, wxy.y, wzb.x);                 // photon -> its previous vertex, world space
+    const V3 beta(wzb.y, byz.x, byz.y);
     V3 photonPrevToPhotonL = c.fr.toLocal(-wiPhoton);
     float eyeRev = bsdfPdf(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
     float lightRev = bsdfPdf(c.sh, -c.toPrevL, -photonPrevToPhotonL, 1.0f);
     float wEye = c.eyeDvcmOverEta + eyeRev * c.eyeDvm;
-    float wLight = lightDvcm * c.invEta + lightRev * lightDvm;
+    float wLight = lightDvcmOverEta + lightRev * lightDvm;
     float w = __fdividef(1.0f, 1.0f + wEye + wLight);
     V3 f = bsdfEval(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
     return applyWeight(P, beta * f * c.scale, w);
 }
 
-__global__ void __launch_bounds__(kBdThreads) bdMerge(SceneView sc, BdState st, BdParams P, int* cnt) {
+__global__ void __launch_bounds__(kMergeThreads) bdMerge(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
     __shared__ uint32_t accBuf[kMergeWarps][64];
+    int* cnt = mq.cnt;
     const int lane = bdLane(), warp = threadIdx.x >> 5;
-    const int n = cnt[BC_MERGE];
+    const int n = min(cnt[BC_MERGE_GEN], mq.cap);
     const float r2 = P.mergeRadius * P.mergeRadius;
     const float norm = 1.0f / (kPi * r2 * (float)P.w * (float)P.h);
     const unsigned ltMask = (1u << lane) - 1u;
+    const PhotonSoA ph = P.photons;
     unsigned long long nMerged = 0, nCand = 0;
     while (true) {
         int base = 0;
-        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], 4);
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE_GEN], 4);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n) break;
         const int end = min(base + 4, n);
         for (int r = base; r < end; ++r) {
-            const float4* rp = reinterpret_cast<const float4*>(st.mergeQ + r);
+            const float4* rp = reinterpret_cast<const float4*>(mq.recs + (mq.cap - 1 - r));
             const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2q = __ldg(rp + 2), r3 = __ldg(rp + 3), r4 = __ldg(rp + 4);
             const V3 eyeP(r0.x, r0.y, r0.z);
             const int pix = __float_as_int(r0.w);
             MergeCtx ctx(resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y)), V3(r1.x, r1.y, r1.z));
-            ctx.eyeP = eyeP; ctx.toPrevL = V3(r2q.x, r2q.y, r2q.z); ctx.scale = V3(r3.x, r3.y, r3.z) * norm;
-            ctx.invEta = 1.0f / P.etaVcm; ctx.eyeDvcmOverEta = r2q.w / P.etaVcm; ctx.eyeDvm = r3.w;
-            ctx.diffuse = ctx.sh.m.type == MAT_DIFFUSE;
-            ctx.wEye = ctx.eyeDvcmOverEta + cosinePdf(ctx.toPrevL) * ctx.eyeDvm;
-            const int3 c0 = gridIndex(eyeP.x, eyeP.y, eyeP.z, P.grid);
-            uint32_t cs = 0, cc = 0;
-            if (lane < 27) {
-                int dz = lane / 9 - 1, dy = (lane / 3) % 3 - 1, dx = lane % 3 - 1;
-                unsigned hsh = hashCell(make_int3(c0.x + dx, c0.y + dy, c0.z + dz), P.grid.tableSize);
-                uint32_t s0 = __ldg(P.cellStart + hsh);
-                if (s0 != 0xFFFFFFFFu) { cs = s0; cc = __ldg(P.cellEnd + hsh) - s0; }
-            }
-            uint32_t incl = cc;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
-            const uint32_t excl = incl - cc;
-            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-            nCand += (lane == 0) ? total : 0;
+            ctx.toPrevL = V3(r2q.x, r2q.y, r2q.z); ctx.scale = V3(r3.x, r3.y, r3.z) * norm;
+            ctx.eyeDvcmOverEta = r2q.w / P.etaVcm; ctx.eyeDvm = r3.w;
+            const MergeCells mc = mergeCells(P, eyeP, lane);
+            nCand += mc.cc;
             int count = 0;
             V3 sum(0.0f);
-            // one sweep step: test candidate q (if live), compact the accepted ones, flush a full warp of them
-            auto sweep = [&](bool live, uint32_t q) {
-                bool accept = false;
-                if (live) {
-                    uint4 A = __ldg(P.photons + (size_t)q * 2);
-                    V3 diff = eyeP - V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
-                    accept = dot(diff, diff) <= r2;
-                }
-                const unsigned m = __ballot_sync(0xffffffffu, accept);
-                if (accept) accBuf[warp][count + __popc(m & ltMask)] = q;
-                count += __popc(m);
-                __syncwarp();
-                if (count >= 32) {
-                    sum += mergeOne(P, ctx, accBuf[warp][lane]);
-                    uint32_t carry = accBuf[warp][32 + lane];
-                    __syncwarp();
-                    accBuf[warp][lane] = carry;
-                    count -= 32; nMerged += 32;
-                    __syncwarp();
-                }
-            };
-            if (total >= 27u * 24u) {
-                // dense neighbourhood: cell by cell, lanes strided over the cell's photons (no per-candidate search)
-                for (int c = 0; c < 27; ++c) {
-                    const uint32_t ccount = __shfl_sync(0xffffffffu, cc, c);
-                    if (ccount == 0) continue;
-                    const uint32_t cstart = __shfl_sync(0xffffffffu, cs, c);
-                    for (uint32_t j0 = 0; j0 < ccount; j0 += 32) sweep(j0 + lane < ccount, cstart + j0 + lane);
-                }
-            } else {
-                // sparse: the 27 ranges concatenated; the cell of candidate j is the largest c with excl[c] <= j
-                for (uint32_t j0 = 0; j0 < total; j0 += 32) {
-                    const uint32_t j = j0 + lane;
-                    int c = 0;
-#pragma unroll
-                    for (int stp = 16; stp >= 1; stp >>= 1) {
-                        int t = c + stp;
-                        uint32_t e = __shfl_sync(0xffffffffu, excl, t & 31);
-                        if (t < 27 && e <= j) c = t;
+            unsigned nonEmpty = __ballot_sync(0xffffffffu, mc.cc != 0u);
+            while (nonEmpty) {
+                const int c = __ffs(nonEmpty) - 1;
+                nonEmpty &= nonEmpty - 1;
+                const uint32_t ccount = __shfl_sync(0xffffffffu, mc.cc, c);
+                const uint32_t cstart = __shfl_sync(0xffffffffu, mc.cs, c);
+                for (uint32_t j0 = 0; j0 < ccount; j0 += 32) {
+                    // one sweep step: test a candidate per lane, compact the accepted ones, flush a full warp of them
+                    const uint32_t q = cstart + j0 + lane;
+                    bool accept = false;
+                    if (j0 + lane < ccount) {
+                        const float4 A = __ldg(ph.a + q);
+                        V3 diff = eyeP - V3(A.x, A.y, A.z);
+                        accept = dot(diff, diff) <= r2;
                     }
-                    sweep(j < total, __shfl_sync(0xffffffffu, cs, c) + (j - __shfl_sync(0xffffffffu, excl, c)));
+                    const unsigned m = __ballot_sync(0xffffffffu, accept);
+                    if (accept) accBuf[warp][count + __popc(m & ltMask)] = q;
+                    count += __popc(m);
+                    __syncwarp();
+                    if (count >= 32) {
+                        sum += mergeOne(P, ctx, accBuf[warp][lane]);
+                        uint32_t carry = accBuf[warp][32 + lane];
+                        __syncwarp();
+                        accBuf[warp][lane] = carry;
+                        count -= 32; nMerged += 32;
+                        __syncwarp();
+                    }
                 }
             }
             if (lane < count) sum += mergeOne(P, ctx, accBuf[warp][lane]);
             nMerged += count;
             __syncwarp();
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                sum.x += __shfl_xor_sync(0xffffffffu, sum.x, o); sum.y += __shfl_xor_sync(0xffffffffu, sum.y, o); sum.z += __shfl_xor_sync(0xffffffffu, sum.z, o);
-            }
-            if (lane == 0 && (sum.x != 0.0f || sum.y != 0.0f || sum.z != 0.0f) && isfinite(sum.x) && isfinite(sum.y) && isfinite(sum.z))
-                atomicAdd(&P.colors[pix], make_float4(sum.x, sum.y, sum.z, 0.f));
+            mergeSplat(P, pix, sum, lane);
         }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nCand += __shfl_xor_sync(0xffffffffu, nCand, o);
     if (lane == 0) { if (nMerged) atomicAdd(&st.stats[4], nMerged); if (nCand) atomicAdd(&st.stats[5], nCand); }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0) atomicAdd(&st.stats[6], (unsigned long long)n);
+}
+
+// ---- coarse spatial binning of a group's Lambert merge records (counting sort on a 64^3 Morton grid over the scene box) ----------
+// The record count lives on the device, so these kernels are grid-stride over cnt[BC_MERGE] and need no host round trip.
+NV_D uint32_t mortonSpread6(uint32_t v) {            // 6 bits -> every third bit
+    v = (v | (v << 8)) & 0x300Fu; v = (v | (v << 4)) & 0x30C3u; v = (v | (v << 2)) & 0x9249u;
+    return v;
+}
+NV_D uint32_t mergeBinOf(const MergeBins& b, float4 p) {
+    const int hi = (1 << kMergeBinBits) - 1;
+    int ix = min(max((int)((p.x - b.minX) * b.sx), 0), hi), iy = min(max((int)((p.y - b.minY) * b.sy), 0), hi), iz = min(max((int)((p.z - b.minZ) * b.sz), 0), hi);
+    return mortonSpread6(ix) | (mortonSpread6(iy) << 1) | (mortonSpread6(iz) << 2);
+}
+__global__ void bdMergeBinCount(MergeQueue mq, MergeBins b, uint32_t* __restrict__ binCount) {
+    const int n = min(mq.cnt[BC_MERGE], mq.cap);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        atomicAdd(&binCount[mergeBinOf(b, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u);
+}
+__global__ void bdMergeBinScatter(MergeQueue mq, MergeBins b, uint32_t* __restrict__ binStart, int* __restrict__ order) {
+    const int n = min(mq.cnt[BC_MERGE], mq.cap);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        order[atomicAdd(&binStart[mergeBinOf(b, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u)] = i;
 }
 
 // ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------
@@ -697,12 +818,21 @@ __global__ void bdCompactSlabs(const uint4* __restrict__ slabs, size_t slabWords
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)n * 2; i += (size_t)gridDim.x * blockDim.x)
         out[(size_t)off * 2 + i] = src[i];
 }
-__global__ void bdReorderPhotons(const uint4* __restrict__ in, const uint32_t* __restrict__ index, int n, uint4* __restrict__ out) {
+// gathers the records into cell order and rewrites them for the merge kernels: the octahedral direction is decoded here, once
+// per photon, instead of once per accepted (photon, eye vertex) pair, and d_vcm is pre-divided by eta_vcm
+__global__ void bdReorderPhotons(const uint4* __restrict__ in, const uint32_t* __restrict__ index, int n, float invEta,
+                                 float4* __restrict__ oa, uint4* __restrict__ ob) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     size_t s = (size_t)index[i] * 2;
     uint4 a = __ldg(in + s), b = __ldg(in + s + 1);
-    out[(size_t)i * 2] = a; out[(size_t)i * 2 + 1] = b;
+    V3 wi = unpackOct(a.w);
+    float2 bxy = unpackHalf2(b.x), bz = unpackHalf2(b.y);
+    oa[i] = make_float4(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z), __uint_as_float(packHalf2(wi.x, wi.y)));
+    b.x = packHalf2(wi.z, bxy.x);
+    b.y = packHalf2(bxy.y, bz.x);
+    b.w = __float_as_uint(__uint_as_float(b.w) * invEta);
+    ob[i] = b;
 }
 
 }  // namespace nv

@@ -16,6 +16,8 @@
 //   C = { info (bit0 delta, bit1 backface, bits 22..31 material), d_vc, d_vcm, 0 }
 // Photon record (reference Photons, objects.cuh:1162-1179, 34 B in 10 arrays; its packedNormal is never read): 32 B
 //   A = { pos.x, pos.y, pos.z, oct(wi) }     B = { half2(beta.x, beta.y), half2(beta.z, 0), d_vm, d_vcm }
+// The grid build gathers the records into cell order in a merge-ready structure of arrays (PhotonSoA, bdReorderPhotons): wi decoded
+// once to 3 x fp16, d_vcm pre-divided by eta_vcm.
 // Photon slab of rank r: [32 B header: int count, int capacity, ...][capacity x 32 B records]; slabs of all ranks are
 // contiguous, so one all-gather on the whole buffer exchanges an iteration's photons.
 #pragma once
@@ -32,11 +34,27 @@ constexpr int kMaxBdDepth = 32;          // eye / light depth limit of the wavef
 constexpr int kSlabHeaderBytes = 32;
 
 // per (pass, depth) counters; one memset per pass clears them all
-enum : int { BC_QUEUE = 0, BC_SHADOW = 1, BC_FETCH_EXTEND = 2, BC_FETCH_STEP = 3, BC_FETCH_RESOLVE = 4, BC_MERGE = 5, BC_FETCH_MERGE = 6, BC_STRIDE = 8 };
+// BC_MERGE counts the Lambert merge records (front of mergeQ), BC_MERGE_GEN the records of every other material (back of mergeQ)
+enum : int { BC_QUEUE = 0, BC_SHADOW = 1, BC_FETCH_EXTEND = 2, BC_FETCH_STEP = 3, BC_FETCH_RESOLVE = 4, BC_MERGE = 5, BC_FETCH_MERGE = 6,
+             BC_MERGE_GEN = 7, BC_FETCH_MERGE_GEN = 8, BC_STRIDE = 16 };
 
 struct __align__(16) BdShadowRec { float4 o_maxT; float4 d_pix; float4 contrib_skip; };   // 48 B
 // eye vertex waiting for its photon gather: {p, pixel} {n, material} {toPrev (local frame), d_vcm} {beta, d_vm} {uv}
 struct __align__(16) BdMergeRec { float4 p_pix, n_mat, toPrev_dvcm, beta_dvm, uv; };      // 80 B
+
+// where one eye step appends its merge records and what the merge kernels consume: Lambert vertices from the front
+// (cnt[BC_MERGE]), every other material from the back (cnt[BC_MERGE_GEN]). Step 0 (primary hits, already coherent in pixel
+// order) is merged at once; deeper steps share a queue per group of kMergeGroup steps, whose Lambert records are binned on a
+// coarse Morton grid before the gather so that neighbouring warps read the same photon cells (L2 instead of HBM).
+struct MergeQueue { BdMergeRec* recs; int cap; int* cnt; const int* order; };
+constexpr int kMergeGroup = 4;
+constexpr int kMergeBinBits = 6;                       // bins per axis = 64, Morton-interleaved
+constexpr int kMergeBins = 1 << (3 * kMergeBinBits);
+struct MergeBins { float minX, minY, minZ, sx, sy, sz; };
+
+// merge-ready photons in cell order, written by bdReorderPhotons, as two dense 16 B streams so that a warp's candidate loads are
+// two fully coalesced 512 B requests:  a = { pos.xyz, half2(wi.x, wi.y) }   b = { half2(wi.z, beta.x), half2(beta.y, beta.z), d_vm, d_vcm / eta_vcm }
+struct PhotonSoA { const float4* a; const uint4* b; };
 
 struct BdState {
     // per local path (shared by the light pass and the eye pass, which run one after the other)
@@ -51,9 +69,11 @@ struct BdState {
     int* pathLen;      // surface vertices stored per light path
     uint4 *lvA, *lvB, *lvC;
     BdShadowRec* shadowQ;
-    BdMergeRec* mergeQ;         // at most one record per path and depth
+    BdMergeRec* mergeQ;         // (1 + kMergeGroup) * nLocal records: [0, nLocal) step 0, the rest the current group of deeper steps
+    int* mergeOrder;            // processing order of a group's Lambert records (kMergeGroup * nLocal)
+    uint32_t* mergeBinCount;    // kMergeBins + scan scratch
     int* counters;     // (kMaxBdDepth + 1) * BC_STRIDE
-    unsigned long long* stats;   // [0] closest rays [1] shadow rays [2] photons stored [3] light vertices stored [4] merges accepted [5] merge candidates (photons in the 27 cells)
+    unsigned long long* stats;   // [0] closest rays [1] shadow rays [2] photons stored [3] light vertices stored [4] merges accepted [5] merge candidates (photons in the 27 cells) [6] merge queries (eye vertices gathered)
     int nLocal;
     int shadowCap;
 };
@@ -73,9 +93,10 @@ struct BdParams {
     // photons
     uint4* slab;                       // this rank's slab (header + records), append target of the light pass
     int slabCap;
-    const uint4* photons;              // records in cell order (eye pass)
+    PhotonSoA photons;                 // records in cell order (eye pass), merge-ready
     const uint32_t* cellStart; const uint32_t* cellEnd;
     GridParams grid;
+    MergeBins bins;
 };
 
 NV_D int localToPixel(const BdParams& P, int l, int& x, int& y) {

@@ -24,7 +24,7 @@ struct BdEngine {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     unsigned long long launches = 0, iterations = 0;
     float deviceMs = 0.f;
-    float stageMs[4] = {0, 0, 0, 0};      // profile bit 0: [0] closest-hit extends [1] light/eye step kernels [2] shadow resolves [3] photon grid build + merge kernels + rest
+    float stageMs[4] = {0, 0, 0, 0};      // profile bit 0: [0] closest-hit extends [1] light/eye step kernels + photon grid build + memsets [2] shadow resolves [3] merge kernels
     unsigned long long stageLaunches[4] = {0, 0, 0, 0};
     bool prof = false, profCount = false;
     std::vector<cudaEvent_t> evs; std::vector<int> evCls; size_t evUsed = 0;
@@ -44,7 +44,7 @@ static void bdFree(BdEngine& e) {
     BdState& s = e.st;
     cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.dv); cudaFree(s.rng); cudaFree(s.hit);
     cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
-    cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.counters); cudaFree(s.stats);
+    cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.mergeOrder); cudaFree(s.mergeBinCount); cudaFree(s.counters); cudaFree(s.stats);
     cudaFree(e.slabs); cudaFree(e.photonsAll); cudaFree(e.photonsSorted); cudaFree(e.d_counts);
     if (e.h_counts) cudaFreeHost(e.h_counts);
     if (e.gridAllocated) hashGridFree(e.grid);
@@ -81,7 +81,11 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     if (cap > 0x7fffffffull) cap = 0x7fffffffull;
     s.shadowCap = (int)cap;
     A((void**)&s.shadowQ, cap * sizeof(BdShadowRec));
-    if (e.mode == BD_MODE_VCM) A((void**)&s.mergeQ, n * sizeof(BdMergeRec));
+    if (e.mode == BD_MODE_VCM) {
+        A((void**)&s.mergeQ, n * (size_t)(1 + kMergeGroup) * sizeof(BdMergeRec));
+        A((void**)&s.mergeOrder, n * (size_t)kMergeGroup * sizeof(int));
+        A((void**)&s.mergeBinCount, ((size_t)kMergeBins + 1024) * sizeof(uint32_t));
+    }
     A((void**)&s.counters, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int));
     A((void**)&s.stats, 8 * sizeof(unsigned long long));
     // photon storage: one slab per rank, sized for that rank's worst case (every vertex of every light path)
@@ -92,7 +96,7 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     A((void**)&e.slabs, e.slabWords * 16 * e.world);
     if (e.mode == BD_MODE_VCM) {
         if (e.world > 1) A((void**)&e.photonsAll, (size_t)e.maxPhotons * 32);
-        A((void**)&e.photonsSorted, (size_t)e.maxPhotons * 32);
+        A((void**)&e.photonsSorted, (((size_t)e.maxPhotons + 63) & ~(size_t)63) * 32);
     }
     A((void**)&e.d_counts, 16 * sizeof(int));
     if (err != cudaSuccess) return (int)err;
@@ -125,7 +129,17 @@ static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
     P.seed = e.seed; P.iter = iter; P.rank = e.rank; P.world = e.world; P.nLocal = e.nLocal;
     P.colors = colors;
     P.slab = e.slabs + (size_t)e.rank * e.slabWords; P.slabCap = e.slabCap;
-    P.photons = e.photonsSorted; P.cellStart = e.grid.cellStart; P.cellEnd = e.grid.cellEnd; P.grid = e.grid.params;
+    for (int k = 0; k < 3; ++k) {
+        float ext = e.scene->sceneMax[k] - e.scene->sceneMin[k];
+        (&P.bins.minX)[k] = e.scene->sceneMin[k];
+        (&P.bins.sx)[k] = ext > 0.0f ? (float)(1 << kMergeBinBits) / ext : 0.0f;
+    }
+    {   // PhotonSoA over the one allocation: a | b, each maxPhotons (rounded to 64) 16 B entries
+        size_t np = ((size_t)e.maxPhotons + 63) & ~(size_t)63;
+        P.photons.a = reinterpret_cast<const float4*>(e.photonsSorted);
+        P.photons.b = e.photonsSorted + np;
+    }
+    P.cellStart = e.grid.cellStart; P.cellEnd = e.grid.cellEnd; P.grid = e.grid.params;
     return P;
 }
 
@@ -147,7 +161,7 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
     cudaMemsetAsync(P.slab, 0, kSlabHeaderBytes, s);                      // photon counter of this rank (deviceCode.cu:3330)
     if (e.nLocal == 0 || sc.numLights == 0) return 0;
     const int numSteps = e.mode == BD_MODE_BDPT ? e.lightDepth - 1 : e.lightDepth;      // :1116 (depth 1..max-1) vs :2029 (0..max-1)
-    bdTick(e, 3);
+    bdTick(e, 1);
     bdLightStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(sc, st, P);
     ++e.launches; bdTick(e, 1);
     const int grid = bdGrid();
@@ -192,10 +206,11 @@ static int bdBuildGrid(BdEngine& e, int iter) {
     if (rc) return rc;
     e.launches += e.grid.launches;
     if (e.photonCount > 0) {
-        bdReorderPhotons<<<(e.photonCount + 255) / 256, 256, 0, s>>>(src, e.grid.index, e.photonCount, e.photonsSorted);
+        bdReorderPhotons<<<(e.photonCount + 255) / 256, 256, 0, s>>>(src, e.grid.index, e.photonCount, 1.0f / P.etaVcm,
+            const_cast<float4*>(P.photons.a), const_cast<uint4*>(P.photons.b));
         ++e.launches;
     }
-    bdTick(e, 3);
+    bdTick(e, 1);
     return (int)cudaGetLastError();
 }
 
@@ -207,10 +222,12 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
     if (e.nLocal == 0) return 0;
     cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
     const int numSteps = e.mode == BD_MODE_BDPT ? e.eyeDepth - 1 : e.eyeDepth;          // :794 vs :2723
-    bdTick(e, 3);
+    bdTick(e, 1);
     bdEyeStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(st, P);
     ++e.launches; bdTick(e, 1);
     const int grid = bdGrid();
+    static const int mergeCtas = [] { const char* v = getenv("NOVUM_MERGE_CTAS"); int k = v ? atoi(v) : 0; return k >= 1 && k <= 16 ? k : 8; }();
+    const int mgrid = smCount() * mergeCtas;         // merge kernels: 128 threads, 8 CTAs per SM (tuning knob: NOVUM_MERGE_CTAS)
     const bool shadows = P.nee || P.connection;
     const bool merging = e.mode == BD_MODE_VCM && P.doMerge && P.mergeRadius > 0.0f;
     TravCounters tc{e.scene->d_counters, e.scene->d_counters + 1};
@@ -219,10 +236,40 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
         if (e.profCount) bdExtend<true><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
         else bdExtend<false><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
         bdTick(e, 0);
-        bdEyeStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
+        // merge records: step 0 has its own queue and is gathered at once; deeper steps append to the queue of their group
+        const bool grouped = step > 0;
+        const int groupFirst = grouped ? 1 + ((step - 1) / kMergeGroup) * kMergeGroup : 0;
+        MergeQueue mq;
+        mq.recs = grouped ? st.mergeQ + e.nLocal : st.mergeQ;
+        mq.cap = grouped ? kMergeGroup * e.nLocal : e.nLocal;
+        mq.cnt = st.counters + groupFirst * BC_STRIDE;
+        mq.order = nullptr;
+        bdEyeStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1], mq);
         bdTick(e, 1);
         if (shadows) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; bdTick(e, 2); }
-        if (merging) { bdMerge<<<grid, kBdThreads, 0, s>>>(sc, st, P, cnt); ++e.launches; bdTick(e, 3); }
+        const bool flush = !grouped || step == groupFirst + kMergeGroup - 1 || step == numSteps - 1;
+        if (merging && flush) {
+            if (grouped && !P.paintWeight) {
+                cudaMemsetAsync(st.mergeBinCount, 0, kMergeBins * sizeof(uint32_t), s);
+                bdMergeBinCount<<<grid, 256, 0, s>>>(mq, P.bins, st.mergeBinCount);
+                int scanLaunches = 0;
+                exclusiveScanU32(st.mergeBinCount, kMergeBins, st.mergeBinCount + kMergeBins, s, &scanLaunches);
+                bdMergeBinScatter<<<grid, 256, 0, s>>>(mq, P.bins, st.mergeBinCount, st.mergeOrder);
+                e.launches += 2 + scanLaunches;
+                mq.order = st.mergeOrder;
+            }
+            // Lambert vertices (front of the queue) and all other materials (back): a kernel whose queue is empty exits at once
+            if (P.paintWeight) {}
+            else if (P.doMis) {
+                if (grouped) bdMergeLambert<true, 1><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+                else bdMergeLambert<true, 4><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+            } else {
+                if (grouped) bdMergeLambert<false, 1><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+                else bdMergeLambert<false, 4><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+            }
+            bdMerge<<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+            e.launches += P.paintWeight ? 1 : 2; bdTick(e, 3);
+        }
         e.launches += 2;
     }
     ++e.iterations;
@@ -235,8 +282,7 @@ static void bdFillStats(BdEngine& e, NovumRenderStats* stats) {
     cudaMemcpy(h, e.st.stats, sizeof(h), cudaMemcpyDeviceToHost);
     memset(stats, 0, sizeof(*stats));
     stats->closestRays = h[0]; stats->shadowRays = h[1]; stats->photons = h[2]; stats->lightVertices = h[3];
-    stats->triTests = h[4];                           // bidirectional renders: photons merged (inside the radius) ...
-    stats->bvhNodeVisits = h[5];                      // ... and merge candidates (photons in the 27 cells), in the two spare counters
+    stats->mergeAccepted = h[4]; stats->mergeCandidates = h[5]; stats->mergeQueries = h[6];
     stats->paths = 2ull * (unsigned long long)e.nLocal * e.iterations;      // one light + one eye path per pixel per iteration
     stats->kernelLaunches = e.launches;
     stats->deviceMs = e.deviceMs;
@@ -245,7 +291,7 @@ static void bdFillStats(BdEngine& e, NovumRenderStats* stats) {
         unsigned long long c2[2] = {0, 0};
         cudaMemcpy(c2, e.scene->d_counters, sizeof(c2), cudaMemcpyDeviceToHost);
         stats->bvhNodeVisits = c2[0];
-        stats->triTests = c2[1];                      // (replaces the merge count in the counted run)
+        stats->triTests = c2[1];
     }
 }
 

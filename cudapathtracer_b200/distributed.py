@@ -43,6 +43,30 @@ def render_striped(scene, cfg, cam, first, count, colors, dist=None, seed=103033
     return scene.render_device(cfg, cam, first, count, colors.data_ptr(), seed=seed, rank=rank, world=world)
 
 
+SLAB_HEADER_BYTES, PHOTON_BYTES = 32, 32          # csrc/vcm.cuh: kSlabHeaderBytes, 2 x 16 B per photon record
+
+
+def used_slab_bytes(max_count, slab_bytes):
+    """Bytes of a slab's prefix that hold `max_count` photons (header included), clamped to the slab."""
+    cap = (slab_bytes - SLAB_HEADER_BYTES) // PHOTON_BYTES
+    return SLAB_HEADER_BYTES + PHOTON_BYTES * max(0, min(int(max_count), cap))
+
+
+def exchange_slabs(dist, slabs, rank, world, slab_bytes):
+    """In-place all-gather of the ranks' photon slabs (`slabs`: flat uint8 tensor of world x slab_bytes; rank r has filled
+    slab r). Every slab is `[32 B header: count][records]` at a fixed stride and a light pass fills only a fraction of the
+    worst-case capacity, so only the used prefix travels: the ranks agree on the largest count (one 4-byte all-reduce + host
+    read), then gather that prefix of every slab into place. Returns the bytes gathered per slab."""
+    import torch
+    mine = slabs[rank * slab_bytes:(rank + 1) * slab_bytes]
+    count = mine[:4].view(torch.int32).clone()
+    dist.all_reduce(count, op=dist.ReduceOp.MAX)
+    used = used_slab_bytes(int(count.item()), slab_bytes)
+    outs = [slabs[r * slab_bytes:r * slab_bytes + used] for r in range(world)]
+    dist.all_gather(outs, mine[:used])
+    return used
+
+
 class TileRenderer:
     """Tile-sharded bidirectional render: keeps the per-rank session (buffers, slabs) alive across calls."""
 
@@ -55,19 +79,24 @@ class TileRenderer:
         self.mine = self.session.my_slab_tensor()
         self.ext_stream = torch.cuda.ExternalStream(self.session.stream())
         self.exchanged_bytes = 0
+        self.last_exchange_bytes = 0
 
     def close(self):
         self.session.close()
 
+    def exchange(self):
+        """All-gather of this iteration's photons on the engine's own stream (behind the light pass, ahead of the grid build)."""
+        with self.torch.cuda.stream(self.ext_stream):
+            used = exchange_slabs(self.dist, self.slabs, self.rank, self.world, self.session.slab_bytes)
+        self.exchanged_bytes += used * self.world
+        self.last_exchange_bytes = used * self.world
+
     def iteration(self, it, colors):
-        torch, dist = self.torch, self.dist
         s = self.session
         s.light_pass(it, colors.data_ptr())
         if self.world > 1:
             # the collective runs on the engine's own stream, right behind the light pass and ahead of the grid build
-            with torch.cuda.stream(self.ext_stream):
-                dist.all_gather_into_tensor(self.slabs, self.mine)
-            self.exchanged_bytes += self.slabs.numel()
+            self.exchange()
         s.build_grid(it)
         s.eye_pass(it, colors.data_ptr())
 

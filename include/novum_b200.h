@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define NOVUM_ABI_VERSION 1
+#define NOVUM_ABI_VERSION 2
 
 /* error codes (negative; positive return values are cudaError_t) */
 #define NOVUM_OK             0
@@ -159,10 +159,12 @@ typedef struct NovumRenderStats {
     uint64_t kernelLaunches;
     float    deviceMs;                 /* CUDA-event time of the sample loop on the launch stream */
     float    _pad;
-    uint64_t bvhNodeVisits, triTests;  /* closest-hit traversal only; filled when profile bit 1 is set. VCM / SPPM renders
-                                          without bit 1 report merge candidates / photons merged here instead */
-    float    stageMs[4];               /* profile bit 0: CUDA-event time of [0] extend (closest hit) [1] shade [2] shadow [3] other */
+    uint64_t bvhNodeVisits, triTests;  /* closest-hit traversal only; filled when profile bit 1 is set */
+    float    stageMs[4];               /* profile bit 0: CUDA-event time of [0] extend (closest hit) [1] shade / light+eye step kernels
+                                          (+ photon grid build) [2] shadow / connection resolves [3] other / photon merge kernels */
     uint64_t stageLaunches[4];
+    uint64_t mergeQueries, mergeCandidates, mergeAccepted;   /* VCM / SPPM: eye vertices gathered, photons scanned in their 27 cells,
+                                                                photons inside the radius */
 } NovumRenderStats;
 
 typedef struct NovumScene NovumScene;  /* opaque: device geometry + BVH8 + materials + lights */

@@ -16,7 +16,7 @@ def test_library_exports_every_declared_symbol(built):
     assert len(nb.DECLARED_SYMBOLS) >= 40
     missing = [s for s in nb.DECLARED_SYMBOLS if not hasattr(L, s)]
     assert not missing, f"declared in novum_b200.h but not exported: {missing}"
-    assert L.novum_abi_version() == 1
+    assert L.novum_abi_version() == 2
 
 
 def test_exports_are_plain_c_symbols(built):
@@ -35,7 +35,7 @@ def test_struct_layouts_match_reference():
     for name, off in (("type", 32), ("albedo", 48), ("roughness", 64), ("eta", 80), ("k", 96), ("ior", 112), ("transmission", 124),
                       ("isSpecular", 128), ("boundary", 129), ("thinWalled", 130), ("absorption", 144), ("priority", 160)):
         assert B.MAT_DTYPE.fields[name][1] == off, name
-    assert C.sizeof(B.RenderStats) == 120
+    assert C.sizeof(B.RenderStats) == 144
 
 
 def test_error_strings_and_null_handles(built):

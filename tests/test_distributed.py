@@ -61,11 +61,45 @@ def test_two_rank_partition_and_reduce(tmp_path, h, w, first, count):
     assert np.allclose(total[..., 2], sum(r + 1 for r in range(world)))                     # full-frame sum over ranks
 
 
+def _exchange_worker(rank, world, port, cap, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sb = 32 + 32 * cap
+        slabs = torch.full((world * sb,), 0xEE, dtype=torch.uint8)       # stale bytes everywhere
+        mine = slabs[rank * sb:(rank + 1) * sb]
+        n = 2 + 3 * rank                                                 # ranks store different photon counts
+        mine[:32] = 0
+        mine[:4].view(torch.int32)[0] = n
+        mine[32:32 + 32 * n] = rank + 1
+        used = nd.exchange_slabs(dist, slabs, rank, world, sb)
+        assert used == 32 + 32 * (2 + 3 * (world - 1))                   # prefix of the fullest slab
+        for r in range(world):
+            s = slabs[r * sb:(r + 1) * sb]
+            nr = 2 + 3 * r
+            assert int(s[:4].view(torch.int32)[0]) == nr
+            assert bool((s[32:32 + 32 * nr] == r + 1).all())
+        if rank == 0:
+            open(os.path.join(out_dir, "ok"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_slab_exchange(tmp_path):
+    port = _free_port()
+    mp.spawn(_exchange_worker, args=(2, port, 16, str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok").exists()
+
+
 def test_single_process_helpers():
     assert nd.shard_of(None) == (0, 1)
     assert nd.local_rows(5, 1, 2) == [1, 3]
     assert nd.local_rows(2, 2, 3) == []
     assert nd.striped_samples(4, 5, 1, 2) == [5, 7]
     assert nd.striped_samples(0, 0, 0, 2) == []
+    assert nd.used_slab_bytes(0, 32 + 32 * 10) == 32
+    assert nd.used_slab_bytes(3, 32 + 32 * 10) == 32 + 96
+    assert nd.used_slab_bytes(99, 32 + 32 * 10) == 32 + 320          # clamped to the slab's capacity
     f = torch.ones((2, 2, 4))
     assert nd.reduce_frames(f, None) is f
