@@ -262,8 +262,11 @@ class Scene:
     def set_profile(self, flags):
         _check(lib().novum_set_profile(self.h, int(flags)), "novum_set_profile")
 
-    def render(self, cfg, cam, first_sample, num_sample, seed=103033, rank=0, world=1):
-        img = np.zeros((cfg.height, cfg.width, 4), np.float32)
+    def render(self, cfg, cam, first_sample, num_sample, seed=103033, rank=0, world=1, out=None):
+        """novum_render: the sum over the passes, copied to host. `out`: optional (h, w, 4) float32 host array to fill (a
+        page-locked one, e.g. torch.empty(..., pin_memory=True).numpy(), receives the frame at full PCIe rate)."""
+        img = out if out is not None else np.empty((cfg.height, cfg.width, 4), np.float32)
+        assert img.shape == (cfg.height, cfg.width, 4) and img.dtype == np.float32 and img.flags.c_contiguous
         st = RenderStats()
         _check(lib().novum_render(self.h, C.byref(cfg), C.byref(cam), first_sample, num_sample, Shard(rank, world), seed, _ptr(img),
                                   C.byref(st)), "novum_render")

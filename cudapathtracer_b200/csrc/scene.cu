@@ -197,6 +197,7 @@ void novum_scene_destroy(NovumScene* s) {
         cudaFree(s->d_positions); cudaFree(s->d_normals); cudaFree(s->d_uvs); cudaFree(s->d_tris);
         cudaFree(s->d_lights); cudaFree(s->d_matsRef); cudaFree(s->d_textures);
     }
+    cudaFree(s->d_frame);
     cudaFree(s->d_mats); cudaFree(s->d_counters); cudaFree(s->d_queueCounter); cudaFree(s->d_stage);
     freeBvh8(s->bvh);
     if (s->ev0) { cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); }

@@ -37,6 +37,7 @@ struct NovumScene {
     // lazily created integrator engines (owned; freed through the stored deleter)
     void* wfEngine = nullptr;  void (*wfEngineFree)(void*) = nullptr;
     void* vcmEngine = nullptr; void (*vcmEngineFree)(void*) = nullptr;
+    void* d_frame = nullptr; size_t frameBytes = 0;     // device framebuffer of novum_render, kept across calls
 
     nv::SceneView view() const;
 };

@@ -42,6 +42,23 @@ NV_D float rcpApprox(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"
 NV_D uint32_t packHalf2(float a, float b) { __half2 h = __halves2half2(__float2half(a), __float2half(b)); return *reinterpret_cast<uint32_t*>(&h); }
 NV_D float2 unpackHalf2(uint32_t u) { __half2 h = *reinterpret_cast<__half2*>(&u); return __half22float2(h); }
 
+// BSDF value / pdf for the connection code. The Lambert case is resolved inline; every other material goes through ONE
+// out-of-line copy of the full dispatch. Inlined at each of the ~15 call sites the dispatch made bdEyeStep 145 KB of SASS,
+// and the kernel stalled on instruction fetch (no_instruction 5.9-10 per issue, profiles/r1_bdEyeStep_inlined.txt).
+__device__ __noinline__ V3 bsdfEvalCall(const Shading& s, V3 wiToward, V3 wo, float etaI) { return bsdfEval(s, wiToward, wo, etaI); }
+__device__ __noinline__ float bsdfPdfCall(const Shading& s, V3 wiToward, V3 wo, float etaI) { return bsdfPdf(s, wiToward, wo, etaI); }
+#ifdef NOVUM_BD_INLINE_BSDF          // A/B build switch: the dispatch inlined at every call site
+NV_D V3 bdEval(const Shading& s, V3 wiToward, V3 wo, float etaI) { return bsdfEval(s, wiToward, wo, etaI); }
+NV_D float bdPdf(const Shading& s, V3 wiToward, V3 wo, float etaI) { return bsdfPdf(s, wiToward, wo, etaI); }
+#else
+NV_D V3 bdEval(const Shading& s, V3 wiToward, V3 wo, float etaI) {
+    return s.m.type == MAT_DIFFUSE ? s.m.albedo / kPi : bsdfEvalCall(s, wiToward, wo, etaI);
+}
+NV_D float bdPdf(const Shading& s, V3 wiToward, V3 wo, float etaI) {
+    return s.m.type == MAT_DIFFUSE ? cosinePdf(wo) : bsdfPdfCall(s, wiToward, wo, etaI);
+}
+#endif
+
 struct LightVtx { V3 p, n, wo, beta; float2 uv; bool delta, backface; int mat; float d_vc, d_vcm; };
 
 // quantises v in place to what the cache holds and writes the three words
@@ -148,8 +165,8 @@ NV_D void lightTraceSplat(const SceneView& sc, const BdState& st, const BdParams
         Frame fl(v.n);
         V3 currToPrevL = fl.toLocal(v.wo), toCamL = fl.toLocal(dirU);
         Shading sh = resolveShading(sc.mats, v.mat, sc.textures, v.uv);
-        f = bsdfEval(sh, -currToPrevL, toCamL, 1.0f);
-        float pdfOne = bsdfPdf(sh, -toCamL, currToPrevL, 1.0f);
+        f = bdEval(sh, -currToPrevL, toCamL, 1.0f);
+        float pdfOne = bdPdf(sh, -toCamL, currToPrevL, 1.0f);
         wLight = pdfCurrRevArea * (P.etaVcm + v.d_vcm + pdfOne * v.d_vc);
     }
     V3 contrib = v.beta * f * (G * We);
@@ -240,7 +257,7 @@ NV_D bool walkVertex(const SceneView& sc, const BdParams& P, BdPath& p, const fl
     V3 f; float pdfFwdSA;
     bsdfSample(p.rng, o.sh, o.woL, 1.0f, o.s.backface, lightWalk ? MODE_IMPORTANCE : MODE_RADIANCE, o.wiL, f, pdfFwdSA);
     o.wiW = fr.toWorld(o.wiL);
-    float pdfRevSA = bsdfPdf(o.sh, -o.wiL, -o.woL, 1.0f);
+    float pdfRevSA = bdPdf(o.sh, -o.wiL, -o.woL, 1.0f);
     if (pdfFwdSA < kEps) return false;
     o.currBeta = p.beta;
     p.beta = p.beta * f * (fabsf(o.wiL.z) / pdfFwdSA);
@@ -470,13 +487,13 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                                     float pdfEmit = cosLight / kPi;
                                     V3 prevToCurrL = -toPrevL;                   // VCM: toLocal(eyePos - prevPos); BDPT: toLocal(-wo)
                                     V3 toLL = fr.toLocal(toLU);
-                                    V3 f = bsdfEval(o.sh, prevToCurrL, toLL, 1.0f);
+                                    V3 f = bdEval(o.sh, prevToCurrL, toLL, 1.0f);
                                     V3 unweighted = f * V3(em.x, em.y, em.z) * (G / pdfConnect) * o.currBeta;
-                                    float pdfBsdfArea = bsdfPdf(o.sh, prevToCurrL, toLL, 1.0f) * fabsf(cosLight) / dSq;
+                                    float pdfBsdfArea = bdPdf(o.sh, prevToCurrL, toLL, 1.0f) * fabsf(cosLight) / dSq;
                                     float ratio = pdfBsdfArea / pdfConnect;
                                     float wLight = vcm ? ratio * ratio : ratio;               // :2526 vs :1519
                                     float pdfCurrRevArea = pdfEmit * fabsf(toLL.z) / dSq;
-                                    float pdfOne = bsdfPdf(o.sh, -toLL, -prevToCurrL, 1.0f);
+                                    float pdfOne = bdPdf(o.sh, -toLL, -prevToCurrL, 1.0f);
                                     float wEye = pdfCurrRevArea * (eta + o.d_vcm + pdfOne * o.d_vc);
                                     float w = 1.0f / (1.0f + wLight + wEye);
                                     pushShadow(st, cnt, s.p + s.n * kRayEps, toLU, sqrtf(dSq) - kEps, lightTri, (unsigned)pix | clampFlag | SR_NEE,
@@ -499,15 +516,15 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                                 Frame fl(lv.n);
                                 Shading shL = resolveShading(sc.mats, lv.mat, sc.textures, lv.uv);
                                 V3 l2eAtLight = fl.toLocal(-e2lU), toLightFromPrevAtLight = fl.toLocal(-lv.wo);
-                                float pdfEyeRevArea = bsdfPdf(shL, toLightFromPrevAtLight, l2eAtLight, 1.0f) * cosEye / dSq;
+                                float pdfEyeRevArea = bdPdf(shL, toLightFromPrevAtLight, l2eAtLight, 1.0f) * cosEye / dSq;
                                 V3 l2eAtEye = fr.toLocal(-e2lU);
-                                float pdfOneBeforeEye = bsdfPdf(o.sh, l2eAtEye, toPrevL, 1.0f);
-                                float pdfLightRevArea = bsdfPdf(o.sh, -toPrevL, -l2eAtEye, 1.0f) * cosLight / dSq;
-                                float pdfOneBeforeLight = bsdfPdf(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
+                                float pdfOneBeforeEye = bdPdf(o.sh, l2eAtEye, toPrevL, 1.0f);
+                                float pdfLightRevArea = bdPdf(o.sh, -toPrevL, -l2eAtEye, 1.0f) * cosLight / dSq;
+                                float pdfOneBeforeLight = bdPdf(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
                                 float wEye = pdfEyeRevArea * (eta + o.d_vcm + pdfOneBeforeEye * o.d_vc);
                                 float wLight = pdfLightRevArea * (eta + lv.d_vcm + pdfOneBeforeLight * lv.d_vc);
-                                V3 fEye = bsdfEval(o.sh, l2eAtEye, toPrevL, 1.0f);
-                                V3 fLight = bsdfEval(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
+                                V3 fEye = bdEval(o.sh, l2eAtEye, toPrevL, 1.0f);
+                                V3 fLight = bdEval(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
                                 float G = fminf(cosEye * cosLight / dSq, 2.0f);
                                 V3 unweighted = o.currBeta * lv.beta * fEye * fLight * G;
                                 float w = 1.0f / (1.0f + wEye + wLight);
@@ -591,8 +608,8 @@ NV_D void mergeSplat(const BdParams& P, int pix, V3 sum, int lane) {
 // bandwidth limit the one-vertex-per-warp form sits on. A photon within r of a vertex always lies in one of that vertex's own
 // 27 cells, so testing a vertex against the cells of its neighbours adds only rejected candidates; table slots are de-duplicated
 // across the union (the reference visits a slot twice when two of a vertex's neighbour cells collide in the table, p ~ 1e-6).
-template <bool MIS, int G>
-__global__ void __launch_bounds__(kMergeThreads) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
+template <bool MIS, int G, int MINB>
+__global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
     int* cnt = mq.cnt;
     const int lane = bdLane();
     const int n = min(cnt[BC_MERGE], mq.cap);
@@ -601,17 +618,23 @@ __global__ void __launch_bounds__(kMergeThreads) bdMergeLambert(SceneView sc, Bd
     const float invEta = 1.0f / P.etaVcm;
     const PhotonSoA ph = P.photons;
     const unsigned ltMask = (1u << lane) - 1u;
+    __shared__ uint2 cellListAll[kMergeWarps][G * 32];
+    __shared__ uint32_t cellKeyAll[kMergeWarps][G * 32];
+    uint2* cellList = cellListAll[threadIdx.x >> 5];
+    uint32_t* cellKey = cellKeyAll[threadIdx.x >> 5];
     unsigned long long nCand = 0;
     unsigned nAcc = 0;
     while (true) {
+        __syncwarp();
         int base = 0;
         if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], G);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n) break;
         V3 eyeP[G], nPi[G], sum[G];
         float C[G];
-        uint32_t cs[G], cc[G], key[G];
         int recIdx[G];
+        // the group's cell list lives in shared memory (entry g * 32 + lane = {first photon, count} of vertex g's neighbour
+        // `lane`), so the sweep below exists once in the code and walks the list with a dynamic index
 #pragma unroll
         for (int g = 0; g < G; ++g) {
             // a short last group repeats its last record (its result is dropped below)
@@ -623,37 +646,43 @@ __global__ void __launch_bounds__(kMergeThreads) bdMergeLambert(SceneView sc, Bd
             nPi[g] = V3(r1.x, r1.y, r1.z) * (1.0f / kPi);                                        // cos/pi = dot(wi, n/pi)
             C[g] = 1.0f + r2q.w * invEta + cosinePdf(V3(r2q.x, r2q.y, r2q.z)) * r3.w;           // 1 + d_vcm/eta + eyeRev * d_vm
             sum[g] = V3(0.0f);
-            const MergeCells mc = mergeCells(P, eyeP[g], lane);
-            cs[g] = mc.cs; cc[g] = mc.cc;
-            // drop table slots already listed: by an earlier lane of this vertex, or by an earlier vertex of the group
-            // (key = first photon of the slot; empty slots get keys no photon index can take)
-            key[g] = mc.cc ? mc.cs : 0xFFFFFF00u + (unsigned)lane;
-            if (G > 1) {
-                const unsigned same = __match_any_sync(0xffffffffu, key[g]);
-                if (same & ltMask) cc[g] = 0u;
-#pragma unroll
-                for (int k = 0; k < g; ++k) {
-                    if (__all_sync(0xffffffffu, key[k] == key[g])) { cc[g] = 0u; continue; }     // same centre cell: identical lists
-                    for (int j = 0; j < 27; ++j) if (__shfl_sync(0xffffffffu, key[k], j) == key[g]) cc[g] = 0u;
-                }
-            }
-            if (base + g >= n) cc[g] = 0u;
+            MergeCells mc = mergeCells(P, eyeP[g], lane);
+            if (base + g >= n) mc.cc = 0u;
+            // key = first photon of the slot; empty slots get keys no photon index can take
+            cellKey[g * 32 + lane] = mc.cc ? mc.cs : 0xFFFFFF00u + (unsigned)lane;
+            cellList[g * 32 + lane] = make_uint2(mc.cs, mc.cc);
         }
-#pragma unroll
+        __syncwarp();
+        if (G > 1) {
+            // drop table slots already listed by an earlier lane of the same vertex or by an earlier vertex of the group
+#pragma unroll 1
+            for (int g = 0; g < G; ++g) {
+                const uint32_t key = cellKey[g * 32 + lane];
+                bool dup = (__match_any_sync(0xffffffffu, key) & ltMask) != 0u;
+#pragma unroll 1
+                for (int k = 0; k < g; ++k) {
+                    if (__all_sync(0xffffffffu, cellKey[k * 32 + lane] == key)) { dup = true; break; }   // same centre cell: identical lists
+#pragma unroll 1
+                    for (int j = 0; j < 27; ++j) dup |= cellKey[k * 32 + j] == key;
+                }
+                if (dup) cellList[g * 32 + lane].y = 0u;
+            }
+            __syncwarp();
+        }
+#pragma unroll 1
         for (int g = 0; g < G; ++g) {
-            nCand += (unsigned long long)cc[g] * (unsigned)min(G, n - base);
-            unsigned nonEmpty = __ballot_sync(0xffffffffu, cc[g] != 0u);
+            const uint2 mine = cellList[g * 32 + lane];
+            nCand += (unsigned long long)mine.y * (unsigned)min(G, n - base);
+            unsigned nonEmpty = __ballot_sync(0xffffffffu, mine.y != 0u);
             while (nonEmpty) {
                 const int c = __ffs(nonEmpty) - 1;
                 nonEmpty &= nonEmpty - 1;
-                const uint32_t cend = __shfl_sync(0xffffffffu, cs[g] + cc[g], c);
-                uint32_t q = __shfl_sync(0xffffffffu, cs[g], c) + lane;
+                const uint2 cell = cellList[g * 32 + c];
+                const uint32_t cend = cell.x + cell.y;
+                uint32_t q = cell.x + lane;
                 // lanes strided over the cell's photons; the next trip's two words are requested before this trip's tests
-                float4 A = make_float4(0.f, 0.f, 0.f, 0.f); uint4 B = make_uint4(0u, 0u, 0u, 0u);
-                if (q < cend) { A = __ldg(ph.a + q); B = __ldg(ph.b + q); }
-                for (; q < cend; q += 32) {
-                    const float4 Ac = A; const uint4 Bc = B;
-                    if (q + 32 < cend) { A = __ldg(ph.a + q + 32); B = __ldg(ph.b + q + 32); }
+                // (two trips per loop turn, so the double buffer needs no register moves)
+                auto test = [&](const float4 Ac, const uint4 Bc) {
                     const float2 wxy = unpackHalf2(__float_as_uint(Ac.w)), wzb = unpackHalf2(Bc.x), byz = unpackHalf2(Bc.y);
 #pragma unroll
                     for (int k = 0; k < G; ++k) {
@@ -667,6 +696,20 @@ __global__ void __launch_bounds__(kMergeThreads) bdMergeLambert(SceneView sc, Bd
                             sum[k].x = fmaf(wzb.y, w, sum[k].x); sum[k].y = fmaf(byz.x, w, sum[k].y); sum[k].z = fmaf(byz.y, w, sum[k].z);
                             ++nAcc;
                         }
+                    }
+                };
+                if (q < cend) {
+                    float4 A0 = __ldg(ph.a + q), A1; uint4 B0 = __ldg(ph.b + q), B1;
+                    while (true) {
+                        const bool more1 = q + 32 < cend;
+                        if (more1) { A1 = __ldg(ph.a + q + 32); B1 = __ldg(ph.b + q + 32); }
+                        test(A0, B0);
+                        if (!more1) break;
+                        const bool more2 = q + 64 < cend;
+                        if (more2) { A0 = __ldg(ph.a + q + 64); B0 = __ldg(ph.b + q + 64); }
+                        test(A1, B1);
+                        if (!more2) break;
+                        q += 64;
                     }
                 }
             }
@@ -702,12 +745,12 @@ NV_D V3 mergeOne(const BdParams& P, const MergeCtx& c, uint32_t q) {
     const V3 wiPhoton(wxy.x, wxy.y, wzb.x);                 // photon -> its previous vertex, world space
     const V3 beta(wzb.y, byz.x, byz.y);
     V3 photonPrevToPhotonL = c.fr.toLocal(-wiPhoton);
-    float eyeRev = bsdfPdf(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
-    float lightRev = bsdfPdf(c.sh, -c.toPrevL, -photonPrevToPhotonL, 1.0f);
+    float eyeRev = bdPdf(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
+    float lightRev = bdPdf(c.sh, -c.toPrevL, -photonPrevToPhotonL, 1.0f);
     float wEye = c.eyeDvcmOverEta + eyeRev * c.eyeDvm;
     float wLight = lightDvcmOverEta + lightRev * lightDvm;
     float w = __fdividef(1.0f, 1.0f + wEye + wLight);
-    V3 f = bsdfEval(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
+    V3 f = bdEval(c.sh, photonPrevToPhotonL, c.toPrevL, 1.0f);
     return applyWeight(P, beta * f * c.scale, w);
 }
 
@@ -780,26 +823,28 @@ __global__ void __launch_bounds__(kMergeThreads) bdMerge(SceneView sc, BdState s
     if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0) atomicAdd(&st.stats[6], (unsigned long long)n);
 }
 
-// ---- coarse spatial binning of a group's Lambert merge records (counting sort on a 64^3 Morton grid over the scene box) ----------
+// ---- spatial binning of a group's Lambert merge records (counting sort: coarse Morton grid over the scene box + cell sub-bin) ----
 // The record count lives on the device, so these kernels are grid-stride over cnt[BC_MERGE] and need no host round trip.
-NV_D uint32_t mortonSpread6(uint32_t v) {            // 6 bits -> every third bit
+NV_D uint32_t mortonSpread(uint32_t v) {            // up to 8 bits -> every third bit
     v = (v | (v << 8)) & 0x300Fu; v = (v | (v << 4)) & 0x30C3u; v = (v | (v << 2)) & 0x9249u;
     return v;
 }
-NV_D uint32_t mergeBinOf(const MergeBins& b, float4 p) {
+NV_D uint32_t mergeBinOf(const MergeBins& b, const GridParams& g, float4 p) {
     const int hi = (1 << kMergeBinBits) - 1;
     int ix = min(max((int)((p.x - b.minX) * b.sx), 0), hi), iy = min(max((int)((p.y - b.minY) * b.sy), 0), hi), iz = min(max((int)((p.z - b.minZ) * b.sz), 0), hi);
-    return mortonSpread6(ix) | (mortonSpread6(iy) << 1) | (mortonSpread6(iz) << 2);
+    const int3 c = gridIndex(p.x, p.y, p.z, g);
+    const uint32_t sub = (73856093u * (unsigned)c.x ^ 19349663u * (unsigned)c.y ^ 83492791u * (unsigned)c.z) >> 7;
+    return ((mortonSpread(ix) | (mortonSpread(iy) << 1) | (mortonSpread(iz) << 2)) << kMergeSubBits) | (sub & ((1u << kMergeSubBits) - 1u));
 }
-__global__ void bdMergeBinCount(MergeQueue mq, MergeBins b, uint32_t* __restrict__ binCount) {
+__global__ void bdMergeBinCount(MergeQueue mq, MergeBins b, GridParams g, uint32_t* __restrict__ binCount) {
     const int n = min(mq.cnt[BC_MERGE], mq.cap);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        atomicAdd(&binCount[mergeBinOf(b, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u);
+        atomicAdd(&binCount[mergeBinOf(b, g, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u);
 }
-__global__ void bdMergeBinScatter(MergeQueue mq, MergeBins b, uint32_t* __restrict__ binStart, int* __restrict__ order) {
+__global__ void bdMergeBinScatter(MergeQueue mq, MergeBins b, GridParams g, uint32_t* __restrict__ binStart, int* __restrict__ order) {
     const int n = min(mq.cnt[BC_MERGE], mq.cap);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        order[atomicAdd(&binStart[mergeBinOf(b, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u)] = i;
+        order[atomicAdd(&binStart[mergeBinOf(b, g, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u)] = i;
 }
 
 // ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------

@@ -48,8 +48,12 @@ struct __align__(16) BdMergeRec { float4 p_pix, n_mat, toPrev_dvcm, beta_dvm, uv
 // coarse Morton grid before the gather so that neighbouring warps read the same photon cells (L2 instead of HBM).
 struct MergeQueue { BdMergeRec* recs; int cap; int* cnt; const int* order; };
 constexpr int kMergeGroup = 4;
-constexpr int kMergeBinBits = 6;                       // bins per axis = 64, Morton-interleaved
-constexpr int kMergeBins = 1 << (3 * kMergeBinBits);
+// bin key = Morton code of a coarse 32^3 grid over the scene box (neighbouring bins -> neighbouring photon cells, L2 reuse),
+// then 6 bits of the vertex's own hash-grid cell, so that consecutive records of a bin mostly share their centre cell and
+// the 4-vertex gather sweeps one 27-cell neighbourhood for all four
+constexpr int kMergeBinBits = 5;
+constexpr int kMergeSubBits = 6;
+constexpr int kMergeBins = 1 << (3 * kMergeBinBits + kMergeSubBits);
 struct MergeBins { float minX, minY, minZ, sx, sy, sz; };
 
 // merge-ready photons in cell order, written by bdReorderPhotons, as two dense 16 B streams so that a warp's candidate loads are

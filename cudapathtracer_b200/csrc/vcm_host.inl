@@ -84,7 +84,7 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     if (e.mode == BD_MODE_VCM) {
         A((void**)&s.mergeQ, n * (size_t)(1 + kMergeGroup) * sizeof(BdMergeRec));
         A((void**)&s.mergeOrder, n * (size_t)kMergeGroup * sizeof(int));
-        A((void**)&s.mergeBinCount, ((size_t)kMergeBins + 1024) * sizeof(uint32_t));
+        A((void**)&s.mergeBinCount, ((size_t)kMergeBins + 2048) * sizeof(uint32_t));
     }
     A((void**)&s.counters, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int));
     A((void**)&s.stats, 8 * sizeof(unsigned long long));
@@ -148,6 +148,19 @@ static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
 namespace nv {
 
 static inline int bdGrid() { return smCount() * 8; }
+
+// bdMergeLambert<MIS, G, MINB>: MINB = resident CTAs per SM the register allocation is held to (5: ~90 registers, 6: 80, 8: 64)
+template <bool MIS, int G>
+static void launchMergeLambertMG(int ctas, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P, const MergeQueue& mq) {
+    if (ctas >= 8) bdMergeLambert<MIS, G, 8><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+    else if (ctas >= 6) bdMergeLambert<MIS, G, 6><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+    else bdMergeLambert<MIS, G, 5><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+}
+static void launchMergeLambert(bool mis, int G, int ctas, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P,
+                               const MergeQueue& mq) {
+    if (mis) { if (G == 1) launchMergeLambertMG<true, 1>(ctas, grid, s, sc, st, P, mq); else launchMergeLambertMG<true, 4>(ctas, grid, s, sc, st, P, mq); }
+    else { if (G == 1) launchMergeLambertMG<false, 1>(ctas, grid, s, sc, st, P, mq); else launchMergeLambertMG<false, 4>(ctas, grid, s, sc, st, P, mq); }
+}
 
 // light pass of iteration `iter` for this rank's rows: fills the light-vertex cache, appends photons to this rank's slab,
 // splats the t = 1 connections into `colors`
@@ -227,6 +240,7 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
     ++e.launches; bdTick(e, 1);
     const int grid = bdGrid();
     static const int mergeCtas = [] { const char* v = getenv("NOVUM_MERGE_CTAS"); int k = v ? atoi(v) : 0; return k >= 1 && k <= 16 ? k : 8; }();
+    static const bool mergeG1Deep = getenv("NOVUM_MERGE_G1_DEEP") != nullptr;     // A/B knob: one vertex per warp on the binned queues
     const int mgrid = smCount() * mergeCtas;         // merge kernels: 128 threads, 8 CTAs per SM (tuning knob: NOVUM_MERGE_CTAS)
     const bool shadows = P.nee || P.connection;
     const bool merging = e.mode == BD_MODE_VCM && P.doMerge && P.mergeRadius > 0.0f;
@@ -251,22 +265,17 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
         if (merging && flush) {
             if (grouped && !P.paintWeight) {
                 cudaMemsetAsync(st.mergeBinCount, 0, kMergeBins * sizeof(uint32_t), s);
-                bdMergeBinCount<<<grid, 256, 0, s>>>(mq, P.bins, st.mergeBinCount);
+                bdMergeBinCount<<<grid, 256, 0, s>>>(mq, P.bins, P.grid, st.mergeBinCount);
                 int scanLaunches = 0;
                 exclusiveScanU32(st.mergeBinCount, kMergeBins, st.mergeBinCount + kMergeBins, s, &scanLaunches);
-                bdMergeBinScatter<<<grid, 256, 0, s>>>(mq, P.bins, st.mergeBinCount, st.mergeOrder);
+                bdMergeBinScatter<<<grid, 256, 0, s>>>(mq, P.bins, P.grid, st.mergeBinCount, st.mergeOrder);
                 e.launches += 2 + scanLaunches;
                 mq.order = st.mergeOrder;
             }
+            const bool mergeG1 = grouped && mergeG1Deep;
             // Lambert vertices (front of the queue) and all other materials (back): a kernel whose queue is empty exits at once
             if (P.paintWeight) {}
-            else if (P.doMis) {
-                if (grouped) bdMergeLambert<true, 1><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-                else bdMergeLambert<true, 4><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-            } else {
-                if (grouped) bdMergeLambert<false, 1><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-                else bdMergeLambert<false, 4><<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-            }
+            else launchMergeLambert(P.doMis != 0, mergeG1 ? 1 : 4, mergeCtas, mgrid, s, sc, st, P, mq);
             bdMerge<<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
             e.launches += P.paintWeight ? 1 : 2; bdTick(e, 3);
         }

@@ -182,13 +182,18 @@ int novum_render(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera*
     if (!s) return NOVUM_E_NOSCENE;
     if (!cfg || !colors) return NOVUM_E_ARG;
     size_t bytes = sizeof(float4) * (size_t)cfg->width * cfg->height;
-    float4* d = nullptr;
-    cudaError_t e = cudaMalloc(&d, bytes);
-    if (e != cudaSuccess) return (int)e;
+    if (s->frameBytes < bytes) {          // the device framebuffer lives with the scene: no allocation per call
+        cudaFree(s->d_frame); s->d_frame = nullptr; s->frameBytes = 0;
+        cudaError_t e = cudaMalloc(&s->d_frame, bytes);
+        if (e != cudaSuccess) return (int)e;
+        s->frameBytes = bytes;
+    }
+    float4* d = (float4*)s->d_frame;
     cudaMemsetAsync(d, 0, bytes, s->stream);
     int rc = novum_render_device(s, cfg, cam, firstSample, numSample, shard, seed, (NovumFloat4*)d, stats);
-    if (rc == 0) rc = (int)cudaMemcpy(colors, d, bytes, cudaMemcpyDeviceToHost);
-    cudaFree(d);
+    // `colors` may be pageable or page-locked host memory; page-locked (cudaHostAlloc / cudaHostRegister) copies at full PCIe rate
+    if (rc == 0) rc = (int)cudaMemcpyAsync(colors, d, bytes, cudaMemcpyDeviceToHost, s->stream);
+    if (rc == 0) rc = (int)cudaStreamSynchronize(s->stream);
     return rc;
 }
 
