@@ -43,9 +43,10 @@ struct __align__(16) BdShadowRec { float4 o_maxT; float4 d_pix; float4 contrib_s
 struct __align__(16) BdMergeRec { float4 p_pix, n_mat, toPrev_dvcm, beta_dvm, uv; };      // 80 B
 
 // where one eye step appends its merge records and what the merge kernels consume: Lambert vertices from the front
-// (cnt[BC_MERGE]), every other material from the back (cnt[BC_MERGE_GEN]). Step 0 (primary hits, already coherent in pixel
-// order) is merged at once; deeper steps share a queue per group of kMergeGroup steps, whose Lambert records are binned on a
-// coarse Morton grid before the gather so that neighbouring warps read the same photon cells (L2 instead of HBM).
+// (cnt[BC_MERGE]), every other material from the back (cnt[BC_MERGE_GEN]). Step 0 (primary hits) is merged at once; deeper
+// steps share a queue per group of kMergeGroup steps. The Lambert records of a queue are binned (coarse Morton grid + cell
+// sub-bin) before the gather so that neighbouring warps read the same photon cells (L2 instead of HBM) and the 4 vertices a
+// warp gathers together mostly share one 27-cell neighbourhood.
 struct MergeQueue { BdMergeRec* recs; int cap; int* cnt; const int* order; };
 constexpr int kMergeGroup = 4;
 // bin key = Morton code of a coarse 32^3 grid over the scene box (neighbouring bins -> neighbouring photon cells, L2 reuse),

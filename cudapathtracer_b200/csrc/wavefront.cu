@@ -7,6 +7,9 @@
 namespace nv {
 
 constexpr int kWfThreads = 128;
+#ifndef NOVUM_TRAV_MINB
+#define NOVUM_TRAV_MINB 8          // resident CTAs per SM the traversal kernels' register allocation is held to (64 registers)
+#endif
 
 __device__ __forceinline__ int laneId() { return threadIdx.x & 31; }
 
@@ -57,7 +60,7 @@ __global__ void wfInit(WfState st, int n) {
 // Rays stream through the warp's lanes with per-lane refill (trav_stream.cuh). Finished paths are staged in a per-warp
 // shared buffer and binned 32 at a time with one ballot-aggregated atomic per class present, as before.
 template <bool COUNT>
-__global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st, const int* __restrict__ queue, TravCounters cnt) {
+__global__ void __launch_bounds__(kWfThreads, NOVUM_TRAV_MINB) wfExtend(SceneView sc, WfState st, const int* __restrict__ queue, TravCounters cnt) {
     __shared__ uint2 stackMem[kSmemStack * kWfThreads];
     __shared__ int2 stage[kWfThreads / 32][64];
     __shared__ int stageCnt[kWfThreads / 32];
@@ -109,7 +112,7 @@ __global__ void __launch_bounds__(kWfThreads) wfExtend(SceneView sc, WfState st,
 }
 
 // ---- shadow: any-hit for every queued NEE connection; unoccluded ones add their contribution --------------
-__global__ void __launch_bounds__(kWfThreads) wfShadow(SceneView sc, WfState st, float4* __restrict__ colors) {
+__global__ void __launch_bounds__(kWfThreads, NOVUM_TRAV_MINB) wfShadow(SceneView sc, WfState st, float4* __restrict__ colors) {
     __shared__ uint2 stackMem[kSmemStack * kWfThreads];
     TravStack ts; ts.init(stackMem + threadIdx.x, kWfThreads);
     const int lane = laneId();

@@ -74,6 +74,7 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
         wfInit<<<(pool + 255) / 256, 256, 0, stream>>>(st, pool);
         ++launches;
         const int grid = smCount() * 8;
+        const int tgrid = smCount() * NOVUM_TRAV_MINB;      // traversal kernels: one wave of resident CTAs
         int cur = 0;
         // Batches of kBatch iterations are enqueued back to back; the "anything left?" counter of batch b is read while
         // batch b+1 is already queued, so the GPU never waits for the host (one surplus batch of no-op launches at the end).
@@ -83,14 +84,14 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
             mark();
             if (iter > 0) {
                 wfAdvance<<<1, 32, 0, stream>>>(st.counters);
-                if (profCount) wfExtend<true><<<grid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
-                else wfExtend<false><<<grid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
+                if (profCount) wfExtend<true><<<tgrid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
+                else wfExtend<false><<<tgrid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
                 launches += 2; stageLaunches[0] += 1; stageLaunches[3] += 1;
             }
             mark();
             wfShade<<<grid, kWfThreads, 0, stream>>>(sc, st, P, st.extendQ[cur ^ 1]);
             mark();
-            wfShadow<<<grid, kWfThreads, 0, stream>>>(sc, st, d_colors);
+            wfShadow<<<tgrid, kWfThreads, 0, stream>>>(sc, st, d_colors);
             mark();
             launches += 2; stageLaunches[1] += 1; stageLaunches[2] += 1;
             cur ^= 1;
