@@ -211,7 +211,10 @@ NV_D bool shadeNaive(const SceneView& sc, const WfParams& P, PathRegs& p, const 
     return p.depth < P.maxDepth;
 }
 
-__global__ void __launch_bounds__(kWfThreads) wfShade(SceneView sc, WfState st, WfParams P, int* __restrict__ nextQueue) {
+#ifndef NOVUM_SHADE_MINB
+#define NOVUM_SHADE_MINB 5
+#endif
+__global__ void __launch_bounds__(kWfThreads, NOVUM_SHADE_MINB) wfShade(SceneView sc, WfState st, WfParams P, int* __restrict__ nextQueue) {
     const int lane = laneId();
     int cnt[NUM_CLS], chunkStart[NUM_CLS + 1];
     chunkStart[0] = 0;

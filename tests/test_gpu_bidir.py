@@ -61,6 +61,42 @@ def test_against_reference_render(name, cornell):
     assert rel_mse(block(img), block(ref)) < 0.02
 
 
+# scenes with delta materials (dielectric water slab, glass dragon): fixtures of tests/golden/make_golden_scenes.py
+DELTA_CASES = [("water", 12, "unidirectional", 0), ("water", 12, "bdpt", 1), ("water", 12, "vcm", 3), ("water", 12, "sppm", 4),
+               ("rainbow", 8, "vcm", 3)]
+
+
+@pytest.mark.parametrize("scene_name,detail,name,integ", DELTA_CASES)
+def test_delta_scenes_against_reference_render(scene_name, detail, name, integ, tmp_path):
+    """Caustic paths through specular interfaces: the reference's own render of the same stand-in scene is the oracle.
+    Tolerances: mean radiance within 4 %, relMSE of 4x4-block averages <= 0.05 (caustic fixtures are noisier than Cornell's,
+    and the reference's firefly clamp makes single pixels heavy-tailed), non-finite reference pixels masked."""
+    path = os.path.join(GOLD, f"{scene_name}_render_{name}.npz")
+    assert os.path.exists(path), f"{path} missing: run tests/golden/make_golden_scenes.py on the GPU box"
+    z = np.load(path)
+    spp, ref = int(z["spp"]), z["img"]
+    h, w = ref.shape[:2]
+    d = str(tmp_path / scene_name)
+    nb.make_scene(scene_name, d, int(z["detail"]))
+    scene = nb.Scene.from_config(os.path.join(d, "configs", "config.rendertron"))
+    try:
+        cfg = _cfg(scene, w, h, integ)
+        cam = nb.camera_make(cfg)
+        img, st = scene.render(cfg, cam, 0, spp)
+    finally:
+        scene.close()
+    img = img[..., :3] / spp
+    assert np.isfinite(img).all() and (img >= 0).all()
+    ok = np.isfinite(ref).all(axis=2)
+    assert ok.mean() > 0.99
+    ref = np.where(ok[..., None], ref, 0.0); img = np.where(ok[..., None], img, 0.0)
+    hb, wb = h - h % 4, w - w % 4
+    r = rel_mse(block(img[:hb, :wb]), block(ref[:hb, :wb]))
+    print(scene_name, name, "mean ours", img.mean(), "ref", ref.mean(), "relMSE(4x4)", r)
+    assert abs(img.mean() - ref.mean()) < 0.04 * ref.mean(), (img.mean(), ref.mean())
+    assert r < 0.05
+
+
 @pytest.mark.parametrize("integ", [3, 1, 4])
 def test_iteration_striping_composes(integ, cornell):
     """novum_render_device stripes whole iterations over ranks: the ranks' frames sum to the single-GPU frame."""
