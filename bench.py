@@ -162,7 +162,7 @@ def run_ours(args):
     S = args.spp_per_step or wl["spp"]
     colors = torch.zeros((h, w, 4), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > L2 (126 MB)
-    tiler = nd.TileRenderer(scene, cfg, cam, dist) if tiles else None
+    tiler = nd.TileRenderer(scene, cfg, cam, dist, exchange=args.exchange) if tiles else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def step(i, profile=0):
@@ -289,7 +289,7 @@ def run_ours(args):
             "config": {"workload": wl["desc"], "scene": args.workload, "tris": info["tris"], "bvh8_nodes": info["bvh8_nodes"],
                        "width": w, "height": h, "passes_per_step_per_gpu": S, "max_depth": cfg.maxDepth,
                        "eye_depth": cfg.bdptEyeDepth, "light_depth": cfg.bdptLightDepth,
-                       "sharding": ("pixel rows striped over ranks, photon slabs all-gathered (NCCL) every iteration, frames sum-reduced at the end"
+                       "sharding": (f"pixel rows striped over ranks, photons exchanged every iteration ({tiler.exchange_mode}), frames sum-reduced at the end"
                                     if tiles else "sample passes / iterations striped over ranks, frames sum-reduced (NCCL) at the end"),
                        "l2": "256 MB flush between steps; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
                        "scene_load_s": round(load_s, 3)},
@@ -388,6 +388,7 @@ def main():
     ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS))
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
     ap.add_argument("--sharding", default="striped", choices=["striped", "tiles"])
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="tiles sharding: photon exchange by peer stores fused into the light pass, or by an NCCL all-gather")
     ap.add_argument("--detail", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -137,6 +137,10 @@ def _declare(L):
     L.novum_vcm_eye_pass.argtypes = [vp, ci, vp]
     L.novum_vcm_stats.argtypes = [vp, C.POINTER(RenderStats)]
     L.novum_vcm_stream.argtypes = [vp, C.POINTER(vp)]
+    L.novum_vcm_ipc_export.argtypes = [vp, vp]
+    L.novum_vcm_ipc_attach.argtypes = [vp, ci, vp]
+    L.novum_vcm_peer_write.argtypes = [vp, ci]
+    L.novum_vcm_attach_pointer.argtypes = [vp, ci, vp]
 
 
 def _check(rc, what):
@@ -372,6 +376,22 @@ class VcmSession:
         s = C.c_void_p()
         _check(lib().novum_vcm_stream(self.h, C.byref(s)), "novum_vcm_stream")
         return s.value
+
+    def ipc_export(self):
+        """64-byte CUDA IPC handle of this rank's slab buffer (to be carried to the other ranks' processes)."""
+        buf = C.create_string_buffer(64)
+        _check(lib().novum_vcm_ipc_export(self.h, C.cast(buf, C.c_void_p)), "novum_vcm_ipc_export")
+        return bytes(buf.raw)
+
+    def ipc_attach(self, peer_rank, handle):
+        buf = C.create_string_buffer(bytes(handle), 64)
+        _check(lib().novum_vcm_ipc_attach(self.h, peer_rank, C.cast(buf, C.c_void_p)), "novum_vcm_ipc_attach")
+
+    def attach_pointer(self, peer_rank, d_base):
+        _check(lib().novum_vcm_attach_pointer(self.h, peer_rank, C.c_void_p(d_base)), "novum_vcm_attach_pointer")
+
+    def peer_write(self, enable=True):
+        _check(lib().novum_vcm_peer_write(self.h, 1 if enable else 0), "novum_vcm_peer_write")
 
     def slabs_tensor(self):
         """All ranks' photon slabs as one uint8 torch tensor on the current device (in-place all-gather target)."""

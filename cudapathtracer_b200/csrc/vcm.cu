@@ -325,6 +325,10 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState 
                             rec[0] = make_uint4(__float_as_uint(o.s.p.x), __float_as_uint(o.s.p.y), __float_as_uint(o.s.p.z), packOct(normalize(-inDir)));
                             rec[1] = make_uint4(packHalf2(o.currBeta.x, o.currBeta.y), packHalf2(o.currBeta.z, 0.0f), __float_as_uint(o.d_vm),
                                                 __float_as_uint(o.d_vcm));
+                            for (int k = 0; k < P.numPeers; ++k) {               // the same record into every peer's copy of this slab (NVLink stores)
+                                uint4* prec = P.peerSlab[k] + (kSlabHeaderBytes / 16) + (size_t)idx * 2;
+                                prec[0] = rec[0]; prec[1] = rec[1];
+                            }
                             ++nPhot;
                         }
                     }
@@ -845,6 +849,15 @@ __global__ void bdMergeBinScatter(MergeQueue mq, MergeBins b, GridParams g, uint
     const int n = min(mq.cnt[BC_MERGE], mq.cap);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         order[atomicAdd(&binStart[mergeBinOf(b, g, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u)] = i;
+}
+
+// end of a peer-write light pass: publish this rank's photon count in every peer's copy of the slab header
+__global__ void bdPushHeader(BdParams P) {
+    if (threadIdx.x < P.numPeers) {
+        uint4 h = *P.slab;
+        *P.peerSlab[threadIdx.x] = h;
+        __threadfence_system();
+    }
 }
 
 // ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------

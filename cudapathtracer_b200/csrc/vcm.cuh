@@ -32,6 +32,7 @@ namespace nv {
 enum : int { BD_MODE_VCM = 0, BD_MODE_BDPT = 1 };
 constexpr int kMaxBdDepth = 32;          // eye / light depth limit of the wavefront counters
 constexpr int kSlabHeaderBytes = 32;
+constexpr int kMaxPeers = 15;            // world <= 16
 
 // per (pass, depth) counters; one memset per pass clears them all
 // BC_MERGE counts the Lambert merge records (front of mergeQ), BC_MERGE_GEN the records of every other material (back of mergeQ)
@@ -98,6 +99,11 @@ struct BdParams {
     // photons
     uint4* slab;                       // this rank's slab (header + records), append target of the light pass
     int slabCap;
+    // peer-write exchange (tile-sharded multi-GPU): this rank's slab inside every OTHER rank's slab buffer, mapped through
+    // CUDA IPC over NVLink. The light pass stores each photon record locally and into all peers, so the all-gather is done
+    // when the light pass is (no separate collective; only a stream-ordered barrier before the grid build).
+    uint4* peerSlab[kMaxPeers];
+    int numPeers;
     PhotonSoA photons;                 // records in cell order (eye pass), merge-ready
     const uint32_t* cellStart; const uint32_t* cellEnd;
     GridParams grid;

@@ -15,6 +15,9 @@ struct BdEngine {
     NovumRenderConfig cfg{};
     // photons: `world` slabs (this rank appends into slab `rank`), compacted copy, cell-ordered copy
     uint4* slabs = nullptr; size_t slabWords = 0; int slabCap = 0;
+    void* peerBase[16] = {nullptr};       // other ranks' slab buffers (index = rank), null = not attached
+    bool peerIpc[16] = {false};           // opened through CUDA IPC here (to be closed), else a pointer the caller owns
+    bool peerWrite = false;               // light pass stores photons into the peers as it appends them
     uint4* photonsAll = nullptr; uint4* photonsSorted = nullptr;
     int maxPhotons = 0, photonCount = 0;
     HashGridDevice grid;
@@ -45,6 +48,7 @@ static void bdFree(BdEngine& e) {
     cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.dv); cudaFree(s.rng); cudaFree(s.hit);
     cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
     cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.mergeOrder); cudaFree(s.mergeBinCount); cudaFree(s.counters); cudaFree(s.stats);
+    for (int r = 0; r < 16; ++r) if (e.peerBase[r] && e.peerIpc[r]) cudaIpcCloseMemHandle(e.peerBase[r]);
     cudaFree(e.slabs); cudaFree(e.photonsAll); cudaFree(e.photonsSorted); cudaFree(e.d_counts);
     if (e.h_counts) cudaFreeHost(e.h_counts);
     if (e.gridAllocated) hashGridFree(e.grid);
@@ -129,6 +133,10 @@ static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
     P.seed = e.seed; P.iter = iter; P.rank = e.rank; P.world = e.world; P.nLocal = e.nLocal;
     P.colors = colors;
     P.slab = e.slabs + (size_t)e.rank * e.slabWords; P.slabCap = e.slabCap;
+    P.numPeers = 0;
+    if (e.peerWrite)
+        for (int r = 0; r < e.world; ++r)
+            if (r != e.rank && e.peerBase[r]) P.peerSlab[P.numPeers++] = (uint4*)e.peerBase[r] + (size_t)e.rank * e.slabWords;
     for (int k = 0; k < 3; ++k) {
         float ext = e.scene->sceneMax[k] - e.scene->sceneMin[k];
         (&P.bins.minX)[k] = e.scene->sceneMin[k];
@@ -172,7 +180,10 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
     e.mergeRadius = P.mergeRadius;
     cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
     cudaMemsetAsync(P.slab, 0, kSlabHeaderBytes, s);                      // photon counter of this rank (deviceCode.cu:3330)
-    if (e.nLocal == 0 || sc.numLights == 0) return 0;
+    if (e.nLocal == 0 || sc.numLights == 0) {
+        if (P.numPeers > 0) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; }
+        return (int)cudaGetLastError();
+    }
     const int numSteps = e.mode == BD_MODE_BDPT ? e.lightDepth - 1 : e.lightDepth;      // :1116 (depth 1..max-1) vs :2029 (0..max-1)
     bdTick(e, 1);
     bdLightStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(sc, st, P);
@@ -190,6 +201,7 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
         e.launches += 2;
     }
     if (numSteps == 0 && P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, st.counters); ++e.launches; bdTick(e, 2); }
+    if (P.numPeers > 0) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; bdTick(e, 1); }
     return (int)cudaGetLastError();
 }
 
@@ -406,6 +418,49 @@ int novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats) {
     if (err != cudaSuccess) return (int)err;
     nv::bdFillStats(v->e, stats);
     stats->photons = (uint64_t)v->e.photonCount;      // photons in the last grid (all ranks)
+    return 0;
+}
+
+/* Peer-write exchange: every rank exports its slab buffer (64-byte CUDA IPC handle), the caller moves the handles between the
+   processes (any transport: torch.distributed all_gather_object, MPI, a pipe) and attaches them; novum_vcm_peer_write(1) then
+   makes each light pass store its photons into all attached peers as it appends them. The caller must order the ranks between
+   light pass and grid build, and between grid build and the next light pass (a tiny collective on novum_vcm_stream). */
+int novum_vcm_ipc_export(NovumVcmState* v, void* handle64) {
+    if (!v || !handle64) return NOVUM_E_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    cudaIpcMemHandle_t h;
+    cudaError_t err = cudaIpcGetMemHandle(&h, v->e.slabs);
+    if (err != cudaSuccess) return (int)err;
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+
+int novum_vcm_ipc_attach(NovumVcmState* v, int peerRank, const void* handle64) {
+    if (!v || !handle64 || peerRank < 0 || peerRank >= v->e.world || peerRank == v->e.rank) return NOVUM_E_ARG;
+    if (v->e.peerBase[peerRank]) return 0;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    cudaError_t err = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (err != cudaSuccess) { cudaGetLastError(); return (int)err; }
+    v->e.peerBase[peerRank] = p; v->e.peerIpc[peerRank] = true;
+    return 0;
+}
+
+/* same-process form (ranks that are sessions of one process, on one GPU or on peer-enabled GPUs): attach by device pointer */
+int novum_vcm_attach_pointer(NovumVcmState* v, int peerRank, void* d_peerCacheBase) {
+    if (!v || !d_peerCacheBase || peerRank < 0 || peerRank >= v->e.world || peerRank == v->e.rank) return NOVUM_E_ARG;
+    if (v->e.peerBase[peerRank] && v->e.peerIpc[peerRank]) cudaIpcCloseMemHandle(v->e.peerBase[peerRank]);
+    v->e.peerBase[peerRank] = d_peerCacheBase; v->e.peerIpc[peerRank] = false;
+    return 0;
+}
+
+int novum_vcm_peer_write(NovumVcmState* v, int enable) {
+    if (!v) return NOVUM_E_ARG;
+    if (enable)
+        for (int r = 0; r < v->e.world; ++r)
+            if (r != v->e.rank && !v->e.peerBase[r]) return NOVUM_E_ARG;      // every peer must be attached first
+    v->e.peerWrite = enable != 0;
     return 0;
 }
 

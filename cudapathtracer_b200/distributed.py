@@ -68,9 +68,15 @@ def exchange_slabs(dist, slabs, rank, world, slab_bytes):
 
 
 class TileRenderer:
-    """Tile-sharded bidirectional render: keeps the per-rank session (buffers, slabs) alive across calls."""
+    """Tile-sharded bidirectional render: keeps the per-rank session (buffers, slabs) alive across calls.
 
-    def __init__(self, scene, cfg, cam, dist=None, seed=103033):
+    exchange="p2p" (default for world > 1): the ranks swap CUDA IPC handles of their slab buffers once; every light pass
+    then stores its photons into all peers over NVLink while it appends them (the all-gather is fused into the light-pass
+    kernels), and the only collectives left are two 4-byte all-reduces per iteration that order the ranks on the engine's
+    stream. exchange="nccl": light pass, then an NCCL all-gather of the used slab prefixes (`exchange_slabs`). Falls back to
+    "nccl" when IPC mapping is not available."""
+
+    def __init__(self, scene, cfg, cam, dist=None, seed=103033, exchange="p2p"):
         import torch
         self.torch, self.dist = torch, dist
         self.rank, self.world = shard_of(dist)
@@ -80,9 +86,41 @@ class TileRenderer:
         self.ext_stream = torch.cuda.ExternalStream(self.session.stream())
         self.exchanged_bytes = 0
         self.last_exchange_bytes = 0
+        self.exchange_mode = "none" if self.world == 1 else exchange
+        self.flag = torch.zeros(1, dtype=torch.int32, device=self.slabs.device) if self.world > 1 else None
+        if self.exchange_mode == "p2p":
+            self.exchange_mode = "p2p" if self._attach_peers() else "nccl"
+
+    def _attach_peers(self):
+        """Swap IPC handles over the process group and map every peer's slab buffer; all ranks agree on the outcome."""
+        dist = self.dist
+        handles = [None] * self.world
+        dist.all_gather_object(handles, self.session.ipc_export())
+        ok = 1
+        try:
+            for r, h in enumerate(handles):
+                if r != self.rank:
+                    self.session.ipc_attach(r, h)
+            self.session.peer_write(True)
+        except nb.NovumError:
+            ok = 0
+        t = self.torch.tensor([ok], dtype=self.torch.int32, device=self.slabs.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        if int(t.item()) == 0:
+            try:
+                self.session.peer_write(False)
+            except nb.NovumError:
+                pass
+            return False
+        return True
 
     def close(self):
         self.session.close()
+
+    def _order_ranks(self):
+        """Stream-ordered rendezvous: completes on a rank only after every rank's preceding work on its engine stream."""
+        with self.torch.cuda.stream(self.ext_stream):
+            self.dist.all_reduce(self.flag)
 
     def exchange(self):
         """All-gather of this iteration's photons on the engine's own stream (behind the light pass, ahead of the grid build)."""
@@ -93,18 +131,25 @@ class TileRenderer:
 
     def iteration(self, it, colors):
         s = self.session
-        s.light_pass(it, colors.data_ptr())
-        if self.world > 1:
-            # the collective runs on the engine's own stream, right behind the light pass and ahead of the grid build
+        s.light_pass(it, colors.data_ptr())           # p2p: also writes this rank's photons + count into every peer
+        if self.exchange_mode == "p2p":
+            self._order_ranks()                       # all light passes (and their peer stores) are complete
+        elif self.exchange_mode == "nccl":
             self.exchange()
-        s.build_grid(it)
+        s.build_grid(it)                              # reads all slabs (host reads the counts here)
+        if self.exchange_mode == "p2p":
+            self._order_ranks()                       # nobody overwrites a slab a peer is still compacting
         s.eye_pass(it, colors.data_ptr())
 
     def render(self, first, count, colors):
         for it in range(first, first + count):
             self.iteration(it, colors)
         nb.lib().novum_sync()
-        return self.session.stats()
+        st = self.session.stats()
+        if self.exchange_mode == "p2p":               # bytes stored into peers + received from them, last iteration
+            self.last_exchange_bytes = PHOTON_BYTES * int(st.photons)
+            self.exchanged_bytes += self.last_exchange_bytes * count
+        return st
 
 
 def frame_to_host(colors):

@@ -293,6 +293,15 @@ int  novum_vcm_eye_pass(NovumVcmState* v, int iter, NovumFloat4* d_colors);
 int  novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats);
 /* the CUDA stream (cudaStream_t) the passes are enqueued on, so the caller can order its collective after the light pass */
 int  novum_vcm_stream(NovumVcmState* v, void** stream);
+/* Peer-write exchange (the fused form of "light pass -> all-gather"): every rank exports its slab buffer as a 64-byte CUDA
+ * IPC handle, the caller carries the handles between the processes and attaches them, and with peer_write enabled each
+ * light pass stores every photon record into its own slab AND into all peers' copies of it over NVLink as it appends them,
+ * then publishes its count in the peers' headers. No collective moves photon data; the caller only orders the ranks with a
+ * tiny stream-ordered collective (a) between light pass and grid build and (b) between grid build and the next light pass. */
+int  novum_vcm_ipc_export(NovumVcmState* v, void* handle64);
+int  novum_vcm_ipc_attach(NovumVcmState* v, int peerRank, const void* handle64);
+int  novum_vcm_attach_pointer(NovumVcmState* v, int peerRank, void* d_peerCacheBase);   /* same-process ranks: novum_vcm_cache_buffer's base of the peer */
+int  novum_vcm_peer_write(NovumVcmState* v, int enable);
 int  novum_sync(void);
 
 /* ---- synthetic scene generator (stand-ins for the reference's LFS-pointer OBJ files) ----- */

@@ -111,6 +111,45 @@ def test_iteration_striping_composes(integ, cornell):
     assert np.allclose(full, a + b, rtol=2e-3, atol=1e-4)
 
 
+@pytest.mark.parametrize("integ,world", [(3, 2), (3, 3), (4, 2)])
+def test_peer_write_exchange_equals_single_gpu(integ, world, cornell):
+    """Peer-write form of the tile-sharded exchange: every session's light pass stores its photons (and its count) straight
+    into the other sessions' slab buffers — attached by device pointer here, by CUDA IPC handle across processes — so no copy
+    happens between light pass and grid build. The image must equal the single-GPU image."""
+    import torch
+    cfg = _cfg(cornell, 48, 30, integ)
+    cam = nb.camera_make(cfg)
+    iters = 4
+    full, _ = cornell.render(cfg, cam, 0, iters)
+    sessions = [nb.VcmSession(cornell, cfg, cam, rank=r, world=world) for r in range(world)]
+    frames = [torch.zeros((cfg.height, cfg.width, 4), dtype=torch.float32, device="cuda") for _ in range(world)]
+    sync = nb.lib().novum_sync
+    try:
+        with pytest.raises(nb.NovumError):
+            sessions[0].peer_write(True)              # refused until every peer is attached
+        for r, s in enumerate(sessions):
+            for q, o in enumerate(sessions):
+                if q != r:
+                    s.attach_pointer(q, o.base)
+            s.peer_write(True)
+        for it in range(iters):
+            for r, s in enumerate(sessions):
+                s.light_pass(it, frames[r].data_ptr())
+            sync()                                    # (across processes: a stream-ordered 4-byte all-reduce)
+            counts = [int(s.slabs_tensor()[q * s.slab_bytes:q * s.slab_bytes + 4].view(torch.int32)[0]) for s in sessions for q in range(world)]
+            assert counts[:world] * world == counts   # every session sees the same per-rank photon counts
+            for r, s in enumerate(sessions):
+                s.build_grid(it)
+                s.eye_pass(it, frames[r].data_ptr())
+            sync()
+        total = sum(f.cpu().numpy() for f in frames)
+        assert sessions[0].stats().photons > 0
+    finally:
+        for s in sessions:
+            s.close()
+    assert np.allclose(total, full, rtol=2e-3, atol=1e-4)
+
+
 @pytest.mark.parametrize("integ,world", [(3, 2), (3, 3), (4, 2), (1, 2)])
 def test_tile_sharded_phases_equal_single_gpu(integ, world, cornell):
     """The phase API with `world` ranks emulated on one GPU (slabs copied between the sessions where NCCL's all-gather
