@@ -47,6 +47,15 @@ __global__ void compactMaterialsKernel(const NovumMaterial* __restrict__ in, DMa
     out[i] = d;
 }
 
+__global__ void shadeTriKernel(const NovumTriangle* __restrict__ tris, const float4* __restrict__ normals, const float2* __restrict__ uvs,
+                               int n, float4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    TriRecord t = loadTri(tris, i);
+    packShadeTri(out + (size_t)i * kShadeTriWords, V3(__ldg(normals + t.na)), V3(__ldg(normals + t.nb)), V3(__ldg(normals + t.nc)),
+                 __ldg(uvs + t.uva), __ldg(uvs + t.uvb), __ldg(uvs + t.uvc), t.mat, t.emission, t.lightInd);
+}
+
 int ensureStage(NovumScene* s, size_t bytes) {
     if (bytes <= s->stageBytes) return 0;
     if (s->d_stage) cudaFree(s->d_stage);
@@ -69,6 +78,8 @@ int sceneFinalize(NovumScene* s) {
     if ((e = cudaMalloc(&s->d_queueCounter, 4 * sizeof(int))) != cudaSuccess) return (int)e;
     e = buildBvh8(s->d_positions, s->d_tris, s->nTri, s->d_mats, s->stream, s->bvh);
     if (e != cudaSuccess) return (int)e;
+    if ((e = cudaMalloc(&s->d_shadeTris, sizeof(float4) * kShadeTriWords * (size_t)s->nTri)) != cudaSuccess) return (int)e;
+    shadeTriKernel<<<(s->nTri + 127) / 128, 128, 0, s->stream>>>(s->d_tris, s->d_normals, s->d_uvs, s->nTri, s->d_shadeTris);
     // main.cu:532-535: centre / radius / min of the root box
     for (int k = 0; k < 3; ++k) { s->sceneMin[k] = s->bvh.boundsMin[k]; s->sceneMax[k] = s->bvh.boundsMax[k]; }
     float c[3], d2 = 0.f;
@@ -120,7 +131,7 @@ SceneView NovumScene::view() const {
     SceneView v;
     v.bvh.nodes = bvh.nodes; v.bvh.tris = bvh.tris; v.bvh.numNodes = bvh.numNodes; v.bvh.numTris = bvh.numTris;
     v.positions = d_positions; v.normals = d_normals; v.uvs = d_uvs;
-    v.tris = d_tris; v.lights = d_lights; v.mats = d_mats; v.textures = d_textures;
+    v.tris = d_tris; v.shadeTris = d_shadeTris; v.lights = d_lights; v.mats = d_mats; v.textures = d_textures;
     v.numTris = nTri; v.numLights = nLights; v.numMats = nMat;
     for (int k = 0; k < 3; ++k) { v.sceneMin[k] = sceneMin[k]; v.sceneCenter[k] = sceneCenter[k]; }
     v.sceneRadius = sceneRadius;
@@ -197,7 +208,7 @@ void novum_scene_destroy(NovumScene* s) {
         cudaFree(s->d_positions); cudaFree(s->d_normals); cudaFree(s->d_uvs); cudaFree(s->d_tris);
         cudaFree(s->d_lights); cudaFree(s->d_matsRef); cudaFree(s->d_textures);
     }
-    cudaFree(s->d_frame);
+    cudaFree(s->d_frame); cudaFree(s->d_shadeTris);
     cudaFree(s->d_mats); cudaFree(s->d_counters); cudaFree(s->d_queueCounter); cudaFree(s->d_stage);
     freeBvh8(s->bvh);
     if (s->ev0) { cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); }

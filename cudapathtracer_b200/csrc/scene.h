@@ -13,6 +13,7 @@ struct NovumScene {
     float4* d_normals = nullptr;
     float2* d_uvs = nullptr;
     NovumTriangle* d_tris = nullptr;
+    float4* d_shadeTris = nullptr;        // nv::packShadeTri records, built by sceneFinalize (owned by the scene in every creation path)
     NovumTriangle* d_lights = nullptr;
     NovumMaterial* d_matsRef = nullptr;   // 176 B reference-layout table
     nv::DMat* d_mats = nullptr;           // compact table

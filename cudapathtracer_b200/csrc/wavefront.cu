@@ -80,13 +80,13 @@ __global__ void __launch_bounds__(kWfThreads, NOVUM_TRAV_MINB) wfExtend(SceneVie
     unsigned traced = streamClosest<COUNT>(sc.bvh, ts, n, &st.counters[C_FETCH_EXTEND], cnt,
         [&](int i, V3& o, V3& d) {
             int slot = __ldg(queue + i);
-            float4 ro = st.rayO[slot], rd = st.rayD[slot];
+            float4 ro = st.slots[(size_t)slot * kSlotWords + W_RAYO], rd = st.slots[(size_t)slot * kSlotWords + W_RAYD];
             o = V3(ro.x, ro.y, ro.z); d = V3(rd.x, rd.y, rd.z);
         },
         [&](int i, const HitRec& h) {
             int slot = __ldg(queue + i);
-            st.hit[slot] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
-            st.hitFlags[slot] = h.flags;
+            st.slots[(size_t)slot * kSlotWords + W_HIT] = make_float4(__int_as_float(h.tri), h.t, h.u, h.v);
+            st.slots[(size_t)slot * kSlotWords + W_AUX].x = __int_as_float(h.flags);
             int cls = h.tri < 0 ? CLS_REGEN : classOfMaterial(sc.mats, h.flags & 0xffff);
             stage[warp][atomicAdd(&stageCnt[warp], 1)] = make_int2(slot, cls);
         },

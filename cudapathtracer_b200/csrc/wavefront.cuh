@@ -28,16 +28,17 @@ enum : int {
 
 struct ShadowRec { float4 o_maxT; float4 d_pix; float4 contrib; };   // 48 B
 
+// One 128 B line per path slot (queues hand out slots in material-class order, i.e. at random: with one array per field a
+// 16 B access used half of every 32 B sector it touched; a line per slot makes every sector fully used):
+//   sector 0  W_RAYO  xyz origin, w = pdf of the last BSDF sample      W_RAYD  xyz direction, w = bits: depth (low 16) | flags (high 16)
+//   sector 1  W_HIT   bits tri, t, u, v                                 W_AUX   x = triangle flags of the hit (material id in the low 16 bits), z,w = RNG state
+//   sector 2  W_BETA  xyz throughput, w = bits: pixel index             W_PREVP xyz last true-hit point (neePDF needs it), w = bits: medium stack top
+//   sector 3  W_MEDIUM 16 x u8 medium stack (deviceCode.cu:306 keeps 16 ints)       (spare)
+// Extend reads sector 0 and writes W_HIT + the flags word of sector 1; shade reads the line and writes sectors 0-3.
+enum : int { W_RAYO = 0, W_RAYD = 1, W_HIT = 2, W_AUX = 3, W_BETA = 4, W_PREVP = 5, W_MEDIUM = 6, kSlotWords = 8 };
+
 struct WfState {
-    // per path slot
-    float4* rayO;        // xyz origin, w = pdf of the last BSDF sample
-    float4* rayD;        // xyz direction, w = bits: depth (low 16) | flags (high 16)
-    float4* beta;        // xyz throughput, w = bits: pixel index
-    float4* prevP;       // xyz last true-hit point (neePDF needs it), w = bits: medium stack top
-    uint4* medium;       // 16 x u8 medium stack (deviceCode.cu:306 keeps 16 ints)
-    unsigned long long* rng;
-    float4* hit;         // bits tri, t, u, v
-    int* hitFlags;       // triangle flags of the hit (material id in the low 16 bits)
+    float4* slots;       // capacity x kSlotWords
     // queues
     int* extendQ[2];
     int* classQ;         // NUM_CLS x capacity

@@ -16,9 +16,7 @@ static int wfAlloc(WfEngine& e, int capacity) {
     cudaError_t err = cudaSuccess;
     auto A = [&](void** p, size_t b) { if (err == cudaSuccess) { err = cudaMalloc(p, b); e.bytes += b; } };
     size_t n = (size_t)capacity;
-    A((void**)&s.rayO, n * sizeof(float4)); A((void**)&s.rayD, n * sizeof(float4)); A((void**)&s.beta, n * sizeof(float4));
-    A((void**)&s.prevP, n * sizeof(float4)); A((void**)&s.medium, n * sizeof(uint4)); A((void**)&s.rng, n * sizeof(unsigned long long));
-    A((void**)&s.hit, n * sizeof(float4)); A((void**)&s.hitFlags, n * sizeof(int));
+    A((void**)&s.slots, n * kSlotWords * sizeof(float4));
     A((void**)&s.extendQ[0], n * sizeof(int)); A((void**)&s.extendQ[1], n * sizeof(int));
     A((void**)&s.classQ, n * NUM_CLS * sizeof(int)); A((void**)&s.shadowQ, n * sizeof(ShadowRec));
     A((void**)&s.counters, C_TOTAL * sizeof(int)); A((void**)&s.rayCounters, 4 * sizeof(unsigned long long));
@@ -31,8 +29,7 @@ static int wfAlloc(WfEngine& e, int capacity) {
 
 static void wfFree(WfEngine& e) {
     WfState& s = e.st;
-    cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.medium); cudaFree(s.rng);
-    cudaFree(s.hit); cudaFree(s.hitFlags); cudaFree(s.extendQ[0]); cudaFree(s.extendQ[1]); cudaFree(s.classQ); cudaFree(s.shadowQ);
+    cudaFree(s.slots); cudaFree(s.extendQ[0]); cudaFree(s.extendQ[1]); cudaFree(s.classQ); cudaFree(s.shadowQ);
     cudaFree(s.counters); cudaFree(s.rayCounters);
     if (e.pinnedCounters) cudaFreeHost(e.pinnedCounters);
     for (int i = 0; i < 2; ++i) if (e.evRead[i]) cudaEventDestroy(e.evRead[i]);

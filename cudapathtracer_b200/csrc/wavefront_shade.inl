@@ -40,23 +40,26 @@ struct PathRegs {
 };
 
 NV_D void loadPath(const WfState& st, int slot, PathRegs& p) {
-    float4 a = st.rayO[slot], b = st.rayD[slot], c = st.beta[slot], e = st.prevP[slot];
-    uint4 m = st.medium[slot];
+    const float4* w = st.slots + (size_t)slot * kSlotWords;
+    float4 a = w[W_RAYO], b = w[W_RAYD], c = w[W_BETA], e = w[W_PREVP], x = w[W_AUX];
+    uint4 m = *reinterpret_cast<const uint4*>(w + W_MEDIUM);
     p.o = V3(a.x, a.y, a.z); p.pdf = a.w;
     p.d = V3(b.x, b.y, b.z);
     unsigned df = __float_as_uint(b.w); p.depth = (int)(df & 0xffffu); p.flags = df & 0xffff0000u;
     p.beta = V3(c.x, c.y, c.z); p.pix = __float_as_int(c.w);
     p.prevP = V3(e.x, e.y, e.z); p.ms.top = __float_as_int(e.w);
     p.ms.w[0] = m.x; p.ms.w[1] = m.y; p.ms.w[2] = m.z; p.ms.w[3] = m.w;
-    p.rng.state = st.rng[slot];
+    p.rng.state = (unsigned long long)__float_as_uint(x.z) | ((unsigned long long)__float_as_uint(x.w) << 32);
 }
 NV_D void storePath(const WfState& st, int slot, const PathRegs& p) {
-    st.rayO[slot] = make_float4(p.o.x, p.o.y, p.o.z, p.pdf);
-    st.rayD[slot] = make_float4(p.d.x, p.d.y, p.d.z, __uint_as_float(((unsigned)p.depth & 0xffffu) | p.flags));
-    st.beta[slot] = make_float4(p.beta.x, p.beta.y, p.beta.z, __int_as_float(p.pix));
-    st.prevP[slot] = make_float4(p.prevP.x, p.prevP.y, p.prevP.z, __int_as_float(p.ms.top));
-    st.medium[slot] = make_uint4(p.ms.w[0], p.ms.w[1], p.ms.w[2], p.ms.w[3]);
-    st.rng[slot] = p.rng.state;
+    float4* w = st.slots + (size_t)slot * kSlotWords;
+    w[W_RAYO] = make_float4(p.o.x, p.o.y, p.o.z, p.pdf);
+    w[W_RAYD] = make_float4(p.d.x, p.d.y, p.d.z, __uint_as_float(((unsigned)p.depth & 0xffffu) | p.flags));
+    w[W_BETA] = make_float4(p.beta.x, p.beta.y, p.beta.z, __int_as_float(p.pix));
+    w[W_PREVP] = make_float4(p.prevP.x, p.prevP.y, p.prevP.z, __int_as_float(p.ms.top));
+    *reinterpret_cast<uint4*>(w + W_MEDIUM) = make_uint4(p.ms.w[0], p.ms.w[1], p.ms.w[2], p.ms.w[3]);
+    // the RNG state shares a word with the hit flags extend writes: store only its two lanes
+    *reinterpret_cast<float2*>(&w[W_AUX].z) = make_float2(__uint_as_float((unsigned)p.rng.state), __uint_as_float((unsigned)(p.rng.state >> 32)));
 }
 
 // A non-finite sample (e.g. the NEE weight inf/inf when the shading point lies exactly in the light's plane, deviceCode.cu:468-471)
@@ -239,8 +242,9 @@ __global__ void __launch_bounds__(kWfThreads, NOVUM_SHADE_MINB) wfShade(SceneVie
         PathRegs p;
         if (valid && cls != CLS_REGEN) {
             loadPath(st, slot, p);
-            float4 hf = st.hit[slot];
-            HitRec h; h.tri = __float_as_int(hf.x); h.t = hf.y; h.u = hf.z; h.v = hf.w; h.flags = st.hitFlags[slot];
+            float4 hf = st.slots[(size_t)slot * kSlotWords + W_HIT];
+            HitRec h; h.tri = __float_as_int(hf.x); h.t = hf.y; h.u = hf.z; h.v = hf.w;
+            h.flags = __float_as_int(st.slots[(size_t)slot * kSlotWords + W_AUX].x);
             alive = P.naive ? shadeNaive(sc, P, p, h) : shadeMIS(sc, st, P, p, h, h.flags);
             if (!alive) ++finished;
         } else if (valid && cls == CLS_REGEN) {
