@@ -11,6 +11,7 @@ namespace nv {
 struct Bvh8Device {
     float4* nodes = nullptr;     // 5 float4 per node
     float4* tris = nullptr;      // 3 float4 per triangle (BVH order)
+    size_t bytes = 0;            // size of the one allocation holding nodes, then triangles
     int numNodes = 0;
     int numTris = 0;             // == scene triangle count
     float boundsMin[3] = {0, 0, 0};   // root box of the padded triangle boxes (main.cu:29-41 pads by 1e-6 as well)

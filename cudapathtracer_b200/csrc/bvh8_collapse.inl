@@ -180,7 +180,7 @@ __global__ void collapseKernel(Bvh2View b2, const uint2* __restrict__ tasksIn, i
 }  // namespace
 
 void freeBvh8(Bvh8Device& b) {
-    cudaFree(b.nodes); cudaFree(b.tris);
+    cudaFree(b.nodes);          // nodes and triangles share one allocation (tris points into it)
     b = Bvh8Device();
 }
 
@@ -250,9 +250,15 @@ cudaError_t buildBvh8(const float4* d_positions, const NovumTriangle* d_tris, in
     out.numNodes = hostCounters[1];
     out.numTris = n;
     if (hostCounters[2] != n) { /* every triangle must land in exactly one leaf slot */ return cudaErrorAssert; }
-    NV_CK(cudaMalloc(&out.nodes, sizeof(float4) * 5 * (size_t)out.numNodes));
-    NV_CK(cudaMemcpyAsync(out.nodes, nodesTmp, sizeof(float4) * 5 * (size_t)out.numNodes, cudaMemcpyDeviceToDevice, stream));
-    out.tris = trisOut;
+    // nodes and triangles in ONE allocation, so that a single L2 access-policy window can cover the whole structure
+    {
+        size_t nodeWords = ((size_t)5 * out.numNodes + 7) & ~(size_t)7;          // keep the triangle array 128 B aligned
+        out.bytes = sizeof(float4) * (nodeWords + 3 * (size_t)n);
+        NV_CK(cudaMalloc(&out.nodes, out.bytes));
+        out.tris = out.nodes + nodeWords;
+        NV_CK(cudaMemcpyAsync(out.nodes, nodesTmp, sizeof(float4) * 5 * (size_t)out.numNodes, cudaMemcpyDeviceToDevice, stream));
+        NV_CK(cudaMemcpyAsync(out.tris, trisOut, sizeof(float4) * 3 * (size_t)n, cudaMemcpyDeviceToDevice, stream));
+    }
     uint32_t hb[18];
     NV_CK(cudaMemcpyAsync(hb, bounds, sizeof(hb), cudaMemcpyDeviceToHost, stream));
     NV_CK(cudaEventRecord(ev1, stream));
@@ -264,7 +270,7 @@ cudaError_t buildBvh8(const float4* d_positions, const NovumTriangle* d_tris, in
     radixSortPlanDestroy(plan);
     cudaFree(triLo); cudaFree(triHi); cudaFree(nodeLo); cudaFree(nodeHi); cudaFree(bounds); cudaFree(keys); cudaFree(vals);
     cudaFree(left); cudaFree(right); cudaFree(parent); cudaFree(rfirst); cudaFree(rlast); cudaFree(flags); cudaFree(counters);
-    cudaFree(tasksA); cudaFree(tasksB); cudaFree(nodesTmp);
+    cudaFree(tasksA); cudaFree(tasksB); cudaFree(nodesTmp); cudaFree(trisOut);
     return cudaGetLastError();
 }
 
