@@ -165,3 +165,56 @@ def test_full_size_dragon_properties(tmp_path_factory, rng):
         _assert_bit_equal(hits[few], o.trace_brute(rays[few]))          # ~1.3 G triangle tests on the host cores
     finally:
         s.close()
+
+
+# ---- full size: the 871k-triangle dragon stand-in of BASELINE configs[1] / configs[4] -------------------------------------------
+@pytest.fixture(scope="module")
+def full_dragon(built, tmp_path_factory):
+    d = str(tmp_path_factory.mktemp("dragon_full"))
+    nb.make_scene("dragon", d, 100)
+    s = nb.Scene.from_config(os.path.join(d, "configs", "config.rendertron"))
+    yield s, d
+    s.close()
+
+
+def test_full_size_dragon_bit_exact_vs_brute_force(full_dragon, rng):
+    """871k triangles: a sample of camera, incoherent and secondary rays against the brute-force oracle (every triangle
+    tested, no acceleration structure): ids exact, t/u/v bit-equal."""
+    from oracle.oracle_binding import OracleScene
+    from scene_utils import load_scene_py
+    s, d = full_dragon
+    cfg, pos, nrm, uv, tris, mats = load_scene_py(d)
+    assert len(tris) > 800_000
+    o = OracleScene(pos, nrm, uv, tris, mats, None, 2)
+    info = s.info()
+    cam = nb.camera_make(s.cfg)
+    prim = camera_rays(cam, s.cfg.width, s.cfg.height, 1500, rng)
+    inco = random_rays(info["min"], info["max"], 1500, rng)
+    sec = secondary_rays(prim, s.trace_closest(prim), pos, nrm, tris, rng)
+    for rays in (prim, inco, sec):
+        _assert_bit_equal(s.trace_closest(rays), o.trace_brute(rays))
+
+
+def test_full_size_closest_and_any_hit_agree(full_dragon, rng):
+    """Size-independent property at full size, 1M rays: the any-hit kernel sees exactly what the closest-hit kernel sees.
+    A shadow ray stopped just short of the closest hit is unoccluded; one that reaches past it is blocked (the dragon scene
+    has no attenuating MAT_LEAF surfaces); rays that hit nothing are unoccluded at any length."""
+    s, _ = full_dragon
+    info = s.info()
+    cam = nb.camera_make(s.cfg)
+    rays = np.concatenate([camera_rays(cam, s.cfg.width, s.cfg.height, 500_000, rng), random_rays(info["min"], info["max"], 500_000, rng)])
+    hit = s.trace_closest(rays)
+    h = hit["tri"] >= 0
+    assert 0.2 < h.mean() < 1.0
+    t = np.where(h, hit["t"], np.float32(1e4)).astype(np.float32)
+    short = s.trace_shadow(rays, (t * np.float32(1 - 1e-4)).astype(np.float32))
+    long_ = s.trace_shadow(rays, (t * np.float32(1 + 1e-4) + np.float32(1e-4)).astype(np.float32))
+    assert np.all(short[:, :3] == 1.0)                       # nothing in front of the closest hit
+    assert np.all(long_[h, :3] == 0.0)                       # the closest hit itself blocks
+    assert np.all(long_[~h, :3] == 1.0)
+    # skipping the closest triangle (the reference's skipTri argument) never blocks earlier than the next surface
+    skip = hit["tri"].astype(np.int32)
+    skipped = s.trace_shadow(rays, (t * np.float32(1 + 1e-4) + np.float32(1e-4)).astype(np.float32), skip)
+    assert np.all((skipped[:, :3] == 0.0) | (skipped[:, :3] == 1.0))
+    assert np.all(skipped[~h, :3] == 1.0)
+    assert (skipped[h, 0] == 1.0).mean() > 0.5              # most rays meet nothing else within 1e-4 t of the hit
