@@ -577,6 +577,8 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
 //                   expensive part - two reverse pdfs, the BSDF value, the VM MIS weight - always runs on full warps.
 constexpr int kMergeThreads = 128;
 constexpr int kMergeWarps = kMergeThreads / 32;
+constexpr int kMergeCtasPerSm = 8;        // 64 registers per thread; the 90-register build at 5 CTAs/SM was 14 % slower
+constexpr int kMergeGather = 4;           // eye vertices a warp gathers together
 
 struct MergeCells { uint32_t cs, cc; };     // per lane (< 27): first photon and photon count of its neighbour cell
 
@@ -612,8 +614,8 @@ NV_D void mergeSplat(const BdParams& P, int pix, V3 sum, int lane) {
 // bandwidth limit the one-vertex-per-warp form sits on. A photon within r of a vertex always lies in one of that vertex's own
 // 27 cells, so testing a vertex against the cells of its neighbours adds only rejected candidates; table slots are de-duplicated
 // across the union (the reference visits a slot twice when two of a vertex's neighbour cells collide in the table, p ~ 1e-6).
-template <bool MIS, int G, int MINB>
-__global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
+template <bool MIS>
+__global__ void __launch_bounds__(kMergeThreads, kMergeCtasPerSm) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
     int* cnt = mq.cnt;
     const int lane = bdLane();
     const int n = min(cnt[BC_MERGE], mq.cap);
@@ -622,8 +624,8 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
     const float invEta = 1.0f / P.etaVcm;
     const PhotonSoA ph = P.photons;
     const unsigned ltMask = (1u << lane) - 1u;
-    __shared__ uint2 cellListAll[kMergeWarps][G * 32];
-    __shared__ uint32_t cellKeyAll[kMergeWarps][G * 32];
+    __shared__ uint2 cellListAll[kMergeWarps][kMergeGather * 32];
+    __shared__ uint32_t cellKeyAll[kMergeWarps][kMergeGather * 32];
     uint2* cellList = cellListAll[threadIdx.x >> 5];
     uint32_t* cellKey = cellKeyAll[threadIdx.x >> 5];
     unsigned long long nCand = 0;
@@ -631,16 +633,16 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
     while (true) {
         __syncwarp();
         int base = 0;
-        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], G);
+        if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], kMergeGather);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n) break;
-        V3 eyeP[G], nPi[G], sum[G];
-        float C[G];
-        int recIdx[G];
+        V3 eyeP[kMergeGather], nPi[kMergeGather], sum[kMergeGather];
+        float C[kMergeGather];
+        int recIdx[kMergeGather];
         // the group's cell list lives in shared memory (entry g * 32 + lane = {first photon, count} of vertex g's neighbour
         // `lane`), so the sweep below exists once in the code and walks the list with a dynamic index
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
+        for (int g = 0; g < kMergeGather; ++g) {
             // a short last group repeats its last record (its result is dropped below)
             const int r = min(base + g, n - 1);
             recIdx[g] = mq.order ? __ldg(mq.order + r) : r;
@@ -657,10 +659,10 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
             cellList[g * 32 + lane] = make_uint2(mc.cs, mc.cc);
         }
         __syncwarp();
-        if (G > 1) {
+        if (kMergeGather > 1) {
             // drop table slots already listed by an earlier lane of the same vertex or by an earlier vertex of the group
 #pragma unroll 1
-            for (int g = 0; g < G; ++g) {
+            for (int g = 0; g < kMergeGather; ++g) {
                 const uint32_t key = cellKey[g * 32 + lane];
                 bool dup = (__match_any_sync(0xffffffffu, key) & ltMask) != 0u;
 #pragma unroll 1
@@ -674,9 +676,9 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
             __syncwarp();
         }
 #pragma unroll 1
-        for (int g = 0; g < G; ++g) {
+        for (int g = 0; g < kMergeGather; ++g) {
             const uint2 mine = cellList[g * 32 + lane];
-            nCand += (unsigned long long)mine.y * (unsigned)min(G, n - base);
+            nCand += (unsigned long long)mine.y * (unsigned)min(kMergeGather, n - base);
             unsigned nonEmpty = __ballot_sync(0xffffffffu, mine.y != 0u);
             while (nonEmpty) {
                 const int c = __ffs(nonEmpty) - 1;
@@ -689,7 +691,7 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
                 auto test = [&](const float4 Ac, const uint4 Bc) {
                     const float2 wxy = unpackHalf2(__float_as_uint(Ac.w)), wzb = unpackHalf2(Bc.x), byz = unpackHalf2(Bc.y);
 #pragma unroll
-                    for (int k = 0; k < G; ++k) {
+                    for (int k = 0; k < kMergeGather; ++k) {
                         const float dx = eyeP[k].x - Ac.x, dy = eyeP[k].y - Ac.y, dz = eyeP[k].z - Ac.z;
                         if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= r2) {
                             float w = 1.0f;
@@ -719,7 +721,7 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
             }
         }
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
+        for (int g = 0; g < kMergeGather; ++g) {
             if (base + g >= n) break;
             const float4* rp = reinterpret_cast<const float4*>(mq.recs + recIdx[g]);
             const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r3 = __ldg(rp + 3), r4 = __ldg(rp + 4);

@@ -157,17 +157,10 @@ namespace nv {
 
 static inline int bdGrid() { return smCount() * 8; }
 
-// bdMergeLambert<MIS, G, MINB>: MINB = resident CTAs per SM the register allocation is held to (5: ~90 registers, 6: 80, 8: 64)
-template <bool MIS, int G>
-static void launchMergeLambertMG(int ctas, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P, const MergeQueue& mq) {
-    if (ctas >= 8) bdMergeLambert<MIS, G, 8><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-    else if (ctas >= 6) bdMergeLambert<MIS, G, 6><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-    else bdMergeLambert<MIS, G, 5><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-}
-static void launchMergeLambert(bool mis, int G, int ctas, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P,
-                               const MergeQueue& mq) {
-    if (mis) { if (G == 1) launchMergeLambertMG<true, 1>(ctas, grid, s, sc, st, P, mq); else launchMergeLambertMG<true, 4>(ctas, grid, s, sc, st, P, mq); }
-    else { if (G == 1) launchMergeLambertMG<false, 1>(ctas, grid, s, sc, st, P, mq); else launchMergeLambertMG<false, 4>(ctas, grid, s, sc, st, P, mq); }
+// bdMergeLambert<MIS>: 4 eye vertices per warp, register allocation held to 64 (8 resident CTAs of 128 threads per SM)
+static void launchMergeLambert(bool mis, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P, const MergeQueue& mq) {
+    if (mis) bdMergeLambert<true><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+    else bdMergeLambert<false><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
 }
 
 // light pass of iteration `iter` for this rank's rows: fills the light-vertex cache, appends photons to this rank's slab,
@@ -251,9 +244,7 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
     bdEyeStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(st, P);
     ++e.launches; bdTick(e, 1);
     const int grid = bdGrid();
-    static const int mergeCtas = [] { const char* v = getenv("NOVUM_MERGE_CTAS"); int k = v ? atoi(v) : 0; return k >= 1 && k <= 16 ? k : 8; }();
-    static const bool mergeG1Deep = getenv("NOVUM_MERGE_G1_DEEP") != nullptr;     // A/B knob: one vertex per warp on the binned queues
-    const int mgrid = smCount() * mergeCtas;         // merge kernels: 128 threads, 8 CTAs per SM (tuning knob: NOVUM_MERGE_CTAS)
+    const int mgrid = smCount() * kMergeCtasPerSm;   // merge kernels: 128 threads, 8 resident CTAs per SM
     const bool shadows = P.nee || P.connection;
     const bool merging = e.mode == BD_MODE_VCM && P.doMerge && P.mergeRadius > 0.0f;
     TravCounters tc{e.scene->d_counters, e.scene->d_counters + 1};
@@ -284,10 +275,9 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
                 e.launches += 2 + scanLaunches;
                 mq.order = st.mergeOrder;
             }
-            const bool mergeG1 = grouped && mergeG1Deep;
             // Lambert vertices (front of the queue) and all other materials (back): a kernel whose queue is empty exits at once
             if (P.paintWeight) {}
-            else launchMergeLambert(P.doMis != 0, mergeG1 ? 1 : 4, mergeCtas, mgrid, s, sc, st, P, mq);
+            else launchMergeLambert(P.doMis != 0, mgrid, s, sc, st, P, mq);
             bdMerge<<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
             e.launches += P.paintWeight ? 1 : 2; bdTick(e, 3);
         }
