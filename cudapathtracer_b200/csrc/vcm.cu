@@ -52,7 +52,7 @@ NV_D V3 bdEval(const Shading& s, V3 wiToward, V3 wo, float etaI) { return bsdfEv
 NV_D float bdPdf(const Shading& s, V3 wiToward, V3 wo, float etaI) { return bsdfPdf(s, wiToward, wo, etaI); }
 #else
 NV_D V3 bdEval(const Shading& s, V3 wiToward, V3 wo, float etaI) {
-    return s.m.type == MAT_DIFFUSE ? s.m.albedo / kPi : bsdfEvalCall(s, wiToward, wo, etaI);
+    return s.m.type == MAT_DIFFUSE ? s.m.albedo * (1.0f / kPi) : bsdfEvalCall(s, wiToward, wo, etaI);
 }
 NV_D float bdPdf(const Shading& s, V3 wiToward, V3 wo, float etaI) {
     return s.m.type == MAT_DIFFUSE ? cosinePdf(wo) : bsdfPdfCall(s, wiToward, wo, etaI);
@@ -514,22 +514,23 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                                 V3 e2l = lv.p - s.p;
                                 float dSq = fmaxf(lengthSq(e2l), kRayEps);
                                 float dist = length(e2l);
-                                V3 e2lU = e2l / dist;
+                                V3 e2lU = e2l * (1.0f / dist);                       // one division instead of three
                                 float cosLight = fabsf(dot(lv.n, -e2lU)), cosEye = fabsf(dot(s.n, e2lU));
                                 if (cosLight < kEps || cosEye < kEps) continue;
+                                const float invDSq = 1.0f / dSq;
                                 Frame fl(lv.n);
                                 Shading shL = resolveShading(sc.mats, lv.mat, sc.textures, lv.uv);
                                 V3 l2eAtLight = fl.toLocal(-e2lU), toLightFromPrevAtLight = fl.toLocal(-lv.wo);
-                                float pdfEyeRevArea = bdPdf(shL, toLightFromPrevAtLight, l2eAtLight, 1.0f) * cosEye / dSq;
+                                float pdfEyeRevArea = bdPdf(shL, toLightFromPrevAtLight, l2eAtLight, 1.0f) * cosEye * invDSq;
                                 V3 l2eAtEye = fr.toLocal(-e2lU);
                                 float pdfOneBeforeEye = bdPdf(o.sh, l2eAtEye, toPrevL, 1.0f);
-                                float pdfLightRevArea = bdPdf(o.sh, -toPrevL, -l2eAtEye, 1.0f) * cosLight / dSq;
+                                float pdfLightRevArea = bdPdf(o.sh, -toPrevL, -l2eAtEye, 1.0f) * cosLight * invDSq;
                                 float pdfOneBeforeLight = bdPdf(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
                                 float wEye = pdfEyeRevArea * (eta + o.d_vcm + pdfOneBeforeEye * o.d_vc);
                                 float wLight = pdfLightRevArea * (eta + lv.d_vcm + pdfOneBeforeLight * lv.d_vc);
                                 V3 fEye = bdEval(o.sh, l2eAtEye, toPrevL, 1.0f);
                                 V3 fLight = bdEval(shL, -l2eAtLight, -toLightFromPrevAtLight, 1.0f);
-                                float G = fminf(cosEye * cosLight / dSq, 2.0f);
+                                float G = fminf(cosEye * cosLight * invDSq, 2.0f);
                                 V3 unweighted = o.currBeta * lv.beta * fEye * fLight * G;
                                 float w = 1.0f / (1.0f + wEye + wLight);
                                 pushShadow(st, cnt, s.p + s.n * kRayEps, e2lU, dist - kRayEps, -1, (unsigned)pix | clampFlag, applyWeight(P, unweighted, w));
