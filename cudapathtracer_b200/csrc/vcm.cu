@@ -141,17 +141,18 @@ NV_D float triArea(const SceneView& sc, const NovumTriangle* t) {
 
 // t = 1 strategy: connect a light-path vertex to the camera and splat (deviceCode.cu:1310-1430, :2266-2382).
 // v holds the quantised vertex; f is evaluated here unless the vertex is the point on the light itself (BDPT s = 1).
-NV_D void lightTraceSplat(const SceneView& sc, const BdState& st, const BdParams& P, int* cnt, const LightVtx& v, bool onLight, float pdfSampleY0) {
+// Returns false when there is nothing to splat; otherwise fills the deferred shadow record.
+NV_D bool prepareSplat(const SceneView& sc, const BdParams& P, const LightVtx& v, bool onLight, float pdfSampleY0, BdShadowRec& rec) {
     float rx, ry;
-    if (!worldToRaster(P.cam, v.p, rx, ry)) return;
+    if (!worldToRaster(P.cam, v.p, rx, ry)) return false;
     int px = (int)rx, py = (int)ry;
-    if (px >= P.w || py >= P.h) return;       // ndc == +1 lands one past the edge in the reference (out-of-range write there)
-    if (v.delta) return;
+    if (px >= P.w || py >= P.h) return false;       // ndc == +1 lands one past the edge in the reference (out-of-range write there)
+    if (v.delta) return false;
     V3 toCam = camOrg(P.cam) - v.p;
     V3 dirU = normalize(toCam);
     float cosAtLight = dot(v.n, dirU);
     float cosAtCamera = fabsf(dot(camFwd(P.cam), -dirU));
-    if (cosAtLight <= kEps) return;
+    if (cosAtLight <= kEps) return false;
     float A = imagePlaneArea(P);
     float We = 1.0f / (A * cosAtCamera * cosAtCamera * cosAtCamera * cosAtCamera);
     float dSq = fmaxf(lengthSq(toCam), kRayEps);
@@ -171,7 +172,20 @@ NV_D void lightTraceSplat(const SceneView& sc, const BdState& st, const BdParams
     }
     V3 contrib = v.beta * f * (G * We);
     float w = 1.0f / (1.0f + wLight);
-    pushShadow(st, cnt, v.p + v.n * kRayEps, dirU, length(toCam) - kRayEps, -1, (unsigned)(py * P.w + px), applyWeight(P, contrib, w));
+    const V3 ro = v.p + v.n * kRayEps, c = applyWeight(P, contrib, w);
+    rec.o_maxT = make_float4(ro.x, ro.y, ro.z, length(toCam) - kRayEps);
+    rec.d_pix = make_float4(dirU.x, dirU.y, dirU.z, __uint_as_float((unsigned)(py * P.w + px)));
+    rec.contrib_skip = make_float4(c.x, c.y, c.z, __int_as_float(-1));
+    return true;
+}
+NV_D void storeShadow(const BdState& st, int pos, const BdShadowRec& rec) {
+    if (pos >= st.shadowCap) return;
+    float4* out = reinterpret_cast<float4*>(st.shadowQ + pos);
+    out[0] = rec.o_maxT; out[1] = rec.d_pix; out[2] = rec.contrib_skip;
+}
+NV_D void lightTraceSplat(const SceneView& sc, const BdState& st, const BdParams& P, int* cnt, const LightVtx& v, bool onLight, float pdfSampleY0) {
+    BdShadowRec rec;
+    if (prepareSplat(sc, P, v, onLight, pdfSampleY0, rec)) storeShadow(st, bdAggAppend(&cnt[BC_SHADOW]), rec);
 }
 
 // ---- light pass -----------------------------------------------------------------------------------------------------------
@@ -296,14 +310,18 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState 
     int* nextCnt = st.counters + (step + 1) * BC_STRIDE;
     const int n = cnt[BC_QUEUE];
     unsigned long long nVerts = 0, nPhot = 0;
+    // The three appends of a packet (photon slab, splat shadow rays, next queue) are each ONE ballot-aggregated atomic at a
+    // converged point instead of an atomic per photon and per splat inside the divergent walk (profiles/r1_bdLightStep_atomics.txt).
     while (true) {
         int base = 0;
         if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_STEP], 32);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n) break;
         int i = base + lane;
-        bool cont = false;
+        bool cont = false, wantPhoton = false, wantSplat = false;
         int l = 0;
+        uint4 ph0 = make_uint4(0u, 0u, 0u, 0u), ph1 = ph0;
+        BdShadowRec splat;
         if (i < n) {
             l = __ldg(queue + i);
             float4 hf = st.hit[l];
@@ -319,20 +337,11 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState 
                     st.pathLen[l] = step + 1;
                     ++nVerts;
                     if (!o.delta && P.mode == BD_MODE_VCM && P.doMerge) {        // photon for merging (:2206-2221)
-                        int idx = bdAggAppend(reinterpret_cast<int*>(P.slab));
-                        if (idx < P.slabCap) {
-                            uint4* rec = P.slab + (kSlabHeaderBytes / 16) + (size_t)idx * 2;
-                            rec[0] = make_uint4(__float_as_uint(o.s.p.x), __float_as_uint(o.s.p.y), __float_as_uint(o.s.p.z), packOct(normalize(-inDir)));
-                            rec[1] = make_uint4(packHalf2(o.currBeta.x, o.currBeta.y), packHalf2(o.currBeta.z, 0.0f), __float_as_uint(o.d_vm),
-                                                __float_as_uint(o.d_vcm));
-                            for (int k = 0; k < P.numPeers; ++k) {               // the same record into every peer's copy of this slab (NVLink stores)
-                                uint4* prec = P.peerSlab[k] + (kSlabHeaderBytes / 16) + (size_t)idx * 2;
-                                prec[0] = rec[0]; prec[1] = rec[1];
-                            }
-                            ++nPhot;
-                        }
+                        wantPhoton = true;
+                        ph0 = make_uint4(__float_as_uint(o.s.p.x), __float_as_uint(o.s.p.y), __float_as_uint(o.s.p.z), packOct(normalize(-inDir)));
+                        ph1 = make_uint4(packHalf2(o.currBeta.x, o.currBeta.y), packHalf2(o.currBeta.z, 0.0f), __float_as_uint(o.d_vm), __float_as_uint(o.d_vcm));
                     }
-                    if (P.lightTrace) lightTraceSplat(sc, st, P, cnt, v, false, 0.0f);
+                    if (P.lightTrace) wantSplat = prepareSplat(sc, P, v, false, 0.0f, splat);
                     bool through = P.mode == BD_MODE_BDPT ? (dot(o.wiW, o.s.n) < 0.0f) : (o.wiL.z < kEps);    // :1274 vs :2229
                     p.o = through ? o.s.p - o.s.n * kRayEps : o.s.p + o.s.n * kRayEps;
                     p.d = o.wiW;
@@ -342,7 +351,19 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState 
                 }
             }
         }
-        int pos = bdWarpAppend(&nextCnt[BC_QUEUE], cont);
+        const int idx = bdWarpAppend(reinterpret_cast<int*>(P.slab), wantPhoton);
+        if (wantPhoton && idx < P.slabCap) {
+            uint4* rec = P.slab + (kSlabHeaderBytes / 16) + (size_t)idx * 2;
+            rec[0] = ph0; rec[1] = ph1;
+            for (int k = 0; k < P.numPeers; ++k) {               // the same record into every peer's copy of this slab (NVLink stores)
+                uint4* prec = P.peerSlab[k] + (kSlabHeaderBytes / 16) + (size_t)idx * 2;
+                prec[0] = ph0; prec[1] = ph1;
+            }
+            ++nPhot;
+        }
+        const int spos = bdWarpAppend(&cnt[BC_SHADOW], wantSplat);
+        if (wantSplat) storeShadow(st, spos, splat);
+        const int pos = bdWarpAppend(&nextCnt[BC_QUEUE], cont);
         if (cont) nextQueue[pos] = l;
     }
     for (int o = 16; o > 0; o >>= 1) { nVerts += __shfl_xor_sync(0xffffffffu, nVerts, o); nPhot += __shfl_xor_sync(0xffffffffu, nPhot, o); }
