@@ -73,8 +73,13 @@ NV_D void storeLightVtx(const BdState& st, size_t idx, LightVtx& v) {
     float2 a = unpackHalf2(bxy), b = unpackHalf2(bz), c = unpackHalf2(puv);
     v.beta = V3(a.x, a.y, b.x); v.uv = c;
 }
-NV_D LightVtx loadLightVtx(const BdState& st, size_t idx) {
-    uint4 A = __ldg(st.lvA + idx), B = __ldg(st.lvB + idx), C = __ldg(st.lvC + idx);
+struct LightVtxRaw { uint4 A, B, C; };
+NV_D LightVtxRaw fetchLightVtx(const BdState& st, size_t idx) {
+    LightVtxRaw r; r.A = __ldg(st.lvA + idx); r.B = __ldg(st.lvB + idx); r.C = __ldg(st.lvC + idx);
+    return r;
+}
+NV_D LightVtx decodeLightVtx(const LightVtxRaw& r) {
+    const uint4 A = r.A, B = r.B, C = r.C;
     LightVtx v;
     v.p = V3(__uint_as_float(A.x), __uint_as_float(A.y), __uint_as_float(A.z));
     v.n = unpackOct(A.w); v.wo = unpackOct(B.x);
@@ -84,6 +89,7 @@ NV_D LightVtx loadLightVtx(const BdState& st, size_t idx) {
     v.d_vc = __uint_as_float(C.y); v.d_vcm = __uint_as_float(C.z);
     return v;
 }
+NV_D LightVtx loadLightVtx(const BdState& st, size_t idx) { return decodeLightVtx(fetchLightVtx(st, idx)); }
 
 struct BdPath {
     V3 o, d, beta, prevP;
@@ -453,6 +459,9 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                     bool endPath = false;
                     V3 sum(0.0f);
                     if (!o.delta) {
+                        // first light vertex of this pixel: requested here so that the fetch overlaps the s = 0 / s = 1 strategies
+                        const int len = P.connection ? st.pathLen[l] : 0;
+                        LightVtxRaw raw = fetchLightVtx(st, (size_t)l);
                         const unsigned clampFlag = vcm ? SR_CLAMP : 0u;
                         const float pdfChoose = 1.0f / (float)(P.sampleEnv ? sc.numLights + 1 : sc.numLights);
                         // vector from this vertex back to the previous one as the reference hands it to the BSDFs:
@@ -528,9 +537,12 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                         }
                         // ---- s >= 2: connect to every stored vertex of this pixel's light path (connectGeneral :2549-2684, connectPath :1653-1762) ----
                         if (P.connection) {
-                            const int len = st.pathLen[l];
+                            // the next vertex's three words are requested before this one is decoded and connected: the wait
+                            // for them was 30 % of this kernel's stall samples
                             for (int k = 0; k < len; ++k) {
-                                LightVtx lv = loadLightVtx(st, (size_t)k * P.nLocal + l);
+                                const LightVtxRaw cur = raw;
+                                if (k + 1 < len) raw = fetchLightVtx(st, (size_t)(k + 1) * P.nLocal + l);
+                                LightVtx lv = decodeLightVtx(cur);
                                 if (lv.delta) continue;
                                 V3 e2l = lv.p - s.p;
                                 float dSq = fmaxf(lengthSq(e2l), kRayEps);
