@@ -120,7 +120,14 @@ def _declare(L):
     L.novum_render.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), ci, ci, Shard, C.c_uint64, vp, C.POINTER(RenderStats)]
     L.novum_render_device.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), ci, ci, Shard, C.c_uint64, vp, C.POINTER(RenderStats)]
     L.novum_make_scene.argtypes = [C.c_char_p, C.c_char_p, ci]
-    L.novum_save_bmp.argtypes = [C.c_char_p, vp, ci, ci, cf, ci]
+    L.novum_save_bmp.argtypes = [C.c_char_p, vp, vp, ci, ci, ci, ci, ci]
+    L.novum_bmp_row_bytes.argtypes = [ci]
+    L.novum_frame_finish_device.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp, vp]
+    L.novum_frame_finish.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp]
+    L.novum_frame_save_bmp.argtypes = [C.c_char_p, vp, vp, ci, ci, ci, ci, ci]
+    L.novum_write_bmp.argtypes = [C.c_char_p, vp, ci, ci]
+    L.novum_frame_last_ms.argtypes = [C.POINTER(cf)]
+    L.novum_frame_gamma_steps.argtypes = [vp]
     L.novum_save_pfm.argtypes = [C.c_char_p, vp, ci, ci, cf]
     L.novum_hashgrid_create.argtypes = [ci, C.POINTER(vp)]
     L.novum_hashgrid_destroy.argtypes = [vp]
@@ -281,6 +288,54 @@ class Scene:
         _check(lib().novum_render_device(self.h, C.byref(cfg), C.byref(cam), first_sample, num_sample, Shard(rank, world), seed,
                                          C.c_void_p(d_colors), C.byref(st)), "novum_render_device")
         return st
+
+
+FRAME_PROGRESSIVE, FRAME_FINAL = 0, 1
+
+
+def bmp_row_bytes(w):
+    return lib().novum_bmp_row_bytes(int(w))
+
+
+def frame_finish(colors, overlay, sample_count, mode=FRAME_FINAL, post_process=True, want_final=False):
+    """Host accumulator (h, w, 4) float32 [+ overlay] -> packed BGR rows (h, row_bytes) uint8 exactly as Image::saveImageBMP writes
+    them (imageUtil.cu:82-96) [and the cleaned linear frame]. Runs novum_frame_finish (upload, one device kernel, read-back)."""
+    colors = np.ascontiguousarray(colors, dtype=np.float32)
+    h, w = colors.shape[:2]
+    ov = None if overlay is None else np.ascontiguousarray(overlay, dtype=np.float32)
+    rows = np.empty((h, bmp_row_bytes(w)), dtype=np.uint8)
+    fin = np.empty((h, w, 4), dtype=np.float32) if want_final else None
+    _check(lib().novum_frame_finish(_ptr(colors), None if ov is None else _ptr(ov), w, h, int(sample_count), int(mode), int(bool(post_process)),
+                                    _ptr(rows), None if fin is None else _ptr(fin)), "novum_frame_finish")
+    return (rows, fin) if want_final else rows
+
+
+def frame_finish_device(d_colors, d_overlay, w, h, sample_count, mode, post_process, d_bgr, d_final=None, stream=None):
+    """Device pointers (ints) in and out; asynchronous on `stream` (cudaStream_t as int, None = default stream)."""
+    _check(lib().novum_frame_finish_device(d_colors, d_overlay, int(w), int(h), int(sample_count), int(mode), int(bool(post_process)), d_bgr,
+                                           d_final, stream), "novum_frame_finish_device")
+
+
+def frame_save_bmp(path, d_colors, d_overlay, w, h, sample_count, mode=FRAME_FINAL, post_process=True):
+    _check(lib().novum_frame_save_bmp(os.fsencode(path), d_colors, d_overlay, int(w), int(h), int(sample_count), int(mode),
+                                      int(bool(post_process))), "novum_frame_save_bmp")
+    ms = C.c_float()
+    lib().novum_frame_last_ms(C.byref(ms))
+    return ms.value
+
+
+def save_bmp(path, colors, overlay, sample_count, mode=FRAME_FINAL, post_process=True):
+    colors = np.ascontiguousarray(colors, dtype=np.float32)
+    h, w = colors.shape[:2]
+    ov = None if overlay is None else np.ascontiguousarray(overlay, dtype=np.float32)
+    _check(lib().novum_save_bmp(os.fsencode(path), _ptr(colors), None if ov is None else _ptr(ov), w, h, int(sample_count), int(mode),
+                                int(bool(post_process))), "novum_save_bmp")
+
+
+def gamma_steps():
+    s = np.empty(257, dtype=np.float32)
+    _check(lib().novum_frame_gamma_steps(_ptr(s)), "novum_frame_gamma_steps")
+    return s
 
 
 class HashGrid:

@@ -322,12 +322,6 @@ bool loadBmpTexture(const std::string& file, std::vector<NovumFloat4>& px, int& 
     return true;
 }
 
-static float tone1(float c) {   // imageUtil.cu:202-210 then :212-221
-    float t = (c * (2.51f * c + 0.03f)) / (c * (2.43f * c + 0.59f) + 0.14f);
-    t = t < 0.f ? 0.f : (t > 1.f ? 1.f : t);
-    return powf(t, 1.0f / 2.2f);
-}
-
 }  // namespace nv
 
 using namespace nv;
@@ -402,32 +396,6 @@ int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene
                             M.tris.data(), (int)M.tris.size(), mats, 24, texels.data(), (int)texels.size(), out);
     if (rc == 0) for (const MeshCfg& m : meshes) (*out)->meshPaths.push_back(m.path);
     return rc;
-}
-
-int novum_save_bmp(const char* path, const NovumFloat4* colors, int w, int h, float scale, int postProcess) {
-    if (!path || !colors || w <= 0 || h <= 0) return NOVUM_E_ARG;
-    FILE* f = fopen(path, "wb");
-    if (!f) return NOVUM_E_IO;
-    int rowSize = (3 * w + 3) & (~3);
-    BmpFileHeader fh = {0x4D42, (uint32_t)(sizeof(BmpFileHeader) + sizeof(BmpInfoHeader) + rowSize * h), 0, 0,
-                        (uint32_t)(sizeof(BmpFileHeader) + sizeof(BmpInfoHeader))};
-    BmpInfoHeader ih = {sizeof(BmpInfoHeader), w, h, 1, 24, 0, (uint32_t)(rowSize * h), 0, 0, 0, 0};
-    fwrite(&fh, sizeof(fh), 1, f); fwrite(&ih, sizeof(ih), 1, f);
-    std::vector<unsigned char> row(rowSize, 0);
-    for (int y = 0; y < h; ++y) {   // row order as imageUtil.cu:82-93 writes it
-        for (int x = 0; x < w; ++x) {
-            const NovumFloat4& c = colors[(size_t)y * w + x];
-            float v[3] = {c.x * scale, c.y * scale, c.z * scale};
-            for (int k = 0; k < 3; ++k) {
-                float t = postProcess ? tone1(v[k]) : v[k];
-                t = t < 0.f ? 0.f : (t > 1.f ? 1.f : t);
-                row[x * 3 + (2 - k)] = (unsigned char)(t * 255.0f + 0.5f);
-            }
-        }
-        fwrite(row.data(), 1, rowSize, f);
-    }
-    fclose(f);
-    return 0;
 }
 
 int novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, float scale) {

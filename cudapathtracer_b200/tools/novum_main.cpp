@@ -45,8 +45,9 @@ int main(int argc, char** argv) {
     printf("{\"paths\": %llu, \"closest_rays\": %llu, \"shadow_rays\": %llu, \"device_ms\": %.3f, \"mrays_per_s\": %.1f, \"launches\": %llu}\n",
            (unsigned long long)st.paths, (unsigned long long)st.closestRays, (unsigned long long)st.shadowRays, st.deviceMs,
            rays / (st.deviceMs * 1e3), (unsigned long long)st.kernelLaunches);
-    float scale = 1.0f / (float)cfg.sampleCount;      // main.cu:862
-    novum_save_bmp((out + ".bmp").c_str(), img.data(), cfg.width, cfg.height, scale, cfg.postProcess);
+    // main.cu:855-907: / sampleCount, NaN / Inf marking, tonemap + gamma + BGR rows — one device kernel, 3 B/pixel read back
+    rc = novum_save_bmp((out + ".bmp").c_str(), img.data(), nullptr, cfg.width, cfg.height, cfg.sampleCount, NOVUM_FRAME_FINAL, cfg.postProcess);
+    if (rc) fprintf(stderr, "bmp write failed: %s\n", novum_error_string(rc));
     if (raw) {
         FILE* f = fopen((out + ".raw").c_str(), "wb");
         if (f) { fwrite(img.data(), sizeof(NovumFloat4), img.size(), f); fclose(f); }

@@ -14,6 +14,8 @@
  *   integratorUtilities.cuh:84   BVHSceneIntersect (per ray)          -> novum_trace_closest (ray batch)
  *   integratorUtilities.cuh:188  BVHShadowRay (per ray)               -> novum_trace_shadow  (ray batch)
  *   deviceCode.cu:3140      buildHashGrid(...)                        -> novum_hashgrid_build
+ *   integratorUtilities.cuh:337  cleanAndFormatImage, main.cu:855-884,
+ *   imageUtil.cu:69-100, 202-232  Image::saveImageBMP / postProcessImage -> novum_frame_finish[_device] / novum_frame_save_bmp
  *   objects.cuh:844         loadConfig, main.cu:936 readObjSimple,
  *   main.cu:397-467         material table, main.cu:235 initRender    -> novum_scene_load_config / novum_render
  *
@@ -31,7 +33,7 @@
 extern "C" {
 #endif
 
-#define NOVUM_ABI_VERSION 2
+#define NOVUM_ABI_VERSION 3
 
 /* error codes (negative; positive return values are cudaError_t) */
 #define NOVUM_OK             0
@@ -308,8 +310,32 @@ int  novum_sync(void);
 /* writes OBJ files + a .rendertron config under outDir; name in {cornell, dragon, water, rainbow}. */
 int  novum_make_scene(const char* name, const char* outDir, int detail);
 
-/* ---- image output (imageUtil.cu:69-142, 202-232) ---------------------------------------- */
-int  novum_save_bmp(const char* path, const NovumFloat4* colors, int w, int h, float scale, int postProcess);
+/* ---- frame finish + image output: the step directly after the path ----------------
+ * One device kernel replaces cleanAndFormatImage (integratorUtilities.cuh:337-380) or the final normalisation of
+ * initRender (main.cu:855-884), Image::postProcessImage = ACES toneMap + gammaCorrect (imageUtil.cu:202-232) and the
+ * clamp / *255+0.5 / BGR / 4-byte-padded-row loop of Image::saveImageBMP (imageUtil.cu:82-96). Bytes are bit-exact with the
+ * reference's host arithmetic. Only the packed rows (3 B/pixel) are read back, not two float4 frames. */
+#define NOVUM_FRAME_PROGRESSIVE 0   /* cleanAndFormatImage: NaN/Inf/negative checks on the raw sum, then * 1/(sampleCount+1);
+                                       sampleCount = the reference's currentSampleCount argument */
+#define NOVUM_FRAME_FINAL       1   /* main.cu:862-870: / sampleCount, then NaN -> pink, Inf -> green */
+int  novum_bmp_row_bytes(int w);                                      /* (3w+3)&~3, imageUtil.cu:80 */
+/* device buffers in, device buffers out; d_overlay, d_bgrRows (h rows of novum_bmp_row_bytes(w), 4-byte aligned) and d_final
+ * (the cleaned linear float4 frame the reference hands to Image::setColor) may each be NULL, not both outputs. Asynchronous on
+ * `stream` (a cudaStream_t, NULL = default stream). */
+int  novum_frame_finish_device(const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h, int sampleCount, int mode,
+                               int postProcess, uint8_t* d_bgrRows, NovumFloat4* d_final, void* stream);
+/* host buffers in and out (uploads, runs the kernel, reads back); blocking */
+int  novum_frame_finish(const NovumFloat4* colors, const NovumFloat4* overlay, int w, int h, int sampleCount, int mode, int postProcess,
+                        uint8_t* bgrRows, NovumFloat4* finalOut);
+/* device accumulators -> .bmp file: kernel, 3 B/pixel read-back into page-locked memory, headers + rows (imageUtil.cu:69-100) */
+int  novum_frame_save_bmp(const char* path, const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h, int sampleCount,
+                          int mode, int postProcess);
+/* host accumulators -> .bmp file (same kernel; no CPU tonemap exists in the product) */
+int  novum_save_bmp(const char* path, const NovumFloat4* colors, const NovumFloat4* overlay, int w, int h, int sampleCount, int mode,
+                    int postProcess);
+int  novum_write_bmp(const char* path, const uint8_t* bgrRows, int w, int h);   /* headers + already packed rows */
+int  novum_frame_last_ms(float* ms);                                  /* CUDA-event time of the last kernel run by the file/host variants */
+int  novum_frame_gamma_steps(float* steps257);                        /* the 255 step positions of byte(t) (host powf), for inspection */
 int  novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, float scale);
 
 #ifdef __cplusplus

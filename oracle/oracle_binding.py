@@ -57,6 +57,11 @@ def lib():
         L.oracle_bsdf_sample.argtypes = [vp, ci, vp, C.POINTER(cf * 3), cf, ci, ci, cf, cf, vp, C.POINTER(cf * 3), C.POINTER(cf * 3), C.POINTER(cf)]
         L.oracle_render_unidirectional.argtypes = [vp, vp, ci, ci, ci, ci, ci, C.c_uint64, vp, ci, vp]
         L.oracle_triangle_intersect.argtypes = [vp, vp, vp, C.POINTER(cf), C.POINTER(cf), C.POINTER(cf)]
+        L.oracle_clean_and_format.argtypes = [vp, vp, vp, ci, ci, ci]
+        L.oracle_final_normalise.argtypes = [vp, vp, vp, ci, ci, ci]
+        L.oracle_bmp_rows.argtypes = [vp, ci, ci, ci, vp]
+        L.oracle_gamma_table_check.restype = C.c_long
+        L.oracle_gamma_table_check.argtypes = [vp, C.c_uint32, C.c_uint32]
         _LIB = L
     return _LIB
 
@@ -170,3 +175,32 @@ def unpack_oct(p):
     out = (C.c_float * 3)()
     lib().oracle_unpack_oct(int(p), C.byref(out))
     return np.array(list(out), np.float32)
+
+
+def frame_clean(acc, overlay, n, final_mode=False):
+    """cleanAndFormatImage (integratorUtilities.cuh:337-380; n = currentSampleCount) or, final_mode, main.cu:855-884 (n = sampleCount)."""
+    acc = np.ascontiguousarray(acc, dtype=np.float32)
+    h, w = acc.shape[:2]
+    ov = None if overlay is None else np.ascontiguousarray(overlay, dtype=np.float32)
+    out = np.empty((h, w, 4), dtype=np.float32)
+    f = lib().oracle_final_normalise if final_mode else lib().oracle_clean_and_format
+    f(_p(acc), None if ov is None else _p(ov), _p(out), w, h, int(n))
+    return out
+
+
+def bmp_rows(frame, post_process):
+    """Image::saveImageBMP's rows (imageUtil.cu:69-100, 202-232) of a cleaned float4 frame: (h, (3w+3)&~3) uint8, B G R."""
+    frame = np.ascontiguousarray(frame, dtype=np.float32)
+    h, w = frame.shape[:2]
+    rows = np.empty((h, (3 * w + 3) & ~3), dtype=np.uint8)
+    lib().oracle_bmp_rows(_p(frame), w, h, int(bool(post_process)), _p(rows))
+    return rows
+
+
+def frame_finish(acc, overlay, n, final_mode, post_process):
+    return bmp_rows(frame_clean(acc, overlay, n, final_mode), post_process)
+
+
+def gamma_table_check(steps, first_bits=0, last_bits=0x3f800000):
+    steps = np.ascontiguousarray(steps, dtype=np.float32)
+    return int(lib().oracle_gamma_table_check(_p(steps), first_bits, last_bits))

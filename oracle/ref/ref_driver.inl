@@ -136,9 +136,65 @@ static int cmdTrace(int argc, char** argv) {
     return err == cudaSuccess ? 0 : 2;
 }
 
+// ---- frame finish: the reference's own post-path code on a raw float4 frame --------------------------------------------
+//   novum_ref bmp   <frame.raw> <w> <h> <postProcess> <out.bmp> [--time N]   CPU ONLY: Image::setColor + Image::saveImageBMP
+//                   (imageUtil.cu:60-100, 202-232: ACES toneMap, gammaCorrect, clamp/*255+0.5, BGR rows). Runs without a GPU.
+//   novum_ref clean <acc.raw> <overlay.raw> <w> <h> <currentSampleCount> <out.raw>   GPU: cleanAndFormatImage
+//                   (integratorUtilities.cuh:337-380), launched with the reference's 16x16 blocks (deviceCode.cu:3313, 3449).
+static bool readRaw(const char* path, std::vector<float4>& v, size_t n) {
+    FILE* f = fopen(path, "rb"); if (!f) return false;
+    v.resize(n); size_t got = fread(v.data(), sizeof(float4), n, f); fclose(f);
+    return got == n;
+}
+
+static int cmdBmp(int argc, char** argv) {
+    int w = atoi(argv[3]), h = atoi(argv[4]); bool post = atoi(argv[5]) != 0; int reps = 1;
+    if (argc >= 9 && !strcmp(argv[7], "--time")) reps = atoi(argv[8]);
+    std::vector<float4> px;
+    if (w <= 0 || h <= 0 || !readRaw(argv[2], px, (size_t)w * h)) { fprintf(stderr, "cannot read %s\n", argv[2]); return 1; }
+    double best = 1e30;
+    for (int r = 0; r < reps; r++) {
+        auto t0 = std::chrono::high_resolution_clock::now();
+        Image image(w, h);
+        image.postProcess = post;
+        for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) image.setColor(x, y, px[(size_t)y * w + x]);
+        image.saveImageBMP(argv[6]);
+        best = std::min(best, std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - t0).count());
+    }
+    printf("\nNOVUM_REF_JSON {\"mode\": \"bmp\", \"w\": %d, \"h\": %d, \"post\": %d, \"host_ms\": %.3f}\n", w, h, (int)post, best * 1e3);
+    return 0;
+}
+
+static int cmdClean(int argc, char** argv) {
+    int w = atoi(argv[4]), h = atoi(argv[5]), n = atoi(argv[6]);
+    std::vector<float4> acc, ov;
+    if (w <= 0 || h <= 0 || !readRaw(argv[2], acc, (size_t)w * h) || !readRaw(argv[3], ov, (size_t)w * h)) { fprintf(stderr, "cannot read inputs\n"); return 1; }
+    size_t bytes = sizeof(float4) * (size_t)w * h;
+    float4 *dA, *dO, *dF; cudaMalloc(&dA, bytes); cudaMalloc(&dO, bytes); cudaMalloc(&dF, bytes);
+    cudaMemcpy(dA, acc.data(), bytes, cudaMemcpyHostToDevice); cudaMemcpy(dO, ov.data(), bytes, cudaMemcpyHostToDevice);
+    dim3 blockSize(16, 16); dim3 gridSize((w + 15) / 16, (h + 15) / 16);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int r = 0; r < 5; r++) {
+        cudaEventRecord(e0);
+        cleanAndFormatImage<<<gridSize, blockSize>>>(dA, dO, dF, w, h, n);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1); best = fminf(best, ms);
+    }
+    cudaError_t err = cudaDeviceSynchronize();
+    std::vector<float4> out((size_t)w * h);
+    cudaMemcpy(out.data(), dF, bytes, cudaMemcpyDeviceToHost);
+    FILE* f = fopen(argv[7], "wb"); if (f) { fwrite(out.data(), sizeof(float4), out.size(), f); fclose(f); }
+    printf("\nNOVUM_REF_JSON {\"mode\": \"clean\", \"w\": %d, \"h\": %d, \"kernel_ms\": %.4f, \"cuda_error\": %d}\n", w, h, best, (int)err);
+    return err == cudaSuccess ? 0 : 2;
+}
+
 int main(int argc, char** argv) {
     if (argc >= 3 && !strcmp(argv[1], "render")) return cmdRender(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "trace")) return cmdTrace(argc, argv);
-    fprintf(stderr, "usage: novum_ref render <sceneDir> [--spp N] [--out f.raw] | trace <sceneDir> <rays.bin> <out.bin> [--shadow]\n");
+    if (argc >= 7 && !strcmp(argv[1], "bmp")) return cmdBmp(argc, argv);
+    if (argc >= 8 && !strcmp(argv[1], "clean")) return cmdClean(argc, argv);
+    fprintf(stderr, "usage: novum_ref render <sceneDir> [--spp N] [--out f.raw] | trace <sceneDir> <rays.bin> <out.bin> [--shadow]\n"
+                    "       novum_ref bmp <frame.raw> <w> <h> <postProcess> <out.bmp> [--time N] | clean <acc.raw> <overlay.raw> <w> <h> <n> <out.raw>\n");
     return 64;
 }
