@@ -21,6 +21,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <algorithm>
+#include <utility>
 #include <mutex>
 #include <vector>
 #include "../../include/novum_b200.h"
@@ -114,30 +115,45 @@ struct __align__(128) FrameSmem {
 // row. mode 0: cleanAndFormatImage (checks on the raw sum, then * 1/(n+1), exact); mode 1: initRender's final pass (/ n, then
 // checks). When the cleaned float frame is wanted (`fin`) the final-mode division is IEEE up front; otherwise the byte path
 // works on x * (1/n) as described above.
+// The five launch options are template parameters (FLAGS bit 0: progressive mode, 1: overlay, 2: cleaned float frame out,
+// 3: byte rows out, 4: postProcess): tested at run time they were a quarter of the per-pixel instructions.
+template <int FLAGS>
 __global__ void __launch_bounds__(FRAME_THREADS, FRAME_CTAS_PER_SM)
-frameFinishKernel(const float4* __restrict__ colors, const float4* __restrict__ overlay, int w, int h, int mode, float norm, float rnorm, int postProcess,
-                  const FrameTables* __restrict__ gT, uint8_t* __restrict__ bgr, int rowSize, float4* __restrict__ fin) {
+frameFinishKernel(const float4* __restrict__ colors, const float4* __restrict__ overlayIn, int w, int h, float norm, float rnorm,
+                  const FrameTables* __restrict__ gT, uint8_t* __restrict__ bgrIn, int rowSize, float4* __restrict__ finIn) {
+    constexpr int mode = (FLAGS & 1) ? NOVUM_FRAME_PROGRESSIVE : NOVUM_FRAME_FINAL;
+    constexpr bool postProcess = (FLAGS & 16) != 0;
+    const float4* const overlay = (FLAGS & 2) ? overlayIn : nullptr;
+    float4* const fin = (FLAGS & 4) ? finIn : nullptr;
+    uint8_t* const bgr = (FLAGS & 8) ? bgrIn : nullptr;
     extern __shared__ __align__(128) unsigned char smemRaw[];
     FrameSmem& S = *reinterpret_cast<FrameSmem*>(smemRaw);
     const int tid = threadIdx.x;
     const int segsPerRow = (w + FRAME_SEG - 1) / FRAME_SEG;
-    const int nSeg = segsPerRow * h;
-    auto issue = [&](int seg, int stage) {      // one thread: arm the stage's barrier and start the copies of segment `seg`
-        const int y = seg / segsPerRow, x0 = (seg - y * segsPerRow) * FRAME_SEG;
+    auto issue = [&](int y, int sx, int stage) { // one thread: arm the stage's barrier and start the copies of segment (row y, sx)
+        const int x0 = sx * FRAME_SEG;
         const unsigned bytes = (unsigned)min(FRAME_SEG, w - x0) * 16u;
         const size_t base = (size_t)y * w + x0;
         mbarExpectTx(&S.bar[stage], overlay ? 2u * bytes : bytes);
         bulkLoad(S.acc[stage], colors + base, bytes, &S.bar[stage]);
         if (overlay) bulkLoad(S.ov[stage], overlay + base, bytes, &S.bar[stage]);
     };
+    // segments are walked with a stride of gridDim.x; (row, segment-in-row) advance incrementally (one division per kernel, not
+    // per segment: the per-segment div/mod was a fifth of all instructions, profiles/r1_frameFinish_v3.txt)
+    const int stepY = gridDim.x / segsPerRow, stepX = gridDim.x - stepY * segsPerRow;
+    auto advance = [&](int& y, int& sx) { y += stepY; sx += stepX; if (sx >= segsPerRow) { sx -= segsPerRow; ++y; } };
     if (tid == 0) {
         for (int s = 0; s < FRAME_STAGES; ++s) mbarInit(&S.bar[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    int y = blockIdx.x / segsPerRow, sx = blockIdx.x - y * segsPerRow;     // this CTA's current segment
+    int py = y, psx = sx;                                                  // the next segment to prefetch (thread 0)
     if (tid == 0)
-        for (int s = 0; s < FRAME_STAGES; ++s)
-            if (blockIdx.x + s * gridDim.x < nSeg) issue(blockIdx.x + s * gridDim.x, s);
+        for (int s = 0; s < FRAME_STAGES; ++s) {
+            if (py < h) issue(py, psx, s);
+            advance(py, psx);
+        }
     if (bgr && postProcess) {
         const uint32_t* src = reinterpret_cast<const uint32_t*>(gT);
         uint32_t* dst = reinterpret_cast<uint32_t*>(&S.T);
@@ -146,9 +162,9 @@ frameFinishKernel(const float4* __restrict__ colors, const float4* __restrict__ 
     __syncthreads();
     const bool exactDiv = fin != nullptr;
     int it = 0;
-    for (int seg = blockIdx.x; seg < nSeg; seg += gridDim.x, ++it) {
+    for (; y < h; advance(y, sx), ++it) {
         const int stage = it % FRAME_STAGES;
-        const int y = seg / segsPerRow, x0 = (seg - y * segsPerRow) * FRAME_SEG;
+        const int x0 = sx * FRAME_SEG;
         const int npx = min(FRAME_SEG, w - x0);
         const size_t rowBase = (size_t)y * w + x0;
         uint8_t* sBytes = reinterpret_cast<uint8_t*>(S.out[it & 1]);
@@ -160,9 +176,11 @@ frameFinishKernel(const float4* __restrict__ colors, const float4* __restrict__ 
             const float4 a = S.acc[stage][x];
             float4 c;            // the cleaned pixel; `divide`: c holds x * (1/n), the exact value is a / norm
             int divide = 0;
-            if (isnan(a.x) || isnan(a.y) || isnan(a.z)) c = make_float4(1.f, 0.f, 1.f, 0.f);          // pink; x / n is NaN / Inf exactly when x is (n >= 1)
-            else if (isinf(a.x) || isinf(a.y) || isinf(a.z)) c = make_float4(0.f, 1.f, 0.f, 0.f);     // green
-            else if (mode == NOVUM_FRAME_PROGRESSIVE) {      // integratorUtilities.cuh:356-371
+            // 0 * x is NaN exactly when x is NaN or +-Inf: one test for the rare marked pixels
+            if (isnan(fmaf(a.x, 0.0f, fmaf(a.y, 0.0f, a.z * 0.0f)))) {
+                if (isnan(a.x) || isnan(a.y) || isnan(a.z)) c = make_float4(1.f, 0.f, 1.f, 0.f);      // pink; x / n is NaN / Inf exactly when x is (n >= 1)
+                else c = make_float4(0.f, 1.f, 0.f, 0.f);                                             // green
+            } else if (mode == NOVUM_FRAME_PROGRESSIVE) {      // integratorUtilities.cuh:356-371
                 if (a.x < 0 || a.y < 0 || a.z < 0) c = make_float4(0.f, 0.f, 1.f, 0.f);
                 else c = make_float4(__fmul_rn(a.x, norm), __fmul_rn(a.y, norm), __fmul_rn(a.z, norm), 1.0f);
             } else if (exactDiv) {                           // main.cu:862; util.cuh:96-99 leaves w
@@ -190,15 +208,20 @@ frameFinishKernel(const float4* __restrict__ colors, const float4* __restrict__ 
                 sBytes[x * 3 + 0] = (uint8_t)b; sBytes[x * 3 + 1] = (uint8_t)g; sBytes[x * 3 + 2] = (uint8_t)r;
             }
         }
-        const bool lastSeg = x0 + npx == w;
-        const int nbytes = lastSeg ? rowSize - x0 * 3 : npx * 3;    // both multiples of 4: x0*3 = 1536*k, rowSize % 4 == 0
-        if (bgr && lastSeg) for (int i = npx * 3 + tid; i < nbytes; i += FRAME_THREADS) sBytes[i] = 0;   // row padding, imageUtil.cu:80
+        // the segment's byte count is a multiple of 4 either way: npx * 3 = 1536 for an inner segment, and for the last one of a
+        // row (rowSize - x0 * 3) with rowSize % 4 == 0 and x0 * 3 = 1536 * sx; the <= 3 bytes past the pixels are the row padding
+        const int nwords = (x0 + npx == w ? rowSize - x0 * 3 : npx * 3) >> 2;
+        if (bgr && tid < nwords * 4 - npx * 3) sBytes[npx * 3 + tid] = 0;                      // imageUtil.cu:80
         __syncthreads();        // every thread is done with this stage's staging buffers, and the segment's bytes are complete
-        if (tid == 0 && seg + FRAME_STAGES * gridDim.x < nSeg) issue(seg + FRAME_STAGES * gridDim.x, stage);
+        if (tid == 0) {
+            if (py < h) issue(py, psx, stage);
+            advance(py, psx);
+        }
         if (bgr) {
             uint32_t* dst = reinterpret_cast<uint32_t*>(bgr + (size_t)y * rowSize + (size_t)x0 * 3);
             const uint32_t* src = S.out[it & 1];
-            for (int i = tid; i < nbytes / 4; i += FRAME_THREADS) dst[i] = src[i];
+            if (tid < nwords) dst[tid] = src[tid];
+            if (tid + FRAME_THREADS < nwords) dst[tid + FRAME_THREADS] = src[tid + FRAME_THREADS];
         }
     }
 }
@@ -257,6 +280,14 @@ static int haveGpu() {
     return cudaGetDeviceCount(&ndev) == cudaSuccess && ndev > 0;
 }
 
+using FrameKernel = void (*)(const float4*, const float4*, int, int, float, float, const FrameTables*, uint8_t*, int, float4*);
+template <int... I> static FrameKernel frameKernelAt(int flags, std::integer_sequence<int, I...>) {
+    static const FrameKernel table[] = {frameFinishKernel<I>...};
+    return table[flags];
+}
+static FrameKernel frameKernelFor(int flags) { return frameKernelAt(flags & 31, std::make_integer_sequence<int, 32>{}); }
+template <typename F> static void forEachFrameKernel(F f) { for (int i = 0; i < 32; ++i) f(frameKernelFor(i)); }
+
 static int launchFinish(const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h, int sampleCount, int mode, int postProcess,
                         uint8_t* d_bgr, NovumFloat4* d_final, cudaStream_t st) {
     if (!d_colors || w <= 0 || h <= 0 || (!d_bgr && !d_final)) return NOVUM_E_ARG;
@@ -271,16 +302,18 @@ static int launchFinish(const NovumFloat4* d_colors, const NovumFloat4* d_overla
     static bool attrSet[16] = {};
     static int smCount[16] = {};
     int dev = 0; cudaGetDevice(&dev);
+    const int flags = (mode == NOVUM_FRAME_PROGRESSIVE ? 1 : 0) | (d_overlay ? 2 : 0) | (d_final ? 4 : 0) | (d_bgr ? 8 : 0) | (postProcess ? 16 : 0);
     if (!attrSet[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(frameFinishKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrameSmem));
+        cudaError_t e = cudaSuccess;
+        forEachFrameKernel([&](FrameKernel k) { if (e == cudaSuccess) e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FrameSmem)); });
         if (e != cudaSuccess) return (int)e;
         cudaDeviceGetAttribute(&smCount[dev], cudaDevAttrMultiProcessorCount, dev);
         attrSet[dev] = true;
     }
     const long nSeg = (long)((w + FRAME_SEG - 1) / FRAME_SEG) * h;
     const int grid = (int)std::min<long>(nSeg, (long)smCount[dev] * FRAME_CTAS_PER_SM);       // persistent CTAs
-    frameFinishKernel<<<grid, FRAME_THREADS, sizeof(FrameSmem), st>>>((const float4*)d_colors, (const float4*)d_overlay, w, h, mode, norm, 1.0f / norm,
-                                                                      postProcess, dT, d_bgr, novum_bmp_row_bytes(w), (float4*)d_final);
+    frameKernelFor(flags)<<<grid, FRAME_THREADS, sizeof(FrameSmem), st>>>((const float4*)d_colors, (const float4*)d_overlay, w, h, norm, 1.0f / norm, dT,
+                                                                           d_bgr, novum_bmp_row_bytes(w), (float4*)d_final);
     return (int)cudaGetLastError();
 }
 

@@ -613,6 +613,10 @@ constexpr int kMergeThreads = 128;
 constexpr int kMergeWarps = kMergeThreads / 32;
 constexpr int kMergeCtasPerSm = 8;        // 64 registers per thread; the 90-register build at 5 CTAs/SM was 14 % slower
 constexpr int kMergeGather = 4;           // eye vertices a warp gathers together
+#ifndef NOVUM_MERGE_CULL
+#define NOVUM_MERGE_CULL 0
+#endif
+constexpr bool kMergeCull = NOVUM_MERGE_CULL != 0;   // drop neighbour cells out of reach of the whole group before the sweep
 
 struct MergeCells { uint32_t cs, cc; };     // per lane (< 27): first photon and photon count of its neighbour cell
 
@@ -686,8 +690,29 @@ __global__ void __launch_bounds__(kMergeThreads, kMergeCtasPerSm) bdMergeLambert
             nPi[g] = V3(r1.x, r1.y, r1.z) * (1.0f / kPi);                                        // cos/pi = dot(wi, n/pi)
             C[g] = 1.0f + r2q.w * invEta + cosinePdf(V3(r2q.x, r2q.y, r2q.z)) * r3.w;           // 1 + d_vcm/eta + eyeRev * d_vm
             sum[g] = V3(0.0f);
+        }
+#pragma unroll
+        for (int g = 0; g < kMergeGather; ++g) {
             MergeCells mc = mergeCells(P, eyeP[g], lane);
             if (base + g >= n) mc.cc = 0u;
+            if (kMergeCull && mc.cc) {
+                // a neighbour cell whose box lies farther than r from ALL vertices of the group cannot hold a photon any of them
+                // accepts (8 corner and 12 edge cells of a 27-neighbourhood are often out of reach): drop it before the sweep.
+                // The test is per (cell, group), so vertices sharing a centre cell keep identical lists (the shortcut below).
+                // 1.1 r^2: slack for the rounding of the cell function; nothing within r is ever dropped.
+                const int3 c0 = gridIndex(eyeP[g].x, eyeP[g].y, eyeP[g].z, P.grid);
+                const float lx = P.grid.minX + (float)(c0.x + lane % 3 - 1) * P.grid.cell, ly = P.grid.minY + (float)(c0.y + (lane / 3) % 3 - 1) * P.grid.cell,
+                            lz = P.grid.minZ + (float)(c0.z + lane / 9 - 1) * P.grid.cell;
+                bool near = false;
+#pragma unroll
+                for (int k = 0; k < kMergeGather; ++k) {
+                    const float dx = fmaxf(fmaxf(lx - eyeP[k].x, eyeP[k].x - (lx + P.grid.cell)), 0.0f);
+                    const float dy = fmaxf(fmaxf(ly - eyeP[k].y, eyeP[k].y - (ly + P.grid.cell)), 0.0f);
+                    const float dz = fmaxf(fmaxf(lz - eyeP[k].z, eyeP[k].z - (lz + P.grid.cell)), 0.0f);
+                    near |= fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= 1.1f * r2;
+                }
+                if (!near) mc.cc = 0u;
+            }
             // key = first photon of the slot; empty slots get keys no photon index can take
             cellKey[g * 32 + lane] = mc.cc ? mc.cs : 0xFFFFFF00u + (unsigned)lane;
             cellList[g * 32 + lane] = make_uint2(mc.cs, mc.cc);
