@@ -12,6 +12,7 @@ Workloads = BASELINE.json configs on the generated stand-in scenes (the referenc
   water_bdpt   configs[2]  water caustic, BDPT, 1920x1080
   water_sppm   configs[3]  water caustic, SPPM, 1024x1024 light paths (~1M photons / iteration)
   cornell      configs[0]  Cornell box 512x512 NEE+MIS
+  trace_batch  SURVEY 8d micro: closest-hit / any-hit kernels alone on identical ray batches (ours vs the reference's routines)
   frame_finish SURVEY 8f row 2: the step after the path (clean + tonemap + gamma + BGR8 rows of a 4K frame), metric Mpixels/s
 metric = Mrays/s: closest-hit + shadow rays actually traced (device counters); paths/s is reported beside it.
 
@@ -505,20 +506,231 @@ def run_frame_reference(args):
                       "e2e": {"value": val, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+TRACE_DESC = "ray batches on the dragon stand-in's BVH (SURVEY 8d micro): primary-like, cosine-bounce secondary and shadow rays, closest-hit / any-hit"
+
+
+def trace_ray_sets(scene, cfg, n_side, dev):
+    """Three ray batches on the GPU (torch), deterministic: primary-like rays from the camera position through an n_side x n_side
+    grid (row-major, coherent), cosine-distributed bounce rays from their hit points (incoherent), and shadow rays from the hit
+    points to a jittered point light above the scene with maxT and the hit triangle as skipTri."""
+    import numpy as np
+    import torch
+    info = scene.info()
+    mn = torch.tensor(info["min"], device=dev, dtype=torch.float32); mx = torch.tensor(info["max"], device=dev, dtype=torch.float32)
+    ctr = (mn + mx) * 0.5
+    radius = float(torch.linalg.norm(mx - ctr))
+    cam = torch.tensor([cfg.camPos[0], cfg.camPos[1], cfg.camPos[2]], device=dev, dtype=torch.float32)
+    fwd = ctr - cam; fwd = fwd / torch.linalg.norm(fwd)
+    up = torch.tensor([0.0, 1.0, 0.0], device=dev)
+    right = torch.linalg.cross(fwd, up); right = right / torch.linalg.norm(right)
+    up = torch.linalg.cross(right, fwd)
+    g = torch.Generator(device=dev); g.manual_seed(1234)
+    u = (torch.arange(n_side, device=dev, dtype=torch.float32) + 0.5) / n_side * 2 - 1
+    yy, xx = torch.meshgrid(-u, u, indexing="ij")
+    tgt = ctr[None, None, :] + 0.7 * radius * (xx[..., None] * right + yy[..., None] * up)
+    d = tgt - cam
+    d = d / torch.linalg.norm(d, dim=-1, keepdim=True)
+    n = n_side * n_side
+    prim = torch.zeros((n, 8), device=dev, dtype=torch.float32)
+    prim[:, 0:3] = cam; prim[:, 4:7] = d.reshape(n, 3)
+    hits = torch.zeros((n, 4), device=dev, dtype=torch.int32)
+    scene.trace_closest_device(prim.data_ptr(), n, hits.data_ptr(), True)
+    tri = hits[:, 0].long(); t = hits[:, 1].view(torch.float32)
+    ok = tri >= 0
+    pos, _, _, tris, _ = scene.download()
+    P = torch.from_numpy(np.ascontiguousarray(pos[:, :3])).to(dev)
+    ia = torch.from_numpy(tris["aInd"].astype(np.int64)).to(dev); ib = torch.from_numpy(tris["bInd"].astype(np.int64)).to(dev)
+    ic = torch.from_numpy(tris["cInd"].astype(np.int64)).to(dev)
+    tri = tri[ok]; o = prim[ok, 0:3] + t[ok, None] * prim[ok, 4:7]; din = prim[ok, 4:7]
+    ng = torch.linalg.cross(P[ib[tri]] - P[ia[tri]], P[ic[tri]] - P[ia[tri]])
+    ng = ng / torch.linalg.norm(ng, dim=-1, keepdim=True).clamp_min(1e-30)
+    ng = torch.where((ng * din).sum(-1, keepdim=True) > 0, -ng, ng)
+    m = tri.numel()
+    r1 = torch.rand(m, device=dev, generator=g); r2 = torch.rand(m, device=dev, generator=g) * (2 * np.pi)
+    a = torch.where(ng[:, 0:1].abs() > 0.9, torch.tensor([0.0, 1.0, 0.0], device=dev), torch.tensor([1.0, 0.0, 0.0], device=dev))
+    tx = torch.linalg.cross(ng, a.expand(m, 3)); tx = tx / torch.linalg.norm(tx, dim=-1, keepdim=True)
+    ty = torch.linalg.cross(ng, tx)
+    sr = torch.sqrt(r1)
+    dsec = sr[:, None] * torch.cos(r2)[:, None] * tx + sr[:, None] * torch.sin(r2)[:, None] * ty + torch.sqrt(1 - r1)[:, None] * ng
+    sec = torch.zeros((m, 8), device=dev, dtype=torch.float32)
+    sec[:, 0:3] = o + 1e-3 * ng; sec[:, 4:7] = dsec / torch.linalg.norm(dsec, dim=-1, keepdim=True)
+    L = ctr + torch.tensor([0.0, 1.0, 0.0], device=dev) * (0.9 * float(mx[1] - ctr[1])) + (torch.rand((m, 3), device=dev, generator=g) - 0.5) * 0.05 * radius
+    dl = L - o; dist = torch.linalg.norm(dl, dim=-1)
+    sh = torch.zeros((m, 8), device=dev, dtype=torch.float32)
+    sh[:, 0:3] = o; sh[:, 4:7] = dl / dist[:, None]
+    return {"primary": (prim, None, None), "secondary": (sec.contiguous(), None, None),
+            "shadow": (sh.contiguous(), (dist * (1 - 1e-3)).contiguous(), tri.int().contiguous())}
+
+
+def ref_trace(sdir, rays, max_t, skip, tmp):
+    """The reference's own BVHSceneIntersect / BVHShadowRay (unmodified, oracle/_ref/novum_ref trace) on the same ray batch on this
+    box's GPU: returns (kernel ms, outputs)."""
+    import numpy as np
+    ref = os.path.join(REPO, "oracle", "_ref", "novum_ref")
+    rp, op = os.path.join(tmp, "rays.bin"), os.path.join(tmp, "out.bin")
+    with open(rp, "wb") as f:
+        np.array([len(rays)], np.int32).tofile(f); rays.tofile(f)
+        if max_t is not None:
+            max_t.tofile(f); skip.tofile(f)
+    cmd = [ref, "trace", sdir, rp, op] + (["--shadow"] if max_t is not None else [])
+    out = subprocess.check_output(cmd, stderr=subprocess.STDOUT).decode()
+    js = json.loads(re.search(r"NOVUM_REF_JSON (\{.*\})", out).group(1))
+    res = np.fromfile(op, np.float32).reshape(-1, 4)
+    os.remove(rp); os.remove(op)
+    return js["kernel_ms"], res
+
+
+def run_trace(args):
+    """--workload trace_batch: the intersection routines alone, on identical ray batches for both arms. One step = the three
+    batches traced once. value = device-resident Mrays/s (CUDA events inside the library around each kernel); e2e = the same
+    through the host-buffer entry points (rays H2D, hits D2H inside the timed region); parity of THIS run's outputs against the
+    reference's own routines (bit-exact classes) is part of the line when oracle/_ref/novum_ref is on the box."""
+    import numpy as np
+    import torch
+    import cudapathtracer_b200 as nb
+    from scene_utils import classify
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    ref_bin = os.path.join(REPO, "oracle", "_ref", "novum_ref")
+    sdir = scene_dir_for("dragon_nee", args.detail, 0, None)
+    tmp = tempfile.mkdtemp()
+    if not torch.cuda.is_available() or nb.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    dev = torch.device("cuda", 0)
+    scene = nb.Scene.from_config(os.path.join(sdir, "configs", "config.rendertron"))
+    info = scene.info()
+    sets = trace_ray_sets(scene, scene.cfg, args.rays_side, dev)
+    HIT = np.dtype([("tri", "<i4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4")])
+    if args.impl == "reference":
+        tot_ms, tot_n, per = 0.0, 0, {}
+        for name, (rays, mt, sk) in sets.items():
+            ms, _ = ref_trace(sdir, rays.cpu().numpy(), None if mt is None else mt.cpu().numpy(), None if sk is None else sk.cpu().numpy(), tmp)
+            per[name] = {"rays": len(rays), "kernel_ms": ms, "mrays_per_s": len(rays) / ms / 1e3}
+            tot_ms += ms; tot_n += len(rays)
+        val = tot_n / tot_ms / 1e3
+        print(json.dumps({"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": 1, "steps": 3, "warmup": 0,
+                          "ms_per_step": tot_ms, "higher_is_better": True, "config": {"workload": TRACE_DESC, "tris": info["tris"], "rays_side": args.rays_side},
+                          "sets": per, "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference",
+                                                        "sample": "the reference's BVHSceneIntersect / BVHShadowRay kernels (one thread per ray, best of 3) on the same batches on one B200"},
+                          "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    outs, per = {}, {}
+    clocks = ClockSampler(0)
+
+    def run_set(name):
+        rays, mt, sk = sets[name]
+        n = len(rays)
+        if mt is None:
+            out = torch.zeros((n, 4), device=dev, dtype=torch.int32)
+            scene.trace_closest_device(rays.data_ptr(), n, out.data_ptr(), True)
+        else:
+            out = torch.zeros((n, 4), device=dev, dtype=torch.float32)
+            scene.trace_shadow_device(rays.data_ptr(), mt.data_ptr(), sk.data_ptr(), n, out.data_ptr(), True)
+        return out, scene.last_trace_ms()
+
+    for i in range(args.warmup):
+        for name in sets:
+            run_set(name)
+    clocks.start()
+    tot_ms, tot_n = 0.0, 0
+    for name in sets:
+        per[name] = {"rays": len(sets[name][0]), "kernel_ms": 0.0}
+    for i in range(args.steps):
+        for name in sets:
+            flush.fill_(i)                       # evict the BVH (52 MB) and the rays from L2 between launches
+            torch.cuda.synchronize()
+            outs[name], ms = run_set(name)
+            per[name]["kernel_ms"] += ms / args.steps
+    for name in sets:
+        per[name]["mrays_per_s"] = per[name]["rays"] / per[name]["kernel_ms"] / 1e3
+        tot_ms += per[name]["kernel_ms"]; tot_n += per[name]["rays"]
+    # nodes / triangles per ray (counted launch, not timed) -> algorithmic bytes of the closest-hit batches
+    scene.counters(True)
+    for name in ("primary", "secondary"):
+        scene.counters(True)
+        run_set(name)
+        nv_, nt_ = scene.counters(True)
+        nr = per[name]["rays"]
+        per[name].update({"nodes_per_ray": nv_ / nr, "tris_per_ray": nt_ / nr, "bytes_per_ray": 48 + 80 * nv_ / nr + 48 * nt_ / nr})
+    scene.counters(False)
+    # e2e: page-locked host buffers through novum_trace_closest / novum_trace_shadow (rays H2D, results D2H inside the call)
+    host = {k: (r.cpu().numpy(), None if m is None else m.cpu().numpy(), None if s_ is None else s_.cpu().numpy()) for k, (r, m, s_) in sets.items()}
+    pinned = {}
+    for k, (r, m, s_) in sets.items():
+        pr = torch.empty(r.shape, dtype=torch.float32, pin_memory=True); pr.copy_(r)
+        po = torch.empty((len(r), 4), dtype=torch.float32, pin_memory=True)
+        pm = ps = None
+        if m is not None:
+            pm = torch.empty(m.shape, dtype=torch.float32, pin_memory=True); pm.copy_(m)
+            ps = torch.empty(s_.shape, dtype=torch.int32, pin_memory=True); ps.copy_(s_)
+        pinned[k] = (pr, pm, ps, po)
+    torch.cuda.synchronize()
+    L = nb.lib()
+    t0 = time.time()
+    for k, (pr, pm, ps, po) in pinned.items():
+        if pm is None:
+            rc = L.novum_trace_closest(scene.h, pr.data_ptr(), len(pr), po.data_ptr())
+        else:
+            rc = L.novum_trace_shadow(scene.h, pr.data_ptr(), pm.data_ptr(), ps.data_ptr(), len(pr), po.data_ptr())
+        if rc:
+            raise SystemExit(f"trace failed: {rc}")
+    e2e_s = time.time() - t0
+    clk = clocks.stop()                 # sampled over the timed launches, the counted launches and the end-to-end calls
+    peak, peak_src = peaks()
+    bpr = (per["primary"]["bytes_per_ray"] * per["primary"]["rays"] + per["secondary"]["bytes_per_ray"] * per["secondary"]["rays"])
+    closest_ms = per["primary"]["kernel_ms"] + per["secondary"]["kernel_ms"]
+    line = {"metric": "Mrays/s", "value": tot_n / tot_ms / 1e3, "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": tot_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": TRACE_DESC, "tris": info["tris"], "bvh8_nodes": info["bvh8_nodes"], "rays_side": args.rays_side,
+                       "l2": "256 MB flush before every launch"},
+            "sets": per, "gpu_launches": 3 * args.steps, "clocks": clk,
+            "e2e": {"value": tot_n / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(sum(32 * len(r) + (8 * len(r) if m is not None else 0) for r, m, _ in host.values())),
+                    "d2h_bytes_per_step": 16 * tot_n, "note": "novum_trace_closest / novum_trace_shadow with page-locked host arrays (PCIe-bound: 48-56 B per ray cross the bus)"},
+            "roofline": {"bound": "hbm", "kernel": "closestBatchKernel (BVH8 closest hit, primary + secondary batches)", "achieved": bpr / (closest_ms * 1e-3) / 1e9,
+                         "peak": peak, "unit": "GB/s", "frac": bpr / (closest_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src}}
+    if os.path.exists(ref_bin) and not args.no_cpu_baseline:
+        parity, ref_ms, ref_n = {}, 0.0, 0
+        for name, (r, m, s_) in host.items():
+            ms, res = ref_trace(sdir, r, m, s_, tmp)
+            ref_ms += ms; ref_n += len(r)
+            per[name]["reference_kernel_ms"] = ms; per[name]["reference_mrays_per_s"] = len(r) / ms / 1e3
+            per[name]["speedup"] = ms / per[name]["kernel_ms"]
+            if m is None:
+                ours = outs[name].cpu().numpy().view(HIT).reshape(-1)
+                refh = np.zeros(len(r), HIT)
+                refh["tri"] = res[:, 0].view(np.int32); refh["t"] = res[:, 1]; refh["u"] = res[:, 2]; refh["v"] = res[:, 3]
+                c = classify(ours, refh); c.pop("mismatch_idx")
+                parity[name] = c
+            else:
+                o = outs[name].cpu().numpy()
+                parity[name] = {"n": len(r), "bit_equal": int((o.view(np.uint32) == res.view(np.uint32)).all(axis=1).sum())}
+        line["parity_vs_reference_routines"] = parity
+        line["cpu_baseline"] = {"value": ref_n / ref_ms / 1e3, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference",
+                                "sample": "the reference's BVHSceneIntersect / BVHShadowRay kernels (one thread per ray, best of 3) on the same three batches on this B200 (the reference has no CPU path)"}
+    print(json.dumps(line))
+    scene.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default 4; frame_finish: 50 — its step is a 55 us kernel)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish"])
+    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish", "trace_batch"])
+    ap.add_argument("--rays-side", type=int, default=2048, help="trace_batch: the primary batch is rays_side^2 rays (2048 -> 4.19 M)")
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
     ap.add_argument("--sharding", default="striped", choices=["striped", "tiles"])
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="tiles sharding: photon exchange by peer stores fused into the light pass, or by an NCCL all-gather")
     ap.add_argument("--detail", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    if args.workload == "frame_finish":
+    if args.steps is None:
+        args.steps = 50 if (args.workload in ("frame_finish", "trace_batch") and args.impl == "ours") else 4
+    if args.workload == "trace_batch":
+        run_trace(args)
+    elif args.workload == "frame_finish":
         (run_frame_reference if args.impl == "reference" else run_frame)(args)
     elif args.impl == "reference":
         run_reference(args)

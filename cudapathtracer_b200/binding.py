@@ -260,6 +260,10 @@ class Scene:
     def trace_closest_device(self, d_rays, n, d_hits, sync=True):
         _check(lib().novum_trace_closest_device(self.h, C.c_void_p(d_rays), n, C.c_void_p(d_hits), int(sync)), "novum_trace_closest_device")
 
+    def trace_shadow_device(self, d_rays, d_max_t, d_skip, n, d_out, sync=True):
+        _check(lib().novum_trace_shadow_device(self.h, C.c_void_p(d_rays), C.c_void_p(d_max_t), C.c_void_p(d_skip), n, C.c_void_p(d_out),
+                                               int(sync)), "novum_trace_shadow_device")
+
     def last_trace_ms(self):
         ms = C.c_float()
         _check(lib().novum_trace_last_ms(self.h, C.byref(ms)), "novum_trace_last_ms")

@@ -31,6 +31,12 @@ struct HitRec { int tri; float t, u, v; int flags; };
 
 constexpr int kSmemStack = 12;          // entries per thread kept in shared memory
 constexpr int kLocalStack = 40;         // overflow entries in local memory
+#ifndef NOVUM_TRI_POSTPONE
+#define NOVUM_TRI_POSTPONE 0
+#endif
+// Triangle postponing (Ylitie et al. 2017, sec. 4.4): when fewer than this many lanes of the warp are in the leaf loop and this
+// lane still has inner nodes to visit, its leaf group goes on the stack and the lane returns to node tests with the others.
+constexpr int kTriPostpone = NOVUM_TRI_POSTPONE;
 
 struct TravCounters { unsigned long long* nodeVisits; unsigned long long* triTests; };
 
@@ -189,6 +195,7 @@ struct ClosestTrav {
             ngroup = make_uint2(0u, 0u);
         }
         while (tgroup.y != 0u) {
+            if (kTriPostpone > 0 && ngroup.y > 0x00ffffffu && __popc(__activemask()) < kTriPostpone) { st.push(tgroup); tgroup.y = 0u; break; }
             unsigned ti = __ffs(tgroup.y) - 1u;
             tgroup.y &= tgroup.y - 1u;
             const float4* tp = bvh.tris + (size_t)(tgroup.x + ti) * 3;

@@ -124,6 +124,7 @@ struct ShadowTrav {
             ngroup = make_uint2(0u, 0u);
         }
         while (tgroup.y != 0u) {
+            if (kTriPostpone > 0 && ngroup.y > 0x00ffffffu && __popc(__activemask()) < kTriPostpone) { st.push(tgroup); tgroup.y = 0u; break; }
             unsigned ti = __ffs(tgroup.y) - 1u;
             tgroup.y &= tgroup.y - 1u;
             const float4* tp = bvh.tris + (size_t)(tgroup.x + ti) * 3;

@@ -98,3 +98,15 @@ def test_dragon_full_detail_triangle_count(tmp_path):
     nb.make_scene("dragon", d, 100)
     n = sum(1 for l in open(os.path.join(d, "scenedata", "dragon_vrip.obj")) if l.startswith("f "))
     assert 860_000 <= n <= 880_000, n
+
+
+def test_bench_frame_reference_arm_runs_on_cpu(built):
+    """bench.py --workload frame_finish --impl reference times the reference's own host code (or the restatement when
+    oracle/_ref is absent) and prints the contract's JSON line; no GPU involved."""
+    import json, subprocess, sys, os
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.check_output([sys.executable, os.path.join(repo, "bench.py"), "--workload", "frame_finish", "--impl", "reference", "--steps", "1"],
+                                  timeout=300).decode()
+    line = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert line["impl"] == "reference" and line["unit"] == "Mpixels/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["e2e"]["value"] == line["value"]
