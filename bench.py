@@ -13,6 +13,7 @@ Workloads = BASELINE.json configs on the generated stand-in scenes (the referenc
   water_sppm   configs[3]  water caustic, SPPM, 1024x1024 light paths (~1M photons / iteration)
   cornell      configs[0]  Cornell box 512x512 NEE+MIS
   trace_batch  SURVEY 8d micro: closest-hit / any-hit kernels alone on identical ray batches (ours vs the reference's routines)
+  hashgrid     SURVEY 8d micro / a15: photon hash grid build vs the reference's buildHashGrid on identical photon sets
   frame_finish SURVEY 8f row 2: the step after the path (clean + tonemap + gamma + BGR8 rows of a 4K frame), metric Mpixels/s
 metric = Mrays/s: closest-hit + shadow rays actually traced (device counters); paths/s is reported beside it.
 
@@ -712,13 +713,135 @@ def run_trace(args):
     scene.close()
 
 
+GRID_DESC = "photon hash grid build (SURVEY 8d micro / row a15): hash + radix sort + cell tables on photon sets shaped like SPPM 1M and VCM 4K iterations"
+
+
+def grid_photons(n, seed):
+    """Photons on the six faces of a 10^3 box (uniform) with a fifth of them in two Gaussian caustic blobs on the floor."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    p = rng.random((n, 3), dtype=np.float32) * 10.0
+    face = rng.integers(0, 6, n)
+    for a in range(3):
+        p[face == 2 * a, a] = 0.0
+        p[face == 2 * a + 1, a] = 10.0
+    k = n // 5
+    blob = rng.normal(0.0, 0.15, (k, 2)).astype(np.float32)
+    ctr = np.where(rng.random(k)[:, None] < 0.5, np.float32([3.0, 6.5]), np.float32([7.2, 2.8]))
+    p[:k, 0] = np.clip(ctr[:, 0] + blob[:, 0], 0, 10); p[:k, 1] = 0.0; p[:k, 2] = np.clip(ctr[:, 1] + blob[:, 1], 0, 10)
+    return np.ascontiguousarray(p[:, 0]), np.ascontiguousarray(p[:, 1]), np.ascontiguousarray(p[:, 2])
+
+
+GRID_CASES = [("sppm_1m", 1 << 20, 10 << 20), ("vcm4k_typical", 10_500_000, 82_944_000)]
+GRID_FULL = [("vcm4k_full", 82_944_000, 82_944_000)]
+
+
+def ref_grid(px, py, pz, max_photons, radius, scene_min, tmp):
+    import numpy as np
+    ref = os.path.join(REPO, "oracle", "_ref", "novum_ref")
+    ip, op = os.path.join(tmp, "photons.bin"), os.path.join(tmp, "grid.bin")
+    with open(ip, "wb") as f:
+        np.array([len(px), max_photons], np.int32).tofile(f); np.array([radius] + list(scene_min), np.float32).tofile(f)
+        px.tofile(f); py.tofile(f); pz.tofile(f)
+    out = subprocess.check_output([ref, "grid", ip, op], stderr=subprocess.STDOUT).decode()
+    js = json.loads(re.search(r"NOVUM_REF_JSON (\{.*\})", out).group(1))
+    res = np.fromfile(op, np.uint32).reshape(4, -1)
+    os.remove(ip); os.remove(op)
+    return js, res
+
+
+def run_grid(args):
+    """--workload hashgrid: one step = one grid build per case. value = photons/s over the cases, device-resident (CUDA events in the
+    library around hash + sort + tables); e2e = novum_hashgrid_build with host positions in and sorted order + tables out."""
+    import numpy as np
+    import torch
+    import cudapathtracer_b200 as nb
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cases = GRID_CASES + (GRID_FULL if args.grid_full else [])
+    radius, scene_min = 0.0866, (0.0, 0.0, 0.0)       # 0.01 x the box's bounding radius, the reference's initial merge radius
+    tmp = tempfile.mkdtemp()
+    ref_bin = os.path.join(REPO, "oracle", "_ref", "novum_ref")
+    if args.impl == "reference":
+        per, tot_ms, tot_n = {}, 0.0, 0
+        for name, n, mx in cases:
+            px, py, pz = grid_photons(n, 7)
+            js, _ = ref_grid(px, py, pz, mx, radius, scene_min, tmp)
+            per[name] = {"photons": n, "max_photons": mx, "build_ms": js["build_ms"], "reorder_ms": js["reorder_ms"], "mphotons_per_s": n / js["build_ms"] / 1e3}
+            tot_ms += js["build_ms"]; tot_n += n
+        val = tot_n / tot_ms / 1e3
+        print(json.dumps({"impl": "reference", "metric": "Mphotons/s", "value": val, "unit": "Mphotons/s", "n_gpus": 1, "steps": 3, "warmup": 0, "ms_per_step": tot_ms,
+                          "higher_is_better": True, "config": {"workload": GRID_DESC}, "cases": per,
+                          "cpu_baseline": {"value": val, "unit": "Mphotons/s", "cores": os.cpu_count(), "kind": "reference",
+                                           "sample": "the reference's own buildHashGrid (computeHashes, cub::DeviceRadixSort, reorderPhotons, 2 table memsets, buildTable; best of 3) on one B200"},
+                          "e2e": {"value": val, "unit": "Mphotons/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+    if not torch.cuda.is_available() or nb.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    dev = torch.device("cuda", 0)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    clocks = ClockSampler(0)
+    clocks.start()
+    per, tot_ms, tot_n, algo = {}, 0.0, 0, 0.0
+    e2e_s, e2e_h2d, e2e_d2h = 0.0, 0, 0
+    for name, n, mx in cases:
+        px, py, pz = grid_photons(n, 7)
+        g = nb.HashGrid(mx)
+        d = [torch.from_numpy(a).to(dev) for a in (px, py, pz)]
+        for i in range(args.warmup):
+            g.build_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), n, scene_min, radius, True)
+        ms = 0.0
+        for i in range(args.steps):
+            flush.fill_(i); torch.cuda.synchronize()
+            g.build_device(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), n, scene_min, radius, True)
+            ms += g.last_ms() / args.steps
+        bits = max(1, int(np.ceil(np.log2(g.table_size))))
+        passes = (bits + 7) // 8
+        bpp = 12 + 8 + passes * 20 + 12
+        per[name] = {"photons": n, "max_photons": mx, "table_size": g.table_size, "build_ms": ms, "mphotons_per_s": n / ms / 1e3, "radix_passes": passes,
+                     "bytes_per_photon": bpp, "gbs": n * bpp / (ms * 1e-3) / 1e9}
+        tot_ms += ms; tot_n += n; algo += n * bpp
+        t0 = time.time()
+        idx, hsh, cs, ce = g.build(px, py, pz, scene_min, radius)
+        e2e_s += time.time() - t0; e2e_h2d += 12 * n; e2e_d2h += 8 * n + 8 * g.table_size
+        if os.path.exists(ref_bin) and not args.no_cpu_baseline:
+            js, res = ref_grid(px, py, pz, mx, radius, scene_min, tmp)
+            per[name].update({"reference_build_ms": js["build_ms"], "reference_reorder_ms": js["reorder_ms"], "speedup": js["build_ms"] / ms,
+                              "speedup_without_reference_reorder": (js["build_ms"] - js["reorder_ms"]) / ms,
+                              "parity": {"sorted_hash_equal": bool(np.array_equal(hsh, res[0])), "sorted_index_equal": bool(np.array_equal(idx, res[1])),
+                                         "cell_start_equal": bool(np.array_equal(cs[hsh], res[2])), "cell_end_equal": bool(np.array_equal(ce[hsh], res[3]))}})
+        g.close()
+        del d
+    clk = clocks.stop()
+    peak, peak_src = peaks()
+    line = {"metric": "Mphotons/s", "value": tot_n / tot_ms / 1e3, "unit": "Mphotons/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": GRID_DESC, "radius": radius, "l2": "256 MB flush before every build",
+                       "scope": "hash + LSD radix sort of (hash, index) + cell tables (+ clearing the previous build's slots); the 32 B photon-record gather of the VCM engine (bdReorderPhotons) is not part of this entry point, the reference's total includes its 34 B reorder (reported separately)"},
+            "cases": per, "gpu_launches": None, "clocks": clk,
+            "e2e": {"value": tot_n / e2e_s / 1e6, "unit": "Mphotons/s", "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
+                    "note": "novum_hashgrid_build: host positions in, sorted index + hash + both cell tables out (the tables dominate the D2H)"},
+            "roofline": {"bound": "hbm", "kernel": "hashKernel + radix passes (digitHistogram, scatterPass) + tableKernel", "achieved": algo / (tot_ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": algo / (tot_ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src}}
+    if not args.no_cpu_baseline:
+        from oracle import oracle_binding as ob
+        px, py, pz = grid_photons(1 << 20, 7)
+        t0 = time.time()
+        ob.hashgrid_build(px, py, pz, scene_min, radius, ob.next_prime(2 * (10 << 20)))
+        dt = time.time() - t0
+        line["cpu_baseline"] = {"value": (1 << 20) / dt / 1e6, "unit": "Mphotons/s", "cores": 1, "kind": "port",
+                                "sample": f"the CPU restatement (hash, stable sort, tables) on the 1M-photon case ({dt:.2f} s); the reference itself has no CPU path — its GPU build is in cases[*].reference_build_ms"}
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=None, help="timed steps (default 4; frame_finish: 50 — its step is a 55 us kernel)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish", "trace_batch"])
+    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish", "trace_batch", "hashgrid"])
+    ap.add_argument("--grid-full", action="store_true", help="hashgrid: add the 82.9 M-photon worst case of a 4K VCM iteration")
     ap.add_argument("--rays-side", type=int, default=2048, help="trace_batch: the primary batch is rays_side^2 rays (2048 -> 4.19 M)")
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
     ap.add_argument("--sharding", default="striped", choices=["striped", "tiles"])
@@ -730,6 +853,8 @@ def main():
         args.steps = 50 if (args.workload in ("frame_finish", "trace_batch") and args.impl == "ours") else 4
     if args.workload == "trace_batch":
         run_trace(args)
+    elif args.workload == "hashgrid":
+        run_grid(args)
     elif args.workload == "frame_finish":
         (run_frame_reference if args.impl == "reference" else run_frame)(args)
     elif args.impl == "reference":

@@ -189,12 +189,77 @@ static int cmdClean(int argc, char** argv) {
     return err == cudaSuccess ? 0 : 2;
 }
 
+// ---- photon hash grid: the reference's own buildHashGrid (deviceCode.cu:3140-3198) on a given photon set ------------------
+//   novum_ref grid <photons.bin> <out.bin>
+// photons.bin: int32 n, int32 maxPhotons, float radius, float sceneMin[3], then x[n], y[n], z[n] (float32).
+// out.bin: uint32 sortedHash[n], uint32 sortedIndex[n], uint32 cellStart[sortedHash[i]] (n), uint32 cellEnd[sortedHash[i]] (n).
+// Buffers are allocated as launch_VCM does (deviceCode.cu:3276-3296): table = GetNextPrime(2 * maxPhotons), cub scratch sized for maxPhotons.
+__global__ void refGatherTable(const unsigned int* hashes, const unsigned int* cs, const unsigned int* ce, int n, unsigned int* o0, unsigned int* o1) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { o0[i] = cs[hashes[i]]; o1[i] = ce[hashes[i]]; }
+}
+
+static int cmdGrid(int argc, char** argv) {
+    FILE* f = fopen(argv[2], "rb"); if (!f) { fprintf(stderr, "cannot open %s\n", argv[2]); return 1; }
+    int n = 0, maxPhotons = 0; float radius = 0, mn[3];
+    if (fread(&n, 4, 1, f) != 1 || fread(&maxPhotons, 4, 1, f) != 1 || fread(&radius, 4, 1, f) != 1 || fread(mn, 4, 3, f) != 3 || n <= 0 || n > maxPhotons) return 1;
+    std::vector<float> h((size_t)n * 3);
+    if (fread(h.data(), 4, h.size(), f) != h.size()) return 1;
+    fclose(f);
+    auto mkPhotons = [&](size_t cap) {
+        Photons p;
+        p.pos_x = devAllocZero<float>(cap); p.pos_y = devAllocZero<float>(cap); p.pos_z = devAllocZero<float>(cap);
+        p.packedWi = devAllocZero<unsigned int>(cap); p.packedNormal = devAllocZero<unsigned int>(cap);
+        p.beta_x = devAllocZero<half>(cap); p.beta_y = devAllocZero<half>(cap); p.beta_z = devAllocZero<half>(cap);
+        p.d_vm = devAllocZero<float>(cap); p.d_vcm = devAllocZero<float>(cap);
+        return p;
+    };
+    Photons ph = mkPhotons(n), sorted = mkPhotons(n);
+    cudaMemcpy(ph.pos_x, h.data(), 4 * (size_t)n, cudaMemcpyHostToDevice);
+    cudaMemcpy(ph.pos_y, h.data() + n, 4 * (size_t)n, cudaMemcpyHostToDevice);
+    cudaMemcpy(ph.pos_z, h.data() + 2 * (size_t)n, 4 * (size_t)n, cudaMemcpyHostToDevice);
+    unsigned int *kin = devAllocZero<unsigned int>(n), *kout = devAllocZero<unsigned int>(n), *iin = devAllocZero<unsigned int>(n), *iout = devAllocZero<unsigned int>(n);
+    int hashTableSize = GetNextPrime(maxPhotons * 2);
+    unsigned int *cs, *ce; cudaMalloc(&cs, (size_t)hashTableSize * 4); cudaMalloc(&ce, (size_t)hashTableSize * 4);
+    void* tmp = NULL; size_t tmpBytes = 0;
+    cub::DeviceRadixSort::SortPairs(tmp, tmpBytes, kin, kout, iin, iout, n);
+    cudaMalloc(&tmp, tmpBytes);
+    float4 sceneMin = f4(mn[0], mn[1], mn[2]);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f, bestReorder = 1e30f;
+    for (int rep = 0; rep < 3; rep++) {
+        cudaDeviceSynchronize();
+        cudaEventRecord(e0);
+        buildHashGrid(ph, sorted, n, kin, kout, iin, iout, tmp, tmpBytes, cs, ce, sceneMin, radius, hashTableSize);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1); best = fminf(best, ms);
+        cudaEventRecord(e0);
+        reorderPhotons<<<(n + 255) / 256, 256>>>(ph, sorted, n, iout);      // its share of the total, timed on its own
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms, e0, e1); bestReorder = fminf(bestReorder, ms);
+    }
+    unsigned int *o0 = devAllocZero<unsigned int>(n), *o1 = devAllocZero<unsigned int>(n);
+    refGatherTable<<<(n + 255) / 256, 256>>>(kout, cs, ce, n, o0, o1);
+    cudaError_t err = cudaDeviceSynchronize();
+    std::vector<unsigned int> out((size_t)n * 4);
+    cudaMemcpy(out.data(), kout, 4 * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(out.data() + n, iout, 4 * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(out.data() + 2 * (size_t)n, o0, 4 * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(out.data() + 3 * (size_t)n, o1, 4 * (size_t)n, cudaMemcpyDeviceToHost);
+    f = fopen(argv[3], "wb"); if (f) { fwrite(out.data(), 4, out.size(), f); fclose(f); }
+    printf("\nNOVUM_REF_JSON {\"mode\": \"grid\", \"photons\": %d, \"table_size\": %d, \"build_ms\": %.4f, \"reorder_ms\": %.4f, \"cuda_error\": %d}\n",
+           n, hashTableSize, best, bestReorder, (int)err);
+    return err == cudaSuccess ? 0 : 2;
+}
+
 int main(int argc, char** argv) {
     if (argc >= 3 && !strcmp(argv[1], "render")) return cmdRender(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "trace")) return cmdTrace(argc, argv);
+    if (argc >= 4 && !strcmp(argv[1], "grid")) return cmdGrid(argc, argv);
     if (argc >= 7 && !strcmp(argv[1], "bmp")) return cmdBmp(argc, argv);
     if (argc >= 8 && !strcmp(argv[1], "clean")) return cmdClean(argc, argv);
     fprintf(stderr, "usage: novum_ref render <sceneDir> [--spp N] [--out f.raw] | trace <sceneDir> <rays.bin> <out.bin> [--shadow]\n"
-                    "       novum_ref bmp <frame.raw> <w> <h> <postProcess> <out.bmp> [--time N] | clean <acc.raw> <overlay.raw> <w> <h> <n> <out.raw>\n");
+                    "       novum_ref bmp <frame.raw> <w> <h> <postProcess> <out.bmp> [--time N] | clean <acc.raw> <overlay.raw> <w> <h> <n> <out.raw>\n"
+                    "       novum_ref grid <photons.bin> <out.bin>\n");
     return 64;
 }
