@@ -30,12 +30,32 @@ float mergeRadiusAt(float initialRadius, float alpha, int currSample) {   // uti
 
 namespace {
 
+// floor((p - min) / cell) exactly as gridIndex computes it (an IEEE division), at the cost of a multiply: the product with the
+// rounded reciprocal is within 2 ulp of the quotient, so the two floors can differ only when the product lies within a few ulp
+// of an integer — then, and only then, the division is done (the literal form made this kernel instruction-bound: 184 warp
+// instructions per 32 photons, three divisions + a 32-bit modulo by a run-time prime).
+__device__ __forceinline__ int cellCoord(float v, float cell, float rcell) {
+    const float q = v * rcell;
+    if (q == 0.0f) return v < 0.0f ? -1 : 0;      // photons ON the scene's lower faces (v = 0) are common: no division for them
+    float f = floorf(q);
+    if (fminf(q - f, (f + 1.0f) - q) <= fabsf(q) * 6e-7f) f = floorf(__fdiv_rn(v, cell));
+    return (int)f;
+}
+
+// n % p for 32-bit n and a fixed p with magic = floor((2^64 - 1) / p) + 1 (Lemire, Kaser, Kurz 2019: exact for every 32-bit n)
+__device__ __forceinline__ unsigned fastMod(unsigned n, unsigned p, unsigned long long magic) {
+    return (unsigned)__umul64hi(magic * (unsigned long long)n, (unsigned long long)p);
+}
+
 __global__ void hashKernel(const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz, int stride,
-                           int n, GridParams g, uint32_t* __restrict__ keys, uint32_t* __restrict__ index) {
+                           int n, GridParams g, float rcell, unsigned long long magic, uint32_t* __restrict__ keys, uint32_t* __restrict__ index) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     size_t o = (size_t)i * stride;
-    keys[i] = hashCell(gridIndex(px[o], py[o], pz[o], g), g.tableSize);
+    const int cx = cellCoord(__ldg(px + o) - g.minX, g.cell, rcell), cy = cellCoord(__ldg(py + o) - g.minY, g.cell, rcell),
+              cz = cellCoord(__ldg(pz + o) - g.minZ, g.cell, rcell);
+    const unsigned h = (73856093u * (unsigned)cx) ^ (19349663u * (unsigned)cy) ^ (83492791u * (unsigned)cz);      // integratorUtilities.cuh:405-412
+    keys[i] = fastMod(h, g.tableSize, magic);
     index[i] = (uint32_t)i;
 }
 
@@ -124,7 +144,8 @@ static int hashGridBuildStrided(HashGridDevice& g, const float* px, const float*
     }
     g.n = n; g.prevN = n;
     if (n == 0) return 0;
-    hashKernel<<<(n + T - 1) / T, T, 0, stream>>>(px, py, pz, stride, n, g.params, g.keys, g.index);
+    hashKernel<<<(n + T - 1) / T, T, 0, stream>>>(px, py, pz, stride, n, g.params, 1.0f / mergeRadius, 0xFFFFFFFFFFFFFFFFull / g.tableSize + 1ull, g.keys,
+                                                  g.index);
     ++g.launches;
     int bits = 1;
     while (bits < 32 && (1ull << bits) < (unsigned long long)g.tableSize) ++bits;

@@ -1,0 +1,6 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_hashgrid.py tests/test_gpu_trace.py -m gpu -q -x > gpurun_out/pytest_58.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_58.log
+timeout 900 python bench.py --workload hashgrid --steps 5 --warmup 2 --no-cpu-baseline > gpurun_out/bench_grid_58.log 2>&1; echo "rc=$?" >> gpurun_out/bench_grid_58.log
+timeout 900 python bench.py --workload hashgrid --steps 3 --warmup 1 > gpurun_out/bench_grid_58p.log 2>&1; echo "rc=$?" >> gpurun_out/bench_grid_58p.log
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_grid_58.csv python bench.py --workload hashgrid --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_l_grid_58.log 2>&1
