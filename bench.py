@@ -302,7 +302,9 @@ def run_ours(args):
                        "sharding": (f"pixel rows striped over ranks, photons exchanged every iteration ({tiler.exchange_mode}), frames sum-reduced at the end"
                                     if tiles else "sample passes / iterations striped over ranks, frames sum-reduced (NCCL) at the end"),
                        "l2": "256 MB flush between steps; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
-                       "scene_load_s": round(load_s, 3)},
+                       "scene_load_s": round(load_s, 3), "scene_parse_s": round(info["parse_ms"] * 1e-3, 3), "bvh8_build_ms": round(info["bvh8_build_ms"], 3),
+                       "bvh8_build_launches": info["bvh8_build_launches"],
+                       "scene_load_note": "first load in this process: bvh8_build_ms includes CUDA module loading and the build's cudaMallocs; repeated loads: parse 0.30 s + build 7.4 ms for 871k triangles (profiles/r1_scene_load_breakdown.txt)"},
             "paths_per_s": tot_paths / (max_dev_ms * 1e-3), "rays_per_path": tot_rays / max(1.0, tot_paths),
             "wall_ms_per_step": max_wall_ms / args.steps,
             "e2e": {"value": float(e2e_t.item()) / e2e_wall / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 112 + 200,
@@ -759,6 +761,8 @@ def run_grid(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     cases = GRID_CASES + (GRID_FULL if args.grid_full else [])
+    if args.grid_small:
+        cases = [("small", 200_000, 1 << 20)]
     radius, scene_min = 0.0866, (0.0, 0.0, 0.0)       # 0.01 x the box's bounding radius, the reference's initial merge radius
     tmp = tempfile.mkdtemp()
     ref_bin = os.path.join(REPO, "oracle", "_ref", "novum_ref")
@@ -841,6 +845,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish", "trace_batch", "hashgrid"])
+    ap.add_argument("--grid-small", action="store_true", help="hashgrid: one 200k-photon case (used by the GPU test suite)")
     ap.add_argument("--grid-full", action="store_true", help="hashgrid: add the 82.9 M-photon worst case of a 4K VCM iteration")
     ap.add_argument("--rays-side", type=int, default=2048, help="trace_batch: the primary batch is rays_side^2 rays (2048 -> 4.19 M)")
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")

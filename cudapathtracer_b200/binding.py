@@ -107,6 +107,9 @@ def _declare(L):
     L.novum_scene_info.argtypes = [vp, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(cf * 3), C.POINTER(cf * 3), C.POINTER(cf)]
     L.novum_scene_counts.argtypes = [vp] + [C.POINTER(ci)] * 5
     L.novum_scene_download.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.novum_scene_timings.argtypes = [vp, C.POINTER(cf), C.POINTER(cf), C.POINTER(ci)]
+    L.novum_parse_double.restype = C.c_double
+    L.novum_parse_double.argtypes = [C.c_char_p, C.POINTER(ci)]
     L.novum_material_table.argtypes = [vp]
     L.novum_camera_make.argtypes = [C.POINTER(RenderConfig), C.POINTER(Camera)]
     L.novum_trace_closest.argtypes = [vp, vp, ci, vp]
@@ -232,7 +235,10 @@ class Scene:
         nt, nl, nn, r = C.c_int(), C.c_int(), C.c_int(), C.c_float()
         mn, mx = (C.c_float * 3)(), (C.c_float * 3)()
         _check(lib().novum_scene_info(self.h, C.byref(nt), C.byref(nl), C.byref(nn), C.byref(mn), C.byref(mx), C.byref(r)), "novum_scene_info")
-        return {"tris": nt.value, "lights": nl.value, "bvh8_nodes": nn.value, "min": list(mn), "max": list(mx), "radius": r.value}
+        pm, bm, bl = C.c_float(), C.c_float(), C.c_int()
+        _check(lib().novum_scene_timings(self.h, C.byref(pm), C.byref(bm), C.byref(bl)), "novum_scene_timings")
+        return {"tris": nt.value, "lights": nl.value, "bvh8_nodes": nn.value, "min": list(mn), "max": list(mx), "radius": r.value,
+                "parse_ms": pm.value, "bvh8_build_ms": bm.value, "bvh8_build_launches": bl.value}
 
     def download(self):
         c = [C.c_int() for _ in range(5)]

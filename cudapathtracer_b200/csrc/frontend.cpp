@@ -8,8 +8,11 @@
 // zero; faces without vn/vt get a flat face normal / a zero uv instead of index -1.
 #include "scene.h"
 #include <algorithm>
+#include <cctype>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
@@ -217,47 +220,124 @@ struct HostMesh {
     int numLights = 0;
 };
 
+// up to n doubles exactly as sscanf("%lf ...") reads them (strtod is what %lf calls; stops at the first field that does not parse)
+// strtod for the common OBJ spellings: [ws][sign]digits[.digits][e[sign]digits] with at most 15 significant digits and a decimal
+// exponent within +-22 is an integer below 2^53 times or divided by an exactly representable power of ten, i.e. ONE correctly
+// rounded double operation — the same value strtod returns (Clinger's fast path). Anything else goes to strtod itself.
+static double fastStrtod(const char* p, char** end) {
+    static const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                      1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    const char* s = p;
+    while (isspace((unsigned char)*s)) ++s;
+    bool neg = false;
+    if (*s == '+' || *s == '-') { neg = *s == '-'; ++s; }
+    if (!((*s >= '0' && *s <= '9') || (*s == '.' && s[1] >= '0' && s[1] <= '9'))) return strtod(p, end);   // inf, nan, hex, junk
+    if (*s == '0' && (s[1] == 'x' || s[1] == 'X')) return strtod(p, end);
+    unsigned long long mant = 0; int sig = 0, exp10 = 0;
+    for (; *s >= '0' && *s <= '9'; ++s) {
+        if (sig > 0 || *s != '0') { if (sig < 19) mant = mant * 10 + (unsigned)(*s - '0'); else ++exp10; ++sig; }
+    }
+    if (*s == '.') {
+        ++s;
+        for (; *s >= '0' && *s <= '9'; ++s) {
+            if (sig > 0 || *s != '0') { if (sig < 19) { mant = mant * 10 + (unsigned)(*s - '0'); --exp10; } ++sig; }
+            else --exp10;
+        }
+    }
+    if (*s == 'e' || *s == 'E') {
+        const char* t = s + 1; bool eneg = false;
+        if (*t == '+' || *t == '-') { eneg = *t == '-'; ++t; }
+        if (*t >= '0' && *t <= '9') {
+            int e = 0;
+            for (; *t >= '0' && *t <= '9'; ++t) if (e < 100000) e = e * 10 + (*t - '0');
+            exp10 += eneg ? -e : e;
+            s = t;
+        }
+    }
+    if (sig > 15 || exp10 < -22 || exp10 > 22) return strtod(p, end);
+    double v = (double)mant;
+    v = exp10 < 0 ? v / kPow10[-exp10] : v * kPow10[exp10];
+    *end = const_cast<char*>(s);
+    return neg ? -v : v;
+}
+
+static int scanDoubles(const char* p, double* out, int n) {
+    int got = 0;
+    while (got < n) {
+        char* e = nullptr;
+        double v = fastStrtod(p, &e);
+        if (e == p) break;
+        out[got++] = v; p = e;
+    }
+    return got;
+}
+
+// Same records as the reference's readObjSimple (main.cu:936-1068) in the same order; the file is read in one piece and walked with
+// strtod / atoi on the buffer (the getline + sscanf + istringstream form of the first version took 0.85 s for the 871k-triangle
+// dragon, all of it parsing).
 int loadObj(const std::string& file, HostMesh& M, const float emission[3], int materialID, float yOffset) {
-    std::ifstream in(file);
-    if (!in.is_open()) return NOVUM_E_IO;
+    FILE* fp = fopen(file.c_str(), "rb");
+    if (!fp) return NOVUM_E_IO;
+    std::string buf;
+    {
+        fseek(fp, 0, SEEK_END); long sz = ftell(fp); fseek(fp, 0, SEEK_SET);
+        if (sz < 0) { fclose(fp); return NOVUM_E_IO; }
+        buf.resize((size_t)sz);
+        size_t got = sz ? fread(&buf[0], 1, (size_t)sz, fp) : 0;
+        fclose(fp);
+        buf.resize(got);
+    }
     int startIndex = (int)M.pos.size(), nStart = (int)M.nrm.size(), uvStart = (int)M.uv.size();
     bool isLight = emission[0] * emission[0] + emission[1] * emission[1] + emission[2] * emission[2] > 0.f;
     int sharedZeroUV = -1;
-    std::string line;
     std::vector<int> vi, ti, ni;
-    while (std::getline(in, line)) {
-        if (line.empty() || line[0] == '#' || line[0] == 's') continue;
-        const char* p = line.c_str();
+    char* cur = buf.empty() ? nullptr : &buf[0];
+    char* const endAll = cur ? cur + buf.size() : nullptr;
+    while (cur && cur < endAll) {
+        char* p = cur;
+        char* nl = (char*)memchr(cur, '\n', (size_t)(endAll - cur));
+        char* lineEnd = nl ? nl : endAll;
+        cur = nl ? nl + 1 : endAll;
+        const char saved = *lineEnd;            // terminate the line in place (std::string keeps a writable NUL at the end)
+        *lineEnd = 0;
+        if (p == lineEnd || p[0] == '#' || p[0] == 's') { *lineEnd = saved; continue; }
         if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) {
-            double x = 0, y = 0, z = 0;
-            sscanf(p + 2, "%lf %lf %lf", &x, &y, &z);
-            NovumFloat4 q = {(float)x, (float)y, (float)z, 0.f};
+            double d[3] = {0, 0, 0};
+            scanDoubles(p + 2, d, 3);
+            NovumFloat4 q = {(float)d[0], (float)d[1], (float)d[2], 0.f};
             q.y = q.y + yOffset;
             M.pos.push_back(q);
         } else if (p[0] == 'v' && p[1] == 't') {
-            double u = 0, v = 0;
-            sscanf(p + 3, "%lf %lf", &u, &v);
-            M.uv.push_back({(float)u, 1.0f - (float)v});
+            double d[2] = {0, 0};
+            scanDoubles(p + 3, d, 2);
+            M.uv.push_back({(float)d[0], 1.0f - (float)d[1]});
         } else if (p[0] == 'v' && p[1] == 'n') {
-            double x = 0, y = 0, z = 0;
-            int got = sscanf(p + 3, "%lf %lf %lf", &x, &y, &z);
-            NovumFloat4 n = {(float)x, (float)y, (float)z, 0.f};
-            if (got != 3 || std::isnan(x) || std::isnan(y) || std::isnan(z) || n.x * n.x + n.y * n.y + n.z * n.z < 1e-12f)
+            double d[3] = {0, 0, 0};
+            int got = scanDoubles(p + 3, d, 3);
+            NovumFloat4 n = {(float)d[0], (float)d[1], (float)d[2], 0.f};
+            if (got != 3 || std::isnan(d[0]) || std::isnan(d[1]) || std::isnan(d[2]) || n.x * n.x + n.y * n.y + n.z * n.z < 1e-12f)
                 n = {0.f, 1.f, 0.f, 0.f};
             M.nrm.push_back(n);
         } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
             vi.clear(); ti.clear(); ni.clear();
-            std::istringstream iss(line.substr(2));
-            std::string tok;
-            while (iss >> tok) {
+            const char* s = p + 2;
+            while (true) {
+                while (*s && isspace((unsigned char)*s)) ++s;          // operator>> on a string: whitespace-separated tokens
+                if (!*s) break;
+                const char* tokEnd = s;
+                while (*tokEnd && !isspace((unsigned char)*tokEnd)) ++tokEnd;
                 int a = 0, b = 0, c = 0;
-                const char* s = tok.c_str();
                 a = atoi(s);
-                const char* s1 = strchr(s, '/');
-                if (s1) { if (s1[1] != '/' && s1[1] != 0) b = atoi(s1 + 1); const char* s2 = strchr(s1 + 1, '/'); if (s2 && s2[1]) c = atoi(s2 + 1); }
+                const char* s1 = (const char*)memchr(s, '/', (size_t)(tokEnd - s));
+                if (s1) {
+                    if (s1 + 1 != tokEnd && s1[1] != '/') b = atoi(s1 + 1);
+                    const char* s2 = (const char*)memchr(s1 + 1, '/', (size_t)(tokEnd - (s1 + 1)));
+                    if (s2 && s2 + 1 != tokEnd) c = atoi(s2 + 1);
+                }
                 if (a != 0) vi.push_back(a - 1);
                 if (b != 0) ti.push_back(b - 1);
                 if (c != 0) ni.push_back(c - 1);
+                s = tokEnd;
             }
             bool hasUV = ti.size() == vi.size(), hasN = ni.size() == vi.size();
             int n = (int)vi.size();
@@ -290,6 +370,7 @@ int loadObj(const std::string& file, HostMesh& M, const float emission[3], int m
                 if (isLight) M.numLights++;
             }
         }
+        *lineEnd = saved;
     }
     return 0;
 }
@@ -381,6 +462,7 @@ int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene
     size_t slash = cfgDir.find_last_of('/');
     cfgDir = slash == std::string::npos ? std::string(".") : cfgDir.substr(0, slash);
     HostMesh M;
+    const auto parseT0 = std::chrono::steady_clock::now();
     for (const MeshCfg& m : meshes) {
         float e[3] = {m.mult * m.color[0], m.mult * m.color[1], m.mult * m.color[2]};
         bool emissive = m.color[0] * m.color[0] + m.color[1] * m.color[1] + m.color[2] * m.color[2] > 0.f;
@@ -392,10 +474,20 @@ int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene
         if (r) fprintf(stderr, "Error: Could not open OBJ file %s\n", m.path.c_str());   // main.cu:941-944: keeps going
     }
     if (M.tris.empty()) return NOVUM_E_IO;   // main.cu:505-508
+    const float parseMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - parseT0).count();
     rc = novum_scene_create(M.pos.data(), (int)M.pos.size(), M.nrm.data(), (int)M.nrm.size(), M.uv.data(), (int)M.uv.size(),
                             M.tris.data(), (int)M.tris.size(), mats, 24, texels.data(), (int)texels.size(), out);
     if (rc == 0) for (const MeshCfg& m : meshes) (*out)->meshPaths.push_back(m.path);
+    if (rc == 0) (*out)->parseMs = parseMs;
     return rc;
+}
+
+double novum_parse_double(const char* text, int* consumed) {
+    if (!text) { if (consumed) *consumed = 0; return 0.0; }
+    char* e = nullptr;
+    double v = fastStrtod(text, &e);
+    if (consumed) *consumed = (int)(e - text);
+    return v;
 }
 
 int novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, float scale) {

@@ -227,6 +227,14 @@ int novum_scene_info(const NovumScene* s, int* nTri, int* nLights, int* nBvh8Nod
     return 0;
 }
 
+int novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs, int* bvhLaunches) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (parseMs) *parseMs = s->parseMs;
+    if (bvhBuildMs) *bvhBuildMs = s->bvh.buildMs;
+    if (bvhLaunches) *bvhLaunches = s->bvh.kernelLaunches;
+    return 0;
+}
+
 int novum_scene_counts(const NovumScene* s, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights) {
     if (!s) return NOVUM_E_NOSCENE;
     if (nPos) *nPos = s->nPos; if (nNorm) *nNorm = s->nNorm; if (nUV) *nUV = s->nUV;

@@ -26,6 +26,7 @@ struct NovumScene {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float lastTraceMs = 0.f;
+    float parseMs = 0.f;                  // host time of the config / OBJ front end (novum_scene_load_config only)
     // traversal counters
     bool countersOn = false;
     int profileFlags = 0;                 // novum_set_profile

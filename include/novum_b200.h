@@ -195,6 +195,12 @@ int  novum_scene_from_device(const NovumVertices* d_vertices, int vertNum, const
 void novum_scene_destroy(NovumScene* s);
 int  novum_scene_info(const NovumScene* s, int* nTri, int* nLights, int* nBvh8Nodes, float sceneMin[3], float sceneMax[3],
                       float* sceneRadius);
+/* the step before the path: host time of the config / OBJ front end (main.cu:936-1068 equivalent; 0 unless the scene came
+ * from novum_scene_load_config) and CUDA-event time + launch count of the device BVH8 build that replaces main.cu:20-233 */
+int  novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs, int* bvhLaunches);
+/* the OBJ front end's number reader (what sscanf("%lf") / operator>> return in main.cu:936-1068, i.e. strtod): exported so that its
+ * fast path can be held to strtod by the CPU tests. *consumed = characters read (0: no number). */
+double novum_parse_double(const char* text, int* consumed);
 int  novum_material_table(NovumMaterial* out24);                      /* main.cu:397-467, 24 entries */
 int  novum_camera_make(const NovumRenderConfig* cfg, NovumCamera* out); /* objects.cuh:221-266, 309-325 */
 /* copies of the scene arrays back to host, for oracles and tests */

@@ -110,3 +110,41 @@ def test_bench_frame_reference_arm_runs_on_cpu(built):
     line = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
     assert line["impl"] == "reference" and line["unit"] == "Mpixels/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["e2e"]["value"] == line["value"]
+
+
+def test_obj_number_reader_equals_strtod(built):
+    """The OBJ loader's fast number path (integer mantissa x exact power of ten) must return what strtod returns — bit for bit — and
+    consume the same characters, falling back to strtod for everything outside its exact range."""
+    import ctypes as C
+    import struct
+    import cudapathtracer_b200 as nb
+    L = nb.lib()
+    libc = C.CDLL(None)
+    libc.strtod.restype = C.c_double
+    libc.strtod.argtypes = [C.c_char_p, C.POINTER(C.c_char_p)]
+
+    def ours(t):
+        n = C.c_int()
+        return L.novum_parse_double(t, C.byref(n)), n.value
+
+    def ref(t):
+        buf = C.create_string_buffer(t)
+        end = C.c_char_p()
+        v = libc.strtod(buf, C.byref(end))
+        return v, C.cast(end, C.c_void_p).value - C.addressof(buf)
+
+    rng = np.random.default_rng(5)
+    cases = [b"0", b"-0", b"0.0", b"-0.0", b"1.", b".5", b"-.5", b"1e5", b"1E-5", b"1e", b"1e+", b"12345678901234567890", b"123456789012345",
+             b"1234567890123456", b"1e22", b"1e23", b"1e-22", b"1e-23", b"3.14159 2.7", b"nan", b"inf", b"-inf", b"0x10", b"+7", b"  42", b"1.5e3x",
+             b"9007199254740993", b"0.1", b"1e308", b"4.9e-324", b"", b" ", b"-", b"+.", b"1.e2", b".e2", b"\t-12.5\r", b"7/8/9"]
+    for v in rng.standard_normal(20000) * 10:
+        cases += [b"%.6f" % v, b"%.9g" % v, b"%.17g" % v, b"%g" % v]
+    for e in rng.integers(-40, 40, 4000):
+        cases.append(b"%.12ge%d" % (rng.random(), e))
+    bad = []
+    for t in cases:
+        a, b = ours(t), ref(t)
+        same = (struct.pack("d", a[0]) == struct.pack("d", b[0]) or (a[0] != a[0] and b[0] != b[0])) and a[1] == b[1]
+        if not same:
+            bad.append((t, a, b))
+    assert not bad, bad[:5]
