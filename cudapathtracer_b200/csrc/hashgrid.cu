@@ -59,21 +59,46 @@ __global__ void hashKernel(const float* __restrict__ px, const float* __restrict
     index[i] = (uint32_t)i;
 }
 
+// four consecutive keys per thread (one 16 B load) + the key before them
 __global__ void clearCellsKernel(const uint32_t* __restrict__ prevKeys, int n, uint32_t* __restrict__ cellStart) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t k = prevKeys[i];
-    if (i == 0 || prevKeys[i - 1] != k) cellStart[k] = 0xFFFFFFFFu;
+    const int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= n) return;
+    uint32_t k[4];
+    if (i0 + 4 <= n) { const uint4 v = __ldg(reinterpret_cast<const uint4*>(prevKeys + i0)); k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w; }
+    else for (int j = 0; j < 4; ++j) k[j] = i0 + j < n ? __ldg(prevKeys + i0 + j) : 0u;
+    uint32_t before = i0 > 0 ? __ldg(prevKeys + i0 - 1) : ~k[0];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (i0 + j < n && k[j] != before) cellStart[k[j]] = 0xFFFFFFFFu;
+        before = k[j];
+    }
 }
 
 __global__ void tableKernel(const uint32_t* __restrict__ keys, int n, uint32_t* __restrict__ cellStart, uint32_t* __restrict__ cellEnd,
                             uint32_t* __restrict__ prevKeys) {     // deviceCode.cu:3113-3138
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t k = keys[i];
-    prevKeys[i] = k;
-    if (i == 0 || keys[i - 1] != k) cellStart[k] = (uint32_t)i;
-    if (i == n - 1 || keys[i + 1] != k) cellEnd[k] = (uint32_t)(i + 1);
+    const int i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= n) return;
+    uint32_t k[4];
+    const bool full = i0 + 4 <= n;
+    if (full) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(keys + i0));
+        k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
+        *reinterpret_cast<uint4*>(prevKeys + i0) = v;
+    } else {
+        for (int j = 0; j < 4; ++j) { k[j] = i0 + j < n ? __ldg(keys + i0 + j) : 0u; if (i0 + j < n) prevKeys[i0 + j] = k[j]; }
+    }
+    const int last = min(i0 + 4, n) - 1;                      // last valid index of this thread
+    const bool haveBefore = i0 > 0, haveAfter = last + 1 < n;
+    const uint32_t before = haveBefore ? __ldg(keys + i0 - 1) : 0u, after = haveAfter ? __ldg(keys + last + 1) : 0u;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int i = i0 + j;
+        if (i > last) break;
+        const bool first = j == 0 ? (!haveBefore || before != k[0]) : k[j - 1] != k[j];
+        const bool lastOfRun = (i == last || j == 3) ? (!haveAfter || after != k[j]) : k[j + 1] != k[j];
+        if (first) cellStart[k[j]] = (uint32_t)i;
+        if (lastOfRun) cellEnd[k[j]] = (uint32_t)(i + 1);
+    }
 }
 
 // 27-cell radius count exactly as doEyePass walks the grid (deviceCode.cu:2968-2995)
@@ -139,7 +164,7 @@ static int hashGridBuildStrided(HashGridDevice& g, const float* px, const float*
     if (g.prevN < 0) {
         cudaMemsetAsync(g.cellStart, 0xFF, sizeof(uint32_t) * (size_t)g.tableSize, stream);
     } else if (g.prevN > 0) {
-        clearCellsKernel<<<(g.prevN + T - 1) / T, T, 0, stream>>>(g.prevKeys, g.prevN, g.cellStart);
+        clearCellsKernel<<<(g.prevN + 4 * T - 1) / (4 * T), T, 0, stream>>>(g.prevKeys, g.prevN, g.cellStart);
         ++g.launches;
     }
     g.n = n; g.prevN = n;
@@ -151,7 +176,7 @@ static int hashGridBuildStrided(HashGridDevice& g, const float* px, const float*
     while (bits < 32 && (1ull << bits) < (unsigned long long)g.tableSize) ++bits;
     cudaError_t e = radixSortPairs(g.plan, g.keys, g.index, n, bits, stream, &g.launches);
     if (e != cudaSuccess) return (int)e;
-    tableKernel<<<(n + T - 1) / T, T, 0, stream>>>(g.keys, n, g.cellStart, g.cellEnd, g.prevKeys);
+    tableKernel<<<(n + 4 * T - 1) / (4 * T), T, 0, stream>>>(g.keys, n, g.cellStart, g.cellEnd, g.prevKeys);
     ++g.launches;
     return (int)cudaGetLastError();
 }

@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_hashgrid.py tests/test_gpu_bench_workloads.py tests/test_gpu_bidir.py -m gpu -q -x > gpurun_out/pytest_72.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_72.log
+timeout 900 python bench.py --workload hashgrid --steps 5 --warmup 2 > gpurun_out/bench_grid_72.log 2>&1; echo "rc=$?" >> gpurun_out/bench_grid_72.log
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_grid_72.csv python bench.py --workload hashgrid --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_l_grid_72.log 2>&1
