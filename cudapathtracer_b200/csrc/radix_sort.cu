@@ -1,6 +1,6 @@
 // radix_sort.cu — LSD radix sort, 8-bit digits, three kernels per pass:
 //   digitHistogram  : per-tile digit counts            (reads 4 B/key, 16 loads per thread in flight)
-//   exclusiveScan   : digit-major scan of the counts   (tiny)
+//   digitRowScan    : per-digit scan over the tiles    (tiny; the scan across digits happens inside every scatter CTA)
 //   scatterPass     : stable warp-ranked scatter       (reads 8 B/key, writes 8 B/key)
 // Algorithmic traffic: 20 B per key per pass. Ranking inside a tile is done per warp with __match_any_sync on the digit (no
 // shared-memory atomics), warps are chained by a 256-thread column scan, so the sort is stable — required for LSD correctness.
@@ -37,6 +37,34 @@ __global__ void __launch_bounds__(kHistThreads) digitHistogram(const uint32_t* _
     hist[(size_t)threadIdx.x * numTiles + blockIdx.x] = cnt[threadIdx.x];
 }
 
+// One CTA per digit: exclusive scan of that digit's per-tile counts in place + the digit's total. Together with a 256-wide scan of
+// the totals inside every scatter CTA this replaces the three-kernel scan of the whole [256][numTiles] array.
+__global__ void __launch_bounds__(256) digitRowScan(uint32_t* __restrict__ hist, int numTiles, uint32_t* __restrict__ rowTotal) {
+    __shared__ uint32_t warpSum[8];
+    __shared__ uint32_t carry;
+    uint32_t* row = hist + (size_t)blockIdx.x * numTiles;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < numTiles; base += 256) {
+        const int i = base + threadIdx.x;
+        const uint32_t v = i < numTiles ? row[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warpSum[warp] = x;
+        __syncthreads();
+        uint32_t before = carry;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) before += w < warp ? warpSum[w] : 0u;
+        if (i < numTiles) row[i] = before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 255) carry = before + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) rowTotal[blockIdx.x] = carry;
+}
+
 // Shared memory of one scatter CTA: per-warp digit counters, the tile's pairs in digit order (staged so that the global writes
 // of a digit's run come from consecutive threads: written key by key from the ranking threads, every 4-byte store was its own
 // L2 transaction — 21 M per pass at 10.5 M pairs, the first two passes took 170 / 136 us against 51 us for already-clustered
@@ -47,12 +75,13 @@ struct ScatterSmem {
     uint32_t vals[kSortTile];
     uint32_t digitStart[256];
     uint32_t toGlobal[256];
-    uint32_t scanWarp[8];
+    uint32_t scanWarp[16];
 };
 
 __global__ void __launch_bounds__(kThreads, 2) scatterPass(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
                                                            uint32_t* __restrict__ keysOut, uint32_t* __restrict__ valsOut, int n,
-                                                           int shift, const uint32_t* __restrict__ histScanned, int numTiles) {
+                                                           int shift, const uint32_t* __restrict__ histScanned, const uint32_t* __restrict__ rowTotal,
+                                                           int numTiles) {
     extern __shared__ __align__(16) unsigned char scatterSmemRaw[];
     ScatterSmem& S = *reinterpret_cast<ScatterSmem*>(scatterSmemRaw);
     for (int i = threadIdx.x; i < kWarps * 256; i += kThreads) (&S.warpCnt[0][0])[i] = 0;
@@ -88,6 +117,10 @@ __global__ void __launch_bounds__(kThreads, 2) scatterPass(const uint32_t* __res
     __syncthreads();
     if (threadIdx.x < 256) {   // thread d: chain the warps for digit d, then an exclusive scan over the digits of the tile
         const unsigned d = threadIdx.x;
+        // global position of the tile's first key with digit d = all keys with smaller digits (scan of the digit totals, done here)
+        //                                                       + this digit's keys in earlier tiles (digitRowScan)
+        const uint32_t tot = __ldg(rowTotal + d);
+        const uint32_t inRow = __ldg(histScanned + (size_t)d * numTiles + tile);
         uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) {
@@ -95,20 +128,24 @@ __global__ void __launch_bounds__(kThreads, 2) scatterPass(const uint32_t* __res
             S.warpCnt[w][d] = run;
             run += c;
         }
-        uint32_t x = run;
+        uint32_t x = run, y = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-            if (lane >= o) x += y;
+            const uint32_t a = __shfl_up_sync(0xffffffffu, x, o);
+            const uint32_t b = __shfl_up_sync(0xffffffffu, y, o);
+            if (lane >= o) { x += a; y += b; }
         }
-        if (lane == 31) S.scanWarp[warp] = x;
+        if (lane == 31) { S.scanWarp[warp] = x; S.scanWarp[8 + warp] = y; }
         asm volatile("bar.sync 1, 256;");               // the 8 warps that hold digits
-        uint32_t before = 0;
+        uint32_t before = 0, smaller = 0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) before += w < warp ? S.scanWarp[w] : 0u;
+        for (int w = 0; w < 8; ++w) {
+            before += w < warp ? S.scanWarp[w] : 0u;
+            smaller += w < warp ? S.scanWarp[8 + w] : 0u;
+        }
         const uint32_t start = before + x - run;
         S.digitStart[d] = start;
-        S.toGlobal[d] = __ldg(histScanned + (size_t)d * numTiles + tile) - start;
+        S.toGlobal[d] = smaller + (y - tot) + inRow - start;
     }
     __syncthreads();
 #pragma unroll
@@ -232,6 +269,7 @@ cudaError_t radixSortPlanCreate(RadixSortPlan& plan, int maxN) {
     if (plan.numTilesMax < 1) plan.numTilesMax = 1;
     size_t histEntries = (size_t)256 * plan.numTilesMax;
     size_t scanBlocks = (histEntries + kScanTile - 1) / kScanTile + 1;
+    if (scanBlocks < 256) scanBlocks = 256;              // digitRowScan keeps the 256 digit totals here
     cudaError_t e;
     size_t nb = (size_t)(maxN > 0 ? maxN : 1) * sizeof(uint32_t);
     if ((e = cudaMalloc(&plan.keysAlt, nb)) != cudaSuccess) return e;
@@ -260,10 +298,9 @@ cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, 
         int shift = p * 8;
         digitHistogram<<<numTiles, kHistThreads, 0, stream>>>(kin, n, shift, plan.hist, numTiles);
         if (launches) *launches += 1;
-        cudaError_t e = exclusiveScanU32(plan.hist, 256 * numTiles, plan.blockSums, stream, launches);
-        if (e != cudaSuccess) return e;
-        scatterPass<<<numTiles, kThreads, sizeof(ScatterSmem), stream>>>(kin, vin, kout, vout, n, shift, plan.hist, numTiles);
-        if (launches) *launches += 1;
+        digitRowScan<<<256, 256, 0, stream>>>(plan.hist, numTiles, plan.blockSums);
+        scatterPass<<<numTiles, kThreads, sizeof(ScatterSmem), stream>>>(kin, vin, kout, vout, n, shift, plan.hist, plan.blockSums, numTiles);
+        if (launches) *launches += 2;
         uint32_t* t;
         t = kin; kin = kout; kout = t;
         t = vin; vin = vout; vout = t;
