@@ -35,14 +35,42 @@ __device__ __forceinline__ int classOfMaterial(const DMat* __restrict__ mats, in
     }
 }
 
-// ---- advance: rotate queues, clear per-iteration counters (1 thread) --------------------------------------
-__global__ void wfAdvance(int* counters) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
+// ---- advance: rotate queues, clear per-iteration counters; with ray bins also scan the bin counts of the queue about to be traced
+constexpr int kAdvanceThreads = 512;
+__global__ void __launch_bounds__(kAdvanceThreads) wfAdvance(WfState st) {
+    int* counters = st.counters;
+    if (threadIdx.x == 0) {
         counters[C_EXTEND_COUNT] = counters[C_NEXT_COUNT];
         counters[C_NEXT_COUNT] = 0;
         counters[C_SHADOW_COUNT] = 0;
         for (int c = 0; c < NUM_CLS; ++c) counters[C_CLASS_COUNT + c] = 0;
         counters[C_FETCH_EXTEND] = 0; counters[C_FETCH_SHADE] = 0; counters[C_FETCH_SHADOW] = 0;
+    }
+    if (kRayBins) {
+        constexpr int kPer = kNumRayBins / kAdvanceThreads;
+        __shared__ int warpSum[kAdvanceThreads / 32];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        int c[kPer], mine = 0;
+#pragma unroll
+        for (int k = 0; k < kPer; ++k) { c[k] = st.binCount[threadIdx.x * kPer + k]; mine += c[k]; }
+        int x = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warpSum[warp] = x;
+        __syncthreads();
+        int before = x - mine;
+        for (int w = 0; w < warp; ++w) before += warpSum[w];
+#pragma unroll
+        for (int k = 0; k < kPer; ++k) { st.binStart[threadIdx.x * kPer + k] = before; before += c[k]; st.binCount[threadIdx.x * kPer + k] = 0; }
+    }
+}
+
+// the continuing paths of the last shade pass, written bin by bin into the extend queue
+__global__ void __launch_bounds__(256) wfBinScatter(WfState st, int* __restrict__ queue) {
+    const int n = st.counters[C_EXTEND_COUNT];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int2 e = st.binTmp[i];
+        queue[__ldg(st.binStart + e.y) + st.binPos[i]] = e.x;
     }
 }
 

@@ -26,6 +26,18 @@ enum : int {
     C_TOTAL = 96
 };
 
+// Ray binning of the extend queue (NOVUM_RAY_BINS): paths that continue are counted into bins keyed by
+// (origin cell of a 2^b x 2^b x 2^b grid over the scene bounds, direction octant) while the shade kernel appends them; after
+// the advance kernel's scan of the bin counts a scatter writes the slots bin by bin, so the 32 rays a warp of the extend
+// kernel pulls together start in the same part of the scene and point into the same octant. Measured: no gain — a
+// ray of these scenes visits ~4.6 BVH8 nodes and 3.8 triangles, there is little divergence to remove. Compiled out.
+#ifndef NOVUM_RAY_BINS
+#define NOVUM_RAY_BINS 0
+#endif
+constexpr bool kRayBins = NOVUM_RAY_BINS != 0;
+constexpr int kRayCellBits = 3;
+constexpr int kNumRayBins = 8 << (3 * kRayCellBits);      // 4096
+
 struct ShadowRec { float4 o_maxT; float4 d_pix; float4 contrib; };   // 48 B
 
 // One 128 B line per path slot (queues hand out slots in material-class order, i.e. at random: with one array per field a
@@ -41,6 +53,10 @@ struct WfState {
     float4* slots;       // capacity x kSlotWords
     // queues
     int* extendQ[2];
+    int2* binTmp;        // capacity x {slot, bin}: continuing paths in append order (kRayBins)
+    int* binPos;         // capacity: rank of the entry inside its bin
+    int* binCount;       // kNumRayBins counters of the queue being appended
+    int* binStart;       // kNumRayBins: exclusive scan of the counts of the queue being traced
     int* classQ;         // NUM_CLS x capacity
     ShadowRec* shadowQ;
     int* counters;       // C_TOTAL ints

@@ -19,6 +19,11 @@ static int wfAlloc(WfEngine& e, int capacity) {
     A((void**)&s.slots, n * kSlotWords * sizeof(float4));
     A((void**)&s.extendQ[0], n * sizeof(int)); A((void**)&s.extendQ[1], n * sizeof(int));
     A((void**)&s.classQ, n * NUM_CLS * sizeof(int)); A((void**)&s.shadowQ, n * sizeof(ShadowRec));
+    if (kRayBins) {
+        A((void**)&s.binTmp, n * sizeof(int2)); A((void**)&s.binPos, n * sizeof(int));
+        A((void**)&s.binCount, kNumRayBins * sizeof(int)); A((void**)&s.binStart, kNumRayBins * sizeof(int));
+        if (err == cudaSuccess) err = cudaMemset(s.binCount, 0, kNumRayBins * sizeof(int));
+    }
     A((void**)&s.counters, C_TOTAL * sizeof(int)); A((void**)&s.rayCounters, 4 * sizeof(unsigned long long));
     if (err != cudaSuccess) return (int)err;
     if ((err = cudaHostAlloc((void**)&e.pinnedCounters, 2 * C_TOTAL * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
@@ -31,6 +36,7 @@ static void wfFree(WfEngine& e) {
     WfState& s = e.st;
     cudaFree(s.slots); cudaFree(s.extendQ[0]); cudaFree(s.extendQ[1]); cudaFree(s.classQ); cudaFree(s.shadowQ);
     cudaFree(s.counters); cudaFree(s.rayCounters);
+    cudaFree(s.binTmp); cudaFree(s.binPos); cudaFree(s.binCount); cudaFree(s.binStart);
     if (e.pinnedCounters) cudaFreeHost(e.pinnedCounters);
     for (int i = 0; i < 2; ++i) if (e.evRead[i]) cudaEventDestroy(e.evRead[i]);
     for (cudaEvent_t ev : e.evPool) cudaEventDestroy(ev);
@@ -68,6 +74,7 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
     cudaEventRecord(scene->ev0, stream);
     if (pool > 0) {
         cudaMemsetAsync(st.rayCounters, 0, 4 * sizeof(unsigned long long), stream);
+        if (kRayBins) cudaMemsetAsync(st.binCount, 0, kNumRayBins * sizeof(int), stream);
         wfInit<<<(pool + 255) / 256, 256, 0, stream>>>(st, pool);
         ++launches;
         const int grid = smCount() * 8;
@@ -80,7 +87,8 @@ static int wfRender(NovumScene* scene, WfEngine& eng, const NovumCamera& cam, in
         for (long iter = 0;; ++iter) {
             mark();
             if (iter > 0) {
-                wfAdvance<<<1, 32, 0, stream>>>(st.counters);
+                wfAdvance<<<1, kAdvanceThreads, 0, stream>>>(st);
+                if (kRayBins) { wfBinScatter<<<grid, 256, 0, stream>>>(st, st.extendQ[cur]); ++launches; }
                 if (profCount) wfExtend<true><<<tgrid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
                 else wfExtend<false><<<tgrid, kWfThreads, 0, stream>>>(sc, st, st.extendQ[cur], cnt);
                 launches += 2; stageLaunches[0] += 1; stageLaunches[3] += 1;

@@ -214,6 +214,19 @@ NV_D bool shadeNaive(const SceneView& sc, const WfParams& P, PathRegs& p, const 
     return p.depth < P.maxDepth;
 }
 
+// bin of a continuing ray: origin cell of the 2^b-per-axis grid over the scene bounds (clamped: the camera may stand outside), direction octant
+NV_D int rayBin(const SceneView& sc, V3 o, V3 d) {
+    constexpr int kCells = 1 << kRayCellBits;
+    const float sx = (float)kCells * 0.5f / fmaxf(sc.sceneCenter[0] - sc.sceneMin[0], 1e-20f);
+    const float sy = (float)kCells * 0.5f / fmaxf(sc.sceneCenter[1] - sc.sceneMin[1], 1e-20f);
+    const float sz = (float)kCells * 0.5f / fmaxf(sc.sceneCenter[2] - sc.sceneMin[2], 1e-20f);
+    const int cx = min(max((int)((o.x - sc.sceneMin[0]) * sx), 0), kCells - 1);
+    const int cy = min(max((int)((o.y - sc.sceneMin[1]) * sy), 0), kCells - 1);
+    const int cz = min(max((int)((o.z - sc.sceneMin[2]) * sz), 0), kCells - 1);
+    const int oct = (d.x < 0.0f ? 1 : 0) | (d.y < 0.0f ? 2 : 0) | (d.z < 0.0f ? 4 : 0);
+    return ((((cz << kRayCellBits) | cy) << kRayCellBits | cx) << 3) | oct;
+}
+
 #ifndef NOVUM_SHADE_MINB
 #define NOVUM_SHADE_MINB 5
 #endif
@@ -280,7 +293,22 @@ __global__ void __launch_bounds__(kWfThreads, NOVUM_SHADE_MINB) wfShade(SceneVie
             }
         }
         int pos = warpAppend(&st.counters[C_NEXT_COUNT], alive);
-        if (alive) { storePath(st, slot, p); nextQueue[pos] = slot; }
+        if (!kRayBins) {
+            if (alive) { storePath(st, slot, p); nextQueue[pos] = slot; }
+        } else {
+            const unsigned am = __ballot_sync(0xffffffffu, alive);
+            if (alive) {
+                storePath(st, slot, p);
+                const int bin = rayBin(sc, p.o, p.d);
+                const unsigned peers = __match_any_sync(am, bin);
+                const int leader = __ffs(peers) - 1;
+                int first = 0;
+                if (lane == leader) first = atomicAdd(&st.binCount[bin], __popc(peers));
+                first = __shfl_sync(peers, first, leader);
+                st.binTmp[pos] = make_int2(slot, bin);
+                st.binPos[pos] = first + __popc(peers & ((1u << lane) - 1u));
+            }
+        }
     }
     for (int o = 16; o > 0; o >>= 1) {
         finished += __shfl_xor_sync(0xffffffffu, finished, o);
