@@ -462,6 +462,28 @@ def run_frame(args):
     for i in range(args.steps):
         nb.frame_save_bmp(out, d_acc.data_ptr(), d_ov.data_ptr(), w, h, n, nb.FRAME_FINAL, True)
     e2e_ms = (time.time() - t0) * 1e3 / args.steps
+    # the asynchronous variant: how long the render stream is held per save (events around the call on that stream), and the
+    # time per save when they are queued back to back (read-back and file write of save k overlap the kernel of save k+1)
+    n_async = min(args.steps, 8)
+    outs = [os.path.join(tempfile.gettempdir(), f"novum_bench_frame_async_{i & 1}.bmp") for i in range(n_async)]
+    nb.frame_save_bmp_async(outs[0], d_acc.data_ptr(), d_ov.data_ptr(), w, h, n, nb.FRAME_FINAL, True, stream.cuda_stream)
+    nb.frame_save_wait(); stream.synchronize()
+    a0 = [torch.cuda.Event(enable_timing=True) for _ in range(n_async)]; a1 = [torch.cuda.Event(enable_timing=True) for _ in range(n_async)]
+    t_queue = 0.0
+    for i in range(n_async):                                   # saves spaced apart, as a progressive render issues them (one every few seconds)
+        a0[i].record(stream)
+        t0 = time.time()
+        nb.frame_save_bmp_async(outs[i], d_acc.data_ptr(), d_ov.data_ptr(), w, h, n, nb.FRAME_FINAL, True, stream.cuda_stream)
+        t_queue += (time.time() - t0) * 1e3 / n_async
+        a1[i].record(stream)
+        nb.frame_save_wait(); stream.synchronize()
+    stall_ms = float(np.median([a0[i].elapsed_time(a1[i]) for i in range(n_async)]))
+    t0 = time.time()
+    for i in range(n_async):                                   # back to back: bounded by the file writes of the two slots
+        nb.frame_save_bmp_async(outs[i], d_acc.data_ptr(), d_ov.data_ptr(), w, h, n, nb.FRAME_FINAL, True, stream.cuda_stream)
+    nb.frame_save_wait(); stream.synchronize()
+    async_ms = (time.time() - t0) * 1e3 / n_async
+    async_same = bool(np.array_equal(np.fromfile(outs[-1], np.uint8), np.fromfile(out, np.uint8)))
     clk = clocks.stop()
     px = w * h
     algo = px * (16 + 16 + 3)
@@ -473,6 +495,10 @@ def run_frame(args):
             "e2e": {"value": px / (e2e_ms * 1e-3) / 1e6, "unit": "Mpixels/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": rowb * h,
                     "note": "novum_frame_save_bmp: device accumulators -> kernel -> 3 B/pixel read-back into page-locked memory -> .bmp on disk; the "
                             "accumulators are produced on the device by the render, so there is no H2D"},
+            "save_async": {"render_stream_stall_ms": stall_ms, "host_call_ms": t_queue, "ms_per_save_back_to_back": async_ms, "saves": n_async,
+                           "file_equals_blocking_variant": async_same,
+                           "note": "novum_frame_save_bmp_async: the render stream waits for the finish kernel only; read-back + file write run "
+                                   "behind it on the save stream / a worker thread (the blocking variant holds the caller for e2e.ms_per_step)"},
             "gpu_launches": args.steps, "clocks": clk, "parity_rows_checked": 64, "parity_ok": parity,
             "roofline": {"bound": "hbm", "kernel": "frameFinishKernel", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": algo / (ms * 1e-3) / 1e9 / peak, "traffic": 285.0e6, "peak_source": peak_src,

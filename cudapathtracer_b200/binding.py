@@ -128,6 +128,7 @@ def _declare(L):
     L.novum_frame_finish_device.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp, vp]
     L.novum_frame_finish.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp]
     L.novum_frame_save_bmp.argtypes = [C.c_char_p, vp, vp, ci, ci, ci, ci, ci]
+    L.novum_frame_save_bmp_async.argtypes = [C.c_char_p, vp, vp, ci, ci, ci, ci, ci, vp]
     L.novum_write_bmp.argtypes = [C.c_char_p, vp, ci, ci]
     L.novum_frame_last_ms.argtypes = [C.POINTER(cf)]
     L.novum_frame_gamma_steps.argtypes = [vp]
@@ -332,6 +333,16 @@ def frame_save_bmp(path, d_colors, d_overlay, w, h, sample_count, mode=FRAME_FIN
     ms = C.c_float()
     lib().novum_frame_last_ms(C.byref(ms))
     return ms.value
+
+
+def frame_save_bmp_async(path, d_colors, d_overlay, w, h, sample_count, mode=FRAME_PROGRESSIVE, post_process=True, stream=None):
+    """Queues kernel + read-back + file write behind `stream` (a cudaStream_t value); `stream` waits for the kernel only."""
+    _check(lib().novum_frame_save_bmp_async(os.fsencode(path), d_colors, d_overlay, int(w), int(h), int(sample_count), int(mode),
+                                            int(bool(post_process)), stream), "novum_frame_save_bmp_async")
+
+
+def frame_save_wait():
+    _check(lib().novum_frame_save_wait(), "novum_frame_save_wait")
 
 
 def save_bmp(path, colors, overlay, sample_count, mode=FRAME_FINAL, post_process=True):

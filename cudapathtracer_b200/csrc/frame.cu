@@ -22,7 +22,11 @@
 #include <string.h>
 #include <algorithm>
 #include <utility>
+#include <condition_variable>
+#include <deque>
 #include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 #include "../../include/novum_b200.h"
 
@@ -362,6 +366,101 @@ static int finishToHost(const NovumFloat4* d_colors, const NovumFloat4* d_overla
     return 0;
 }
 
+// ---- asynchronous save: the read-back and the file write overlap the next sample pass ------------------------------------------
+// The reference stops its sample loop every 5 s for cleanAndFormatImage + two float4 frame copies + the host post-process + the file
+// write (deviceCode.cu:1905-1927; 0.37 s of host work for a 4K frame). Here the finish kernel runs on a stream of its own once the
+// render stream has reached the call; the render stream then waits for that kernel only (it has read the accumulators - ~55 us at 4K),
+// while the 3 B/pixel copy and the write happen behind it: copy on a second stream, write on a worker thread. Two slots, so a save
+// may still be on its way to disk while the next one is being produced; a third call waits for the oldest.
+struct SaveSlot {
+    uint8_t* dBgr = nullptr; uint8_t* hBgr = nullptr; size_t cap = 0;
+    cudaEvent_t copied = nullptr;
+    bool busy = false;
+    std::string path; int w = 0, h = 0;
+};
+struct FrameSaver {
+    std::mutex mu;
+    std::condition_variable cv;
+    cudaStream_t stream = nullptr, copyStream = nullptr;      // kernels / read-backs: save k+1's kernel need not queue behind save k's copy
+    cudaEvent_t reached = nullptr, kernelDone = nullptr;
+    SaveSlot slot[2];
+    int next = 0, pending = 0, firstError = 0, dev = -1;
+    std::deque<int> jobs;
+    bool started = false;
+};
+static FrameSaver* g_saver = nullptr;       // created on first use, never destroyed (its thread is detached)
+
+static void saverLoop(FrameSaver* S) {
+    cudaSetDevice(S->dev);
+    while (true) {
+        int k;
+        {
+            std::unique_lock<std::mutex> lk(S->mu);
+            S->cv.wait(lk, [&] { return !S->jobs.empty(); });
+            k = S->jobs.front(); S->jobs.pop_front();
+        }
+        SaveSlot& sl = S->slot[k];
+        int rc = (int)cudaEventSynchronize(sl.copied);
+        if (rc == 0) rc = writeBmpFile(sl.path.c_str(), sl.hBgr, sl.w, sl.h);
+        {
+            std::lock_guard<std::mutex> lk(S->mu);
+            if (rc && !S->firstError) S->firstError = rc;
+            sl.busy = false; --S->pending;
+        }
+        S->cv.notify_all();
+    }
+}
+
+static int saveAsync(const char* path, const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h, int sampleCount, int mode,
+                     int postProcess, cudaStream_t renderStream) {
+    int dev = 0; cudaGetDevice(&dev);
+    if (!g_saver) g_saver = new FrameSaver();
+    FrameSaver* S = g_saver;
+    cudaError_t e;
+    std::unique_lock<std::mutex> lk(S->mu);
+    if (S->dev >= 0 && S->dev != dev) return NOVUM_E_ARG;           // one saver per process, bound to the device of its first call
+    if (!S->stream) {
+        if ((e = cudaStreamCreateWithFlags(&S->stream, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+        if ((e = cudaStreamCreateWithFlags(&S->copyStream, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+        cudaEventCreateWithFlags(&S->reached, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&S->kernelDone, cudaEventDisableTiming);
+        for (SaveSlot& sl : S->slot) cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming);
+        S->dev = dev;
+    }
+    const int k = S->next;
+    SaveSlot& sl = S->slot[k];
+    S->cv.wait(lk, [&] { return !sl.busy; });                        // its previous file is on disk
+    const size_t bytes = (size_t)novum_bmp_row_bytes(w) * h;
+    if (sl.cap < bytes) {
+        if (sl.dBgr) cudaFree(sl.dBgr);
+        if (sl.hBgr) cudaFreeHost(sl.hBgr);
+        sl.dBgr = sl.hBgr = nullptr; sl.cap = 0;
+        if ((e = cudaMalloc(&sl.dBgr, bytes)) != cudaSuccess) return (int)e;
+        if ((e = cudaMallocHost(&sl.hBgr, bytes)) != cudaSuccess) return (int)e;
+        sl.cap = bytes;
+    }
+    if ((e = cudaEventRecord(S->reached, renderStream)) != cudaSuccess) return (int)e;
+    cudaStreamWaitEvent(S->stream, S->reached, 0);
+    int rc;
+    {
+        std::lock_guard<std::mutex> fl(g_frame.mu);
+        rc = launchFinish(d_colors, d_overlay, w, h, sampleCount, mode, postProcess, sl.dBgr, nullptr, S->stream);
+    }
+    if (rc) return rc;
+    cudaEventRecord(S->kernelDone, S->stream);
+    cudaStreamWaitEvent(renderStream, S->kernelDone, 0);             // the next pass may touch the accumulators from here on
+    cudaStreamWaitEvent(S->copyStream, S->kernelDone, 0);
+    if ((e = cudaMemcpyAsync(sl.hBgr, sl.dBgr, bytes, cudaMemcpyDeviceToHost, S->copyStream)) != cudaSuccess) return (int)e;
+    cudaEventRecord(sl.copied, S->copyStream);
+    sl.path = path; sl.w = w; sl.h = h; sl.busy = true;
+    ++S->pending; S->next = k ^ 1;
+    S->jobs.push_back(k);
+    if (!S->started) { S->started = true; std::thread(saverLoop, S).detach(); }
+    lk.unlock();
+    S->cv.notify_all();
+    return 0;
+}
+
 }  // namespace nv
 
 using namespace nv;
@@ -427,6 +526,22 @@ int novum_frame_save_bmp(const char* path, const NovumFloat4* d_colors, const No
     int rc = finishToHost(d_colors, d_overlay, w, h, sampleCount, mode, postProcess, &rows);
     if (rc) return rc;
     return writeBmpFile(path, rows, w, h);
+}
+
+int novum_frame_save_bmp_async(const char* path, const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h, int sampleCount,
+                               int mode, int postProcess, void* renderStream) {
+    if (!path) return NOVUM_E_ARG;
+    if (!haveGpu()) return NOVUM_E_NOGPU;
+    return saveAsync(path, d_colors, d_overlay, w, h, sampleCount, mode, postProcess, (cudaStream_t)renderStream);
+}
+
+int novum_frame_save_wait(void) {
+    FrameSaver* S = g_saver;
+    if (!S) return 0;
+    std::unique_lock<std::mutex> lk(S->mu);
+    S->cv.wait(lk, [&] { return S->pending == 0; });
+    int rc = S->firstError; S->firstError = 0;
+    return rc;
 }
 
 int novum_save_bmp(const char* path, const NovumFloat4* colors, const NovumFloat4* overlay, int w, int h, int sampleCount, int mode,

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define NOVUM_ABI_VERSION 3
+#define NOVUM_ABI_VERSION 4
 
 /* error codes (negative; positive return values are cudaError_t) */
 #define NOVUM_OK             0
@@ -336,6 +336,14 @@ int  novum_frame_finish(const NovumFloat4* colors, const NovumFloat4* overlay, i
 /* device accumulators -> .bmp file: kernel, 3 B/pixel read-back into page-locked memory, headers + rows (imageUtil.cu:69-100) */
 int  novum_frame_save_bmp(const char* path, const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h, int sampleCount,
                           int mode, int postProcess);
+/* The same, off the critical path (the reference stalls its sample loop for this every 5 s, deviceCode.cu:1905-1927):
+ * the kernel runs on the library's save stream once `renderStream` (a cudaStream_t, NULL = default stream) has reached this call,
+ * `renderStream` then waits for the kernel only - it has read the accumulators - and the read-back and the file write overlap whatever
+ * is queued next. Returns once the work is queued; at most two saves in flight (a third call waits for the oldest).
+ * novum_frame_save_wait blocks until every queued file is on disk and returns the first error since the last wait. */
+int  novum_frame_save_bmp_async(const char* path, const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h,
+                                int sampleCount, int mode, int postProcess, void* renderStream);
+int  novum_frame_save_wait(void);
 /* host accumulators -> .bmp file (same kernel; no CPU tonemap exists in the product) */
 int  novum_save_bmp(const char* path, const NovumFloat4* colors, const NovumFloat4* overlay, int w, int h, int sampleCount, int mode,
                     int postProcess);

@@ -76,4 +76,7 @@ def test_frame_abi_without_gpu_is_an_error(built):
         pytest.skip("a GPU is present")
     with pytest.raises(nb.NovumError):
         nb.frame_finish(np.zeros((4, 4, 4), np.float32), None, 1)
+    with pytest.raises(nb.NovumError):                          # the asynchronous save has no host path either
+        nb.frame_save_bmp_async("unused.bmp", None, None, 4, 4, 1)
+    nb.frame_save_wait()                                        # nothing was ever queued: returns at once
     assert nb.bmp_row_bytes(61) == 184 and nb.bmp_row_bytes(64) == 192 and nb.bmp_row_bytes(1) == 4

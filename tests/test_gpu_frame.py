@@ -128,6 +128,39 @@ def test_full_size_4k_device_entry_point(built, tmp_path):
     assert np.array_equal(body, ob.bmp_rows(ob.frame_clean(q, None, n, final_mode=True), False)[:, : 3 * w].reshape(h, w, 3))
 
 
+def test_async_save_snapshots_the_accumulator(built, tmp_path):
+    """Progressive saves queued behind a stream that keeps adding samples (deviceCode.cu:1905-1927 stalls the loop here): every file
+    holds exactly the state the accumulator had when its save was queued, and equals the blocking variant byte for byte."""
+    torch = pytest.importorskip("torch")
+    w, h = 1001, 333                      # ragged: rows padded, last 512-pixel segment short
+    rng = np.random.default_rng(5)
+    sample = np.zeros((h, w, 4), np.float32); sample[..., :3] = rng.random((h, w, 3), dtype=np.float32) * 2.0
+    sample[7, 11, 0] = np.nan; sample[8, 12, 1] = np.inf
+    d_sample = torch.from_numpy(sample).cuda()
+    d_acc = torch.zeros_like(d_sample)
+    s = torch.cuda.Stream()
+    paths, states = [], []
+    with torch.cuda.stream(s):
+        for k in range(5):
+            d_acc += d_sample * float(k + 1)                    # the "next sample pass", queued right behind the previous save
+            states.append(d_acc.clone())
+            p = str(tmp_path / f"async_{k}.bmp"); paths.append(p)
+            nb.frame_save_bmp_async(p, d_acc.data_ptr(), None, w, h, k, nb.FRAME_PROGRESSIVE, True, s.cuda_stream)
+    nb.frame_save_wait()
+    s.synchronize()
+    for k, p in enumerate(paths):
+        q = str(tmp_path / f"sync_{k}.bmp")
+        nb.frame_save_bmp(q, states[k].data_ptr(), None, w, h, k, nb.FRAME_PROGRESSIVE, True)
+        a, b = np.fromfile(p, np.uint8), np.fromfile(q, np.uint8)
+        assert a.size == 54 + nb.bmp_row_bytes(w) * h and np.array_equal(a, b), k
+        want = ob.bmp_rows(ob.frame_clean(states[k].cpu().numpy(), None, k, final_mode=False), True)
+        assert np.array_equal(a[54:].reshape(h, -1), want), k
+    nb.frame_save_wait()                                        # nothing pending: returns at once
+    with pytest.raises(nb.NovumError):
+        nb.frame_save_bmp_async(str(tmp_path / "no_such_dir" / "x.bmp"), d_acc.data_ptr(), None, w, h, 1, nb.FRAME_PROGRESSIVE, True, s.cuda_stream)
+        nb.frame_save_wait()                                    # the write error surfaces at the wait
+
+
 def test_bad_arguments(built):
     a = np.zeros((4, 4, 4), np.float32)
     with pytest.raises(nb.NovumError):
