@@ -133,6 +133,9 @@ def _declare(L):
     L.novum_frame_last_ms.argtypes = [C.POINTER(cf)]
     L.novum_frame_gamma_steps.argtypes = [vp]
     L.novum_save_pfm.argtypes = [C.c_char_p, vp, ci, ci, cf]
+    L.novum_accum_save.argtypes = [C.c_char_p, vp, ci, ci, ci, C.c_uint64, ci]
+    L.novum_accum_info.argtypes = [C.c_char_p, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(C.c_uint64), C.POINTER(ci)]
+    L.novum_accum_load.argtypes = [C.c_char_p, vp, ci, ci, C.POINTER(ci), C.POINTER(C.c_uint64)]
     L.novum_hashgrid_create.argtypes = [ci, C.POINTER(vp)]
     L.novum_hashgrid_destroy.argtypes = [vp]
     L.novum_hashgrid_table_size.argtypes = [vp]
@@ -299,6 +302,28 @@ class Scene:
         _check(lib().novum_render_device(self.h, C.byref(cfg), C.byref(cam), first_sample, num_sample, Shard(rank, world), seed,
                                          C.c_void_p(d_colors), C.byref(st)), "novum_render_device")
         return st
+
+
+def accum_save(path, colors, sample_count, seed=103033, integrator=0):
+    """Checkpoint of the running sums (h, w, 4) float32 after `sample_count` passes (novum_accum_save; host only)."""
+    colors = np.ascontiguousarray(colors, dtype=np.float32)
+    h, w = colors.shape[:2]
+    _check(lib().novum_accum_save(os.fsencode(path), _ptr(colors), w, h, int(sample_count), int(seed), int(integrator)), "novum_accum_save")
+
+
+def accum_info(path):
+    w, h, n, integ, seed = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_uint64()
+    _check(lib().novum_accum_info(os.fsencode(path), C.byref(w), C.byref(h), C.byref(n), C.byref(seed), C.byref(integ)), "novum_accum_info")
+    return {"width": w.value, "height": h.value, "sample_count": n.value, "seed": seed.value, "integrator": integ.value}
+
+
+def accum_load(path):
+    """-> (sums (h, w, 4) float32, sample_count, seed); raises on a truncated / corrupted file."""
+    info = accum_info(path)
+    img = np.empty((info["height"], info["width"], 4), np.float32)
+    n, seed = C.c_int(), C.c_uint64()
+    _check(lib().novum_accum_load(os.fsencode(path), _ptr(img), info["width"], info["height"], C.byref(n), C.byref(seed)), "novum_accum_load")
+    return img, n.value, seed.value
 
 
 FRAME_PROGRESSIVE, FRAME_FINAL = 0, 1

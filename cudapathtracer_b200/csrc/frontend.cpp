@@ -507,4 +507,84 @@ int novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, fl
     return 0;
 }
 
+// ---- resumable accumulators -------------------------------------------------------------------------------------
+// The reference keeps its running sums only in device memory: a stopped render starts again from sample 0. The sums of this library
+// are a pure function of (scene, config, seed, sample index) - counter-based RNG - so a render resumes by loading the file and calling
+// novum_render with firstSample = the stored count. Layout: 64-byte little-endian header, then w*h float4 sums, row-major.
+namespace {
+#pragma pack(push, 1)
+struct AccumHeader {
+    char magic[8];               // "NOVUMACC"
+    uint32_t version;            // 1
+    int32_t w, h, sampleCount, integrator;
+    uint32_t reserved0;
+    uint64_t seed, payloadBytes, checksum;     // FNV-1a 64 over the payload
+    uint64_t reserved1;
+};
+#pragma pack(pop)
+static_assert(sizeof(AccumHeader) == 64, "accumulator header is 64 bytes");
+uint64_t fnv1a64(const void* data, size_t n) {
+    const uint64_t* p8 = (const uint64_t*)data;                 // word-wise variant: 8 bytes per multiply (the payload is 16 B per pixel)
+    uint64_t hsh = 1469598103934665603ull;
+    for (size_t i = 0; i < n / 8; ++i) { hsh ^= p8[i]; hsh *= 1099511628211ull; }
+    return hsh;
+}
+int readAccumHeader(FILE* f, AccumHeader& hd) {
+    if (fread(&hd, sizeof(hd), 1, f) != 1) return NOVUM_E_IO;
+    if (memcmp(hd.magic, "NOVUMACC", 8) != 0 || hd.version != 1 || hd.w <= 0 || hd.h <= 0 || hd.sampleCount < 0) return NOVUM_E_IO;
+    if (hd.payloadBytes != (uint64_t)hd.w * (uint64_t)hd.h * sizeof(NovumFloat4)) return NOVUM_E_IO;
+    return 0;
+}
+}  // namespace
+
+int novum_accum_save(const char* path, const NovumFloat4* colors, int w, int h, int sampleCount, uint64_t seed, int integrator) {
+    if (!path || !colors || w <= 0 || h <= 0 || sampleCount < 0) return NOVUM_E_ARG;
+    AccumHeader hd;
+    memset(&hd, 0, sizeof(hd));
+    memcpy(hd.magic, "NOVUMACC", 8);
+    hd.version = 1; hd.w = w; hd.h = h; hd.sampleCount = sampleCount; hd.integrator = integrator; hd.seed = seed;
+    hd.payloadBytes = (uint64_t)w * (uint64_t)h * sizeof(NovumFloat4);
+    hd.checksum = fnv1a64(colors, (size_t)hd.payloadBytes);
+    // written under a temporary name and renamed: a crash during the write never leaves a truncated checkpoint under `path`
+    std::string tmp = std::string(path) + ".part";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return NOVUM_E_IO;
+    bool ok = fwrite(&hd, sizeof(hd), 1, f) == 1 && fwrite(colors, 1, (size_t)hd.payloadBytes, f) == (size_t)hd.payloadBytes;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok || rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); return NOVUM_E_IO; }
+    return 0;
+}
+
+int novum_accum_info(const char* path, int* w, int* h, int* sampleCount, uint64_t* seed, int* integrator) {
+    if (!path) return NOVUM_E_ARG;
+    FILE* f = fopen(path, "rb");
+    if (!f) return NOVUM_E_IO;
+    AccumHeader hd;
+    int rc = readAccumHeader(f, hd);
+    fclose(f);
+    if (rc) return rc;
+    if (w) *w = hd.w;
+    if (h) *h = hd.h;
+    if (sampleCount) *sampleCount = hd.sampleCount;
+    if (seed) *seed = hd.seed;
+    if (integrator) *integrator = hd.integrator;
+    return 0;
+}
+
+int novum_accum_load(const char* path, NovumFloat4* colors, int w, int h, int* sampleCount, uint64_t* seed) {
+    if (!path || !colors || w <= 0 || h <= 0) return NOVUM_E_ARG;
+    FILE* f = fopen(path, "rb");
+    if (!f) return NOVUM_E_IO;
+    AccumHeader hd;
+    int rc = readAccumHeader(f, hd);
+    if (rc == 0 && (hd.w != w || hd.h != h)) rc = NOVUM_E_ARG;              // a checkpoint of another frame size
+    if (rc == 0 && fread(colors, 1, (size_t)hd.payloadBytes, f) != (size_t)hd.payloadBytes) rc = NOVUM_E_IO;
+    fclose(f);
+    if (rc == 0 && fnv1a64(colors, (size_t)hd.payloadBytes) != hd.checksum) rc = NOVUM_E_IO;
+    if (rc) return rc;
+    if (sampleCount) *sampleCount = hd.sampleCount;
+    if (seed) *seed = hd.seed;
+    return 0;
+}
+
 }  // extern "C"

@@ -351,6 +351,13 @@ int  novum_write_bmp(const char* path, const uint8_t* bgrRows, int w, int h);   
 int  novum_frame_last_ms(float* ms);                                  /* CUDA-event time of the last kernel run by the file/host variants */
 int  novum_frame_gamma_steps(float* steps257);                        /* the 255 step positions of byte(t) (host powf), for inspection */
 int  novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, float scale);
+/* Resumable accumulators (the reference has no equivalent - its sums live in device memory only, main.cu:818-853).
+ * File = 64-byte header {"NOVUMACC", version 1, w, h, sampleCount, integrator, seed, payload bytes, checksum} + w*h float4 sums.
+ * Resume: novum_accum_load, then novum_render(..., firstSample = sampleCount, ...) and add - sample k of a pixel depends only on
+ * (seed, pixel, k). Host only, no GPU needed. Written via "<path>.part" + rename; load verifies size and checksum (NOVUM_E_IO). */
+int  novum_accum_save(const char* path, const NovumFloat4* colors, int w, int h, int sampleCount, uint64_t seed, int integrator);
+int  novum_accum_info(const char* path, int* w, int* h, int* sampleCount, uint64_t* seed, int* integrator);
+int  novum_accum_load(const char* path, NovumFloat4* colors, int w, int h, int* sampleCount, uint64_t* seed);
 
 #ifdef __cplusplus
 }

@@ -68,6 +68,24 @@ def test_sample_ranges_and_shards_compose(cornell):
     assert np.allclose(full, again, rtol=1e-5, atol=1e-6)              # only float-atomic ordering differs run to run
 
 
+def test_render_resumes_from_a_checkpoint(cornell, tmp_path):
+    """stop after 5 passes, write the sums, load them in a 'new process', continue at sample 5 - the result is
+    the uninterrupted 12-pass render (up to float-atomic ordering) and the saved frame finishes to the same picture."""
+    cfg = _small_cfg(cornell, 56, 40)
+    cam = nb.camera_make(cfg)
+    full, _ = cornell.render(cfg, cam, 0, 12, seed=777)
+    part, _ = cornell.render(cfg, cam, 0, 5, seed=777)
+    ck = str(tmp_path / "cornell.novumacc")
+    nb.accum_save(ck, part, 5, seed=777, integrator=cfg.integrator)
+    sums, done, seed = nb.accum_load(ck)
+    assert done == 5 and seed == 777 and np.array_equal(sums.view(np.uint32), part.view(np.uint32))
+    rest, _ = cornell.render(cfg, cam, done, 12 - done, seed=seed)
+    assert np.allclose(full, sums + rest, rtol=1e-4, atol=1e-5)
+    a = nb.frame_finish(full, None, 12, nb.FRAME_FINAL, True)
+    b = nb.frame_finish(sums + rest, None, 12, nb.FRAME_FINAL, True)
+    assert np.mean(a != b) < 1e-3 and np.abs(a.astype(int) - b.astype(int)).max() <= 1      # a byte may sit on a rounding step
+
+
 def test_odd_resolution_and_zero_samples(cornell):
     cfg = _small_cfg(cornell, 37, 19)
     cam = nb.camera_make(cfg)
