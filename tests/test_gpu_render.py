@@ -86,6 +86,35 @@ def test_render_resumes_from_a_checkpoint(cornell, tmp_path):
     assert np.mean(a != b) < 1e-3 and np.abs(a.astype(int) - b.astype(int)).max() <= 1      # a byte may sit on a rounding step
 
 
+def test_cli_checkpointed_run_resumes(scene_dirs, tmp_path):
+    """The command-line driver with --checkpoint: a run cut short at 5 passes and started again reaches the same sums as an
+    uninterrupted run of 8 (the tool renders `--every` passes at a time and rewrites the checkpoint after each chunk)."""
+    import subprocess
+    tool = os.path.join(os.path.dirname(os.path.abspath(nb.__file__)), "novum")
+    if not os.path.exists(tool):
+        pytest.skip("command-line driver not built")
+    cfgp = os.path.join(scene_dirs["cornell"], "configs", "config.rendertron")
+    cwd = scene_dirs["cornell"]
+
+    def run(*extra):
+        r = subprocess.run([tool, "--config", cfgp, "--seed", "4242", *extra], cwd=cwd, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout + r.stderr
+        return r.stdout
+
+    ck = str(tmp_path / "cli.novumacc")
+    run("--spp", "8", "--out", str(tmp_path / "full"), "--raw")
+    run("--spp", "5", "--out", str(tmp_path / "cut"), "--checkpoint", ck, "--every", "3")
+    assert nb.accum_info(ck)["sample_count"] == 5 and nb.accum_info(ck)["seed"] == 4242
+    out = run("--spp", "8", "--out", str(tmp_path / "resumed"), "--checkpoint", ck, "--every", "3", "--raw")
+    assert "resuming at sample 5 of 8" in out and nb.accum_info(ck)["sample_count"] == 8
+    full = np.fromfile(str(tmp_path / "full.raw"), np.float32)
+    resumed = np.fromfile(str(tmp_path / "resumed.raw"), np.float32)
+    assert full.size == resumed.size and np.allclose(full, resumed, rtol=1e-4, atol=1e-5)
+    sums, n, _ = nb.accum_load(ck)
+    assert n == 8 and np.array_equal(sums.ravel().view(np.uint32), resumed.view(np.uint32))
+    assert os.path.getsize(str(tmp_path / "resumed_progress.bmp")) == os.path.getsize(str(tmp_path / "resumed.bmp"))
+
+
 def test_odd_resolution_and_zero_samples(cornell):
     cfg = _small_cfg(cornell, 37, 19)
     cam = nb.camera_make(cfg)
