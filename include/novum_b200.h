@@ -340,7 +340,8 @@ int  novum_frame_save_bmp(const char* path, const NovumFloat4* d_colors, const N
  * the kernel runs on the library's save stream once `renderStream` (a cudaStream_t, NULL = default stream) has reached this call,
  * `renderStream` then waits for the kernel only - it has read the accumulators - and the read-back and the file write overlap whatever
  * is queued next. Returns once the work is queued; at most two saves in flight (a third call waits for the oldest).
- * novum_frame_save_wait blocks until every queued file is on disk and returns the first error since the last wait. */
+ * novum_frame_save_wait blocks until every queued file is on disk and returns the first error since the last wait. One saver per
+ * process (one process per GPU): it belongs to the device current at its first call, calls from another device return NOVUM_E_ARG. */
 int  novum_frame_save_bmp_async(const char* path, const NovumFloat4* d_colors, const NovumFloat4* d_overlay, int w, int h,
                                 int sampleCount, int mode, int postProcess, void* renderStream);
 int  novum_frame_save_wait(void);
