@@ -133,6 +133,11 @@ def _declare(L):
     L.novum_frame_last_ms.argtypes = [C.POINTER(cf)]
     L.novum_frame_gamma_steps.argtypes = [vp]
     L.novum_save_pfm.argtypes = [C.c_char_p, vp, ci, ci, cf]
+    L.novum_obj_parse.argtypes = [C.c_char_p, C.POINTER(cf * 3), ci, cf, ci, ci, C.POINTER(vp)]
+    L.novum_obj_free.argtypes = [vp]
+    L.novum_obj_free.restype = None
+    L.novum_obj_counts.argtypes = [vp, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)]
+    L.novum_obj_download.argtypes = [vp, vp, vp, vp, vp]
     L.novum_accum_save.argtypes = [C.c_char_p, vp, ci, ci, ci, C.c_uint64, ci]
     L.novum_accum_info.argtypes = [C.c_char_p, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(C.c_uint64), C.POINTER(ci)]
     L.novum_accum_load.argtypes = [C.c_char_p, vp, ci, ci, C.POINTER(ci), C.POINTER(C.c_uint64)]
@@ -302,6 +307,23 @@ class Scene:
         _check(lib().novum_render_device(self.h, C.byref(cfg), C.byref(cam), first_sample, num_sample, Shard(rank, world), seed,
                                          C.c_void_p(d_colors), C.byref(st)), "novum_render_device")
         return st
+
+
+def obj_parse(path, emission=(0.0, 0.0, 0.0), material_id=0, y_offset=0.0, threads=0, chunk_bytes=0):
+    """One OBJ file through the host front end (no GPU): -> (pos (n,4), nrm (n,4), uv (n,2), tris TRI_DTYPE, n_lights)."""
+    h = C.c_void_p()
+    e = (C.c_float * 3)(*[float(x) for x in emission])
+    _check(lib().novum_obj_parse(os.fsencode(path), C.byref(e), int(material_id), float(y_offset), int(threads), int(chunk_bytes), C.byref(h)),
+           "novum_obj_parse")
+    try:
+        n = [C.c_int() for _ in range(5)]
+        _check(lib().novum_obj_counts(h, *[C.byref(x) for x in n]), "novum_obj_counts")
+        pos = np.zeros((n[0].value, 4), np.float32); nrm = np.zeros((n[1].value, 4), np.float32)
+        uv = np.zeros((n[2].value, 2), np.float32); tris = np.zeros(n[3].value, TRI_DTYPE)
+        _check(lib().novum_obj_download(h, _ptr(pos), _ptr(nrm), _ptr(uv), _ptr(tris)), "novum_obj_download")
+        return pos, nrm, uv, tris, n[4].value
+    finally:
+        lib().novum_obj_free(h)
 
 
 def accum_save(path, colors, sample_count, seed=103033, integrator=0):

@@ -16,7 +16,9 @@
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace nv {
@@ -272,10 +274,140 @@ static int scanDoubles(const char* p, double* out, int n) {
     return got;
 }
 
-// Same records as the reference's readObjSimple (main.cu:936-1068) in the same order; the file is read in one piece and walked with
-// strtod / atoi on the buffer (the getline + sscanf + istringstream form of the first version took 0.85 s for the 871k-triangle
-// dragon, all of it parsing).
-int loadObj(const std::string& file, HostMesh& M, const float emission[3], int materialID, float yOffset) {
+// Same records as the reference's readObjSimple (main.cu:936-1068) in the same order. The file is read in one piece, cut into chunks at
+// line ends and parsed by several host threads in two sweeps (the getline + sscanf + istringstream form of the first version took
+// 0.85 s for the 871k-triangle dragon, the single-threaded buffer walk 0.30 s):
+//   sweep A  every chunk parses its `v` lines; positions are concatenated, so that sweep B may look up any vertex of the file;
+//   sweep B  every chunk parses its vt / vn / f lines into chunk-local arrays in file order. What the sequential loader decides from
+//            "how far the file has been read" is kept: a face may only use positions declared before it (chunk base + running count),
+//            face normals generated for faces without `vn` references sit between the `vn` records in file order, and the single
+//            all-zero uv shared by faces without `vt` references is inserted where the FIRST such face stands;
+//   fix-up   prefix sums over the chunks turn chunk-local normal / triangle / light numbers into global ones.
+// One chunk (small files, threads = 1) is the sequential loader; tests/test_host.py holds chunked parses of adversarial files equal to it.
+struct ObjChunk {
+    char* begin = nullptr; char* end = nullptr;
+    std::vector<NovumFloat4> pos, nrm;
+    std::vector<NovumFloat2> uv;
+    std::vector<NovumTriangle> tris;
+    std::vector<unsigned char> flags;       // per triangle: 1 = normal index is chunk-local (generated), 2 = uses the shared zero uv
+    int posBase = 0, zeroUvAt = -1;
+};
+
+template <class F> static void forEachLine(char* cur, char* const endAll, F f) {
+    while (cur && cur < endAll) {
+        char* p = cur;
+        char* nl = (char*)memchr(cur, '\n', (size_t)(endAll - cur));
+        char* lineEnd = nl ? nl : endAll;
+        cur = nl ? nl + 1 : endAll;
+        const char saved = *lineEnd;            // terminate the line in place (std::string keeps a writable NUL at the end)
+        *lineEnd = 0;
+        if (!(p == lineEnd || p[0] == '#' || p[0] == 's')) f(p);
+        *lineEnd = saved;
+    }
+}
+static inline bool isPosLine(const char* p) { return p[0] == 'v' && (p[1] == ' ' || p[1] == '\t'); }
+
+static void objSweepA(ObjChunk& c, float yOffset) {
+    // one allocation per array, sized from the chunk's bytes (a record line has at least ~8 characters per number): growing by
+    // doubling would map, touch and unmap every array several times, and with many threads the page faults serialise in the kernel
+    if ((size_t)(c.end - c.begin) > 65536) c.pos.reserve((size_t)(c.end - c.begin) / 16);
+    forEachLine(c.begin, c.end, [&](char* p) {
+        if (!isPosLine(p)) return;
+        double d[3] = {0, 0, 0};
+        scanDoubles(p + 2, d, 3);
+        NovumFloat4 q = {(float)d[0], (float)d[1], (float)d[2], 0.f};
+        q.y = q.y + yOffset;
+        c.pos.push_back(q);
+    });
+}
+
+static void objSweepB(ObjChunk& c, const std::vector<NovumFloat4>& allPos, int startIndex, int nStart, int uvStart,
+                      const float emission[3], int materialID) {
+    std::vector<int> vi, ti, ni;
+    int posSeen = startIndex + c.posBase;        // M.pos.size() of the sequential loader at the current line
+    if ((size_t)(c.end - c.begin) > 65536) {
+        const size_t lines = (size_t)(c.end - c.begin) / 8;      // upper bound on triangles / normals of the chunk ("f 1 2 3\n" = 8 bytes)
+        c.tris.reserve(lines); c.flags.reserve(lines); c.nrm.reserve(lines); c.uv.reserve(lines / 2);
+    }
+    forEachLine(c.begin, c.end, [&](char* p) {
+        if (isPosLine(p)) { ++posSeen; return; }
+        if (p[0] == 'v' && p[1] == 't') {
+            double d[2] = {0, 0};
+            scanDoubles(p + 3, d, 2);
+            c.uv.push_back({(float)d[0], 1.0f - (float)d[1]});
+        } else if (p[0] == 'v' && p[1] == 'n') {
+            double d[3] = {0, 0, 0};
+            int got = scanDoubles(p + 3, d, 3);
+            NovumFloat4 n = {(float)d[0], (float)d[1], (float)d[2], 0.f};
+            if (got != 3 || std::isnan(d[0]) || std::isnan(d[1]) || std::isnan(d[2]) || n.x * n.x + n.y * n.y + n.z * n.z < 1e-12f)
+                n = {0.f, 1.f, 0.f, 0.f};
+            c.nrm.push_back(n);
+        } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
+            vi.clear(); ti.clear(); ni.clear();
+            const char* s = p + 2;
+            while (true) {
+                while (*s && isspace((unsigned char)*s)) ++s;          // operator>> on a string: whitespace-separated tokens
+                if (!*s) break;
+                const char* tokEnd = s;
+                while (*tokEnd && !isspace((unsigned char)*tokEnd)) ++tokEnd;
+                int a = 0, b = 0, cc = 0;
+                a = atoi(s);
+                const char* s1 = (const char*)memchr(s, '/', (size_t)(tokEnd - s));
+                if (s1) {
+                    if (s1 + 1 != tokEnd && s1[1] != '/') b = atoi(s1 + 1);
+                    const char* s2 = (const char*)memchr(s1 + 1, '/', (size_t)(tokEnd - (s1 + 1)));
+                    if (s2 && s2 + 1 != tokEnd) cc = atoi(s2 + 1);
+                }
+                if (a != 0) vi.push_back(a - 1);
+                if (b != 0) ti.push_back(b - 1);
+                if (cc != 0) ni.push_back(cc - 1);
+                s = tokEnd;
+            }
+            bool hasUV = ti.size() == vi.size(), hasN = ni.size() == vi.size();
+            int n = (int)vi.size();
+            for (int i = 1; i < n - 1; ++i) {
+                int i0 = vi[0] + startIndex, i1 = vi[i] + startIndex, i2 = vi[i + 1] + startIndex;
+                if (i0 < 0 || i1 < 0 || i2 < 0 || i0 >= posSeen || i1 >= posSeen || i2 >= posSeen) continue;
+                const NovumFloat4 &p0 = allPos[i0], &p1 = allPos[i1], &p2 = allPos[i2];
+                float e1[3] = {p1.x - p0.x, p1.y - p0.y, p1.z - p0.z}, e2[3] = {p2.x - p0.x, p2.y - p0.y, p2.z - p0.z};
+                float cp[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+                float areaSq = cp[0] * cp[0] + cp[1] * cp[1] + cp[2] * cp[2];
+                if (areaSq < 1e-18f) continue;
+                NovumTriangle t; memset(&t, 0, sizeof(t));
+                unsigned char fl = 0;
+                t.aInd = i0; t.bInd = i1; t.cInd = i2;
+                if (hasN) { t.naInd = ni[0] + nStart; t.nbInd = ni[i] + nStart; t.ncInd = ni[i + 1] + nStart; }
+                else {   // the reference would index normals[-1]; use the face normal instead
+                    float il = 1.0f / sqrtf(areaSq);
+                    c.nrm.push_back({cp[0] * il, cp[1] * il, cp[2] * il, 0.f});
+                    t.naInd = t.nbInd = t.ncInd = (int)c.nrm.size() - 1;
+                    fl |= 1;
+                }
+                if (hasUV) { t.uvaInd = ti[0] + uvStart; t.uvbInd = ti[i] + uvStart; t.uvcInd = ti[i + 1] + uvStart; }
+                else {
+                    if (c.zeroUvAt < 0) { c.uv.push_back({0.f, 0.f}); c.zeroUvAt = (int)c.uv.size() - 1; }
+                    fl |= 2;
+                }
+                t.materialID = materialID;
+                t.emission = {emission[0], emission[1], emission[2], 0.f};
+                c.tris.push_back(t);
+                c.flags.push_back(fl);
+            }
+        }
+    });
+}
+
+template <class F> static void runChunks(int nChunks, int threads, F f) {
+    if (threads <= 1 || nChunks <= 1) { for (int i = 0; i < nChunks; ++i) f(i); return; }
+    std::atomic<int> next(0);
+    auto work = [&]() { for (int i; (i = next.fetch_add(1)) < nChunks;) f(i); };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < std::min(threads, nChunks); ++t) pool.emplace_back(work);
+    work();
+    for (std::thread& t : pool) t.join();
+}
+
+int loadObj(const std::string& file, HostMesh& M, const float emission[3], int materialID, float yOffset, int threads = 0, size_t chunkBytes = 0) {
     FILE* fp = fopen(file.c_str(), "rb");
     if (!fp) return NOVUM_E_IO;
     std::string buf;
@@ -287,91 +419,79 @@ int loadObj(const std::string& file, HostMesh& M, const float emission[3], int m
         fclose(fp);
         buf.resize(got);
     }
-    int startIndex = (int)M.pos.size(), nStart = (int)M.nrm.size(), uvStart = (int)M.uv.size();
-    bool isLight = emission[0] * emission[0] + emission[1] * emission[1] + emission[2] * emission[2] > 0.f;
-    int sharedZeroUV = -1;
-    std::vector<int> vi, ti, ni;
-    char* cur = buf.empty() ? nullptr : &buf[0];
-    char* const endAll = cur ? cur + buf.size() : nullptr;
-    while (cur && cur < endAll) {
-        char* p = cur;
-        char* nl = (char*)memchr(cur, '\n', (size_t)(endAll - cur));
-        char* lineEnd = nl ? nl : endAll;
-        cur = nl ? nl + 1 : endAll;
-        const char saved = *lineEnd;            // terminate the line in place (std::string keeps a writable NUL at the end)
-        *lineEnd = 0;
-        if (p == lineEnd || p[0] == '#' || p[0] == 's') { *lineEnd = saved; continue; }
-        if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) {
-            double d[3] = {0, 0, 0};
-            scanDoubles(p + 2, d, 3);
-            NovumFloat4 q = {(float)d[0], (float)d[1], (float)d[2], 0.f};
-            q.y = q.y + yOffset;
-            M.pos.push_back(q);
-        } else if (p[0] == 'v' && p[1] == 't') {
-            double d[2] = {0, 0};
-            scanDoubles(p + 3, d, 2);
-            M.uv.push_back({(float)d[0], 1.0f - (float)d[1]});
-        } else if (p[0] == 'v' && p[1] == 'n') {
-            double d[3] = {0, 0, 0};
-            int got = scanDoubles(p + 3, d, 3);
-            NovumFloat4 n = {(float)d[0], (float)d[1], (float)d[2], 0.f};
-            if (got != 3 || std::isnan(d[0]) || std::isnan(d[1]) || std::isnan(d[2]) || n.x * n.x + n.y * n.y + n.z * n.z < 1e-12f)
-                n = {0.f, 1.f, 0.f, 0.f};
-            M.nrm.push_back(n);
-        } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
-            vi.clear(); ti.clear(); ni.clear();
-            const char* s = p + 2;
-            while (true) {
-                while (*s && isspace((unsigned char)*s)) ++s;          // operator>> on a string: whitespace-separated tokens
-                if (!*s) break;
-                const char* tokEnd = s;
-                while (*tokEnd && !isspace((unsigned char)*tokEnd)) ++tokEnd;
-                int a = 0, b = 0, c = 0;
-                a = atoi(s);
-                const char* s1 = (const char*)memchr(s, '/', (size_t)(tokEnd - s));
-                if (s1) {
-                    if (s1 + 1 != tokEnd && s1[1] != '/') b = atoi(s1 + 1);
-                    const char* s2 = (const char*)memchr(s1 + 1, '/', (size_t)(tokEnd - (s1 + 1)));
-                    if (s2 && s2 + 1 != tokEnd) c = atoi(s2 + 1);
-                }
-                if (a != 0) vi.push_back(a - 1);
-                if (b != 0) ti.push_back(b - 1);
-                if (c != 0) ni.push_back(c - 1);
-                s = tokEnd;
-            }
-            bool hasUV = ti.size() == vi.size(), hasN = ni.size() == vi.size();
-            int n = (int)vi.size();
-            for (int i = 1; i < n - 1; ++i) {
-                int i0 = vi[0] + startIndex, i1 = vi[i] + startIndex, i2 = vi[i + 1] + startIndex;
-                if (i0 < 0 || i1 < 0 || i2 < 0 || i0 >= (int)M.pos.size() || i1 >= (int)M.pos.size() || i2 >= (int)M.pos.size()) continue;
-                const NovumFloat4 &p0 = M.pos[i0], &p1 = M.pos[i1], &p2 = M.pos[i2];
-                float e1[3] = {p1.x - p0.x, p1.y - p0.y, p1.z - p0.z}, e2[3] = {p2.x - p0.x, p2.y - p0.y, p2.z - p0.z};
-                float cp[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
-                float areaSq = cp[0] * cp[0] + cp[1] * cp[1] + cp[2] * cp[2];
-                if (areaSq < 1e-18f) continue;
-                NovumTriangle t; memset(&t, 0, sizeof(t));
-                t.aInd = i0; t.bInd = i1; t.cInd = i2;
-                if (hasN) { t.naInd = ni[0] + nStart; t.nbInd = ni[i] + nStart; t.ncInd = ni[i + 1] + nStart; }
-                else {   // the reference would index normals[-1]; use the face normal instead
-                    float il = 1.0f / sqrtf(areaSq);
-                    M.nrm.push_back({cp[0] * il, cp[1] * il, cp[2] * il, 0.f});
-                    t.naInd = t.nbInd = t.ncInd = (int)M.nrm.size() - 1;
-                }
-                if (hasUV) { t.uvaInd = ti[0] + uvStart; t.uvbInd = ti[i] + uvStart; t.uvcInd = ti[i + 1] + uvStart; }
-                else {
-                    if (sharedZeroUV < 0) { M.uv.push_back({0.f, 0.f}); sharedZeroUV = (int)M.uv.size() - 1; }
-                    t.uvaInd = t.uvbInd = t.uvcInd = sharedZeroUV;
-                }
-                t.materialID = materialID;
-                t.emission = {emission[0], emission[1], emission[2], 0.f};
-                t.lightInd = isLight ? M.numLights : -51;
-                t.triInd = (int)M.tris.size();
-                M.tris.push_back(t);
-                if (isLight) M.numLights++;
-            }
+    const bool timing = getenv("NOVUM_OBJ_TIMING") != nullptr;
+    auto tick = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "loadObj %-10s %.1f ms\n", what, std::chrono::duration<double, std::milli>(now - tick).count());
+        tick = now;
+    };
+    lap("read");
+    if (threads <= 0) { threads = (int)std::thread::hardware_concurrency(); if (threads < 1) threads = 1; if (threads > 16) threads = 16; }
+    // chunks of 256 KiB .. 1 MiB handed out from a queue, about eight per thread: positions sit at the start of a file and faces at its
+    // end, so the two sweeps load different chunks; files below 256 KiB are one chunk, i.e. the sequential loader
+    if (chunkBytes == 0) chunkBytes = std::min<size_t>(std::max<size_t>(buf.size() / ((size_t)threads * 8) + 1, (size_t)256 << 10), (size_t)1 << 20);
+    const int startIndex = (int)M.pos.size(), nStart = (int)M.nrm.size(), uvStart = (int)M.uv.size();
+    const bool isLight = emission[0] * emission[0] + emission[1] * emission[1] + emission[2] * emission[2] > 0.f;
+    std::vector<ObjChunk> chunks;
+    if (!buf.empty()) {
+        char* const base = &buf[0];
+        char* const endAll = base + buf.size();
+        char* cur = base;
+        while (cur < endAll) {
+            char* want = (size_t)(endAll - cur) > chunkBytes ? cur + chunkBytes : endAll;
+            if (want < endAll) { char* nl = (char*)memchr(want, '\n', (size_t)(endAll - want)); want = nl ? nl + 1 : endAll; }
+            ObjChunk c; c.begin = cur; c.end = want;
+            chunks.push_back(std::move(c));
+            cur = want;
         }
-        *lineEnd = saved;
     }
+    const int nc = (int)chunks.size();
+    lap("split");
+    runChunks(nc, threads, [&](int i) { objSweepA(chunks[i], yOffset); });
+    lap("sweepA");
+    size_t addPos = 0;
+    for (ObjChunk& c : chunks) { c.posBase = (int)addPos; addPos += c.pos.size(); }
+    M.pos.resize((size_t)startIndex + addPos);
+    runChunks(nc, threads, [&](int i) { if (!chunks[i].pos.empty()) memcpy(&M.pos[(size_t)startIndex + chunks[i].posBase], chunks[i].pos.data(), chunks[i].pos.size() * sizeof(NovumFloat4)); });
+    lap("gatherPos");
+    runChunks(nc, threads, [&](int i) { objSweepB(chunks[i], M.pos, startIndex, nStart, uvStart, emission, materialID); });
+    lap("sweepB");
+    // fix-up: only the first chunk (in file order) that needed the shared zero uv keeps its copy
+    int firstZero = -1;
+    for (int i = 0; i < nc && firstZero < 0; ++i) if (chunks[i].zeroUvAt >= 0) firstZero = i;
+    std::vector<size_t> nrmBase(nc), uvBase(nc), triBase(nc);
+    size_t nN = M.nrm.size(), nU = M.uv.size(), nT = M.tris.size();
+    int sharedZeroUV = -1;
+    for (int i = 0; i < nc; ++i) {
+        nrmBase[i] = nN; uvBase[i] = nU; triBase[i] = nT;
+        if (i == firstZero) sharedZeroUV = (int)(nU + (size_t)chunks[i].zeroUvAt);
+        nN += chunks[i].nrm.size();
+        nU += chunks[i].uv.size() - ((chunks[i].zeroUvAt >= 0 && i != firstZero) ? 1 : 0);
+        nT += chunks[i].tris.size();
+    }
+    const int lightBase = M.numLights;
+    const size_t triStart = M.tris.size();
+    M.nrm.resize(nN); M.uv.resize(nU); M.tris.resize(nT);
+    lap("resize");
+    runChunks(nc, threads, [&](int i) {
+        ObjChunk& c = chunks[i];
+        if (!c.nrm.empty()) memcpy(&M.nrm[nrmBase[i]], c.nrm.data(), c.nrm.size() * sizeof(NovumFloat4));
+        size_t o = uvBase[i];
+        for (size_t k = 0; k < c.uv.size(); ++k) { if ((int)k == c.zeroUvAt && i != firstZero) continue; M.uv[o++] = c.uv[k]; }
+        for (size_t k = 0; k < c.tris.size(); ++k) {
+            NovumTriangle t = c.tris[k];
+            if (c.flags[k] & 1) { t.naInd += (int)nrmBase[i]; t.nbInd = t.ncInd = t.naInd; }
+            if (c.flags[k] & 2) t.uvaInd = t.uvbInd = t.uvcInd = sharedZeroUV;
+            const size_t g = triBase[i] + k;
+            t.triInd = (int)g;
+            t.lightInd = isLight ? lightBase + (int)(g - triStart) : -51;
+            M.tris[g] = t;
+        }
+    });
+    lap("fixup");
+    if (isLight) M.numLights += (int)(nT - triStart);
     return 0;
 }
 
@@ -504,6 +624,37 @@ int novum_save_pfm(const char* path, const NovumFloat4* colors, int w, int h, fl
         fwrite(row.data(), sizeof(float), row.size(), f);
     }
     fclose(f);
+    return 0;
+}
+
+// ---- host-only view of the OBJ front end (inspection / tests: no GPU, no BVH) ------------------------------------------------------------
+struct NovumObjMesh { HostMesh M; };
+
+int novum_obj_parse(const char* path, const float emission[3], int materialID, float yOffset, int threads, int chunkBytes, NovumObjMesh** out) {
+    if (!path || !out || threads < 0 || chunkBytes < 0) return NOVUM_E_ARG;
+    const float zero[3] = {0.f, 0.f, 0.f};
+    NovumObjMesh* m = new NovumObjMesh();
+    int rc = loadObj(path, m->M, emission ? emission : zero, materialID, yOffset, threads, (size_t)chunkBytes);
+    if (rc) { delete m; return rc; }
+    *out = m;
+    return 0;
+}
+void novum_obj_free(NovumObjMesh* m) { delete m; }
+int novum_obj_counts(const NovumObjMesh* m, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights) {
+    if (!m) return NOVUM_E_ARG;
+    if (nPos) *nPos = (int)m->M.pos.size();
+    if (nNorm) *nNorm = (int)m->M.nrm.size();
+    if (nUV) *nUV = (int)m->M.uv.size();
+    if (nTri) *nTri = (int)m->M.tris.size();
+    if (nLights) *nLights = m->M.numLights;
+    return 0;
+}
+int novum_obj_download(const NovumObjMesh* m, NovumFloat4* positions, NovumFloat4* normals, NovumFloat2* uvs, NovumTriangle* tris) {
+    if (!m) return NOVUM_E_ARG;
+    if (positions && !m->M.pos.empty()) memcpy(positions, m->M.pos.data(), m->M.pos.size() * sizeof(NovumFloat4));
+    if (normals && !m->M.nrm.empty()) memcpy(normals, m->M.nrm.data(), m->M.nrm.size() * sizeof(NovumFloat4));
+    if (uvs && !m->M.uv.empty()) memcpy(uvs, m->M.uv.data(), m->M.uv.size() * sizeof(NovumFloat2));
+    if (tris && !m->M.tris.empty()) memcpy(tris, m->M.tris.data(), m->M.tris.size() * sizeof(NovumTriangle));
     return 0;
 }
 

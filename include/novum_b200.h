@@ -201,6 +201,15 @@ int  novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs,
 /* the OBJ front end's number reader (what sscanf("%lf") / operator>> return in main.cu:936-1068, i.e. strtod): exported so that its
  * fast path can be held to strtod by the CPU tests. *consumed = characters read (0: no number). */
 double novum_parse_double(const char* text, int* consumed);
+/* Host-only view of the OBJ front end (main.cu:936-1068 restated; no GPU, no BVH): parses ONE file into the arrays a scene load would
+ * append. threads 0 = one per host core (at most 16), chunkBytes 0 = 256 KiB .. 1 MiB, about eight chunks per thread; any (threads, chunkBytes)
+ * gives the arrays of the sequential loader (threads = 1, one chunk) - the tests parse adversarial files in 48-byte chunks. */
+typedef struct NovumObjMesh NovumObjMesh;
+int  novum_obj_parse(const char* path, const float emission[3], int materialID, float yOffset, int threads, int chunkBytes,
+                     NovumObjMesh** out);
+void novum_obj_free(NovumObjMesh* m);
+int  novum_obj_counts(const NovumObjMesh* m, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights);
+int  novum_obj_download(const NovumObjMesh* m, NovumFloat4* positions, NovumFloat4* normals, NovumFloat2* uvs, NovumTriangle* tris);
 int  novum_material_table(NovumMaterial* out24);                      /* main.cu:397-467, 24 entries */
 int  novum_camera_make(const NovumRenderConfig* cfg, NovumCamera* out); /* objects.cuh:221-266, 309-325 */
 /* copies of the scene arrays back to host, for oracles and tests */

@@ -181,3 +181,68 @@ def test_accumulator_checkpoint_roundtrip_and_damage(built, tmp_path):
         nb.accum_info(str(tmp_path / "missing.novumacc"))
     with pytest.raises(nb.NovumError):
         nb.accum_save(str(tmp_path / "no_dir" / "x.novumacc"), acc, 1)
+
+
+def _adversarial_obj(path, rng, n_lines=600):
+    """An OBJ whose result depends on everything the sequential loader decides from 'how far the file has been read'."""
+    out, nv, nvt, nvn = [], 0, 0, 0
+    for k in range(n_lines):
+        r = rng.random()
+        if r < 0.30 or nv < 4:
+            out.append("v %s %s %s" % tuple(rng.choice(["%.6f", "%.3e", "%d", "%.17g"]) % x for x in rng.normal(0, 3, 3))); nv += 1
+        elif r < 0.38:
+            out.append("vt %.5f %.5f" % tuple(rng.random(2))); nvt += 1
+        elif r < 0.46:
+            out.append(rng.choice(["vn %.4f %.4f %.4f" % tuple(rng.normal(0, 1, 3)), "vn 0 0 0", "vn 1 2", "vn nan 0 1"])); nvn += 1
+        elif r < 0.50:
+            out.append(rng.choice(["# comment", "s off", "", "g group", "usemtl m", "   "]))
+        else:
+            m = int(rng.integers(3, 6))
+            hi = nv + (3 if rng.random() < 0.15 else 0)              # sometimes a vertex that is only declared LATER (must be dropped)
+            idx = rng.integers(1, hi + 1, m)
+            if rng.random() < 0.08:
+                idx[1] = idx[0]                                       # degenerate
+            if rng.random() < 0.05:
+                idx[0] = -int(rng.integers(1, 3))                     # negative index: no relative addressing in the reference
+            style = rng.random()
+            if style < 0.3 or nvt == 0 or nvn == 0:
+                toks = ["%d" % a for a in idx]                                          # generated normal + shared zero uv
+            elif style < 0.5:
+                toks = ["%d//%d" % (a, rng.integers(1, nvn + 1)) for a in idx]          # shared zero uv only
+            elif style < 0.7:
+                toks = ["%d/%d" % (a, rng.integers(1, nvt + 1)) for a in idx]           # generated normal only
+            else:
+                toks = ["%d/%d/%d" % (a, rng.integers(1, nvt + 1), rng.integers(1, nvn + 1)) for a in idx]
+            out.append("f " + rng.choice([" ", "\t", "  "]).join(toks))
+    text = "\r\n".join(out) if rng.random() < 0.3 else "\n".join(out)
+    open(path, "w", newline="").write(text + ("" if rng.random() < 0.5 else "\n"))
+
+
+def test_obj_chunked_parse_equals_sequential(built, tmp_path):
+    """The multi-threaded OBJ front end: any chunking gives the arrays of the one-chunk (sequential) parse, bit for bit."""
+    rng = np.random.default_rng(2024)
+    for trial in range(12):
+        p = str(tmp_path / f"adv{trial}.obj")
+        _adversarial_obj(p, rng)
+        e = (0.0, 0.0, 0.0) if trial % 3 else (5.0, 4.0, 3.0)
+        ref = nb.obj_parse(p, e, 7, 0.25, threads=1, chunk_bytes=1 << 30)
+        assert len(ref[3]) > 50 and len(ref[1]) > 10
+        for threads, chunk in ((1, 48), (4, 48), (3, 333), (8, 4096), (0, 0)):
+            got = nb.obj_parse(p, e, 7, 0.25, threads=threads, chunk_bytes=chunk)
+            for a, b in zip(ref[:4], got[:4]):
+                assert a.shape == b.shape and a.tobytes() == b.tobytes(), (trial, threads, chunk)
+            assert got[4] == ref[4] == (len(ref[3]) if trial % 3 == 0 else 0)
+
+
+def test_obj_parse_equals_python_loader(scene_dirs):
+    """Independent restatement (tests/scene_utils.py) on a generated mesh, parsed in 64 KiB chunks by 4 threads."""
+    from scene_utils import load_obj_into
+    path = os.path.join(scene_dirs["dragon"], "scenedata", "dragon_vrip.obj")
+    pos, nrm, uv, tris, nl = [], [], [], [], [0]
+    load_obj_into(path, pos, nrm, uv, tris, (0.0, 0.0, 0.0), 5, nl)
+    g = nb.obj_parse(path, (0.0, 0.0, 0.0), 5, 0.0, threads=4, chunk_bytes=65536)
+    assert np.array_equal(np.array(pos, np.float32), g[0]) and np.array_equal(np.array(nrm, np.float32), g[1])
+    assert np.array_equal(np.array(uv, np.float32), g[2])
+    want = np.array(tris, g[3].dtype)
+    for f in ("aInd", "bInd", "cInd", "naInd", "nbInd", "ncInd", "uvaInd", "uvbInd", "uvcInd", "materialID", "lightInd", "triInd"):
+        assert np.array_equal(want[f], g[3][f]), f
