@@ -304,7 +304,7 @@ def run_ours(args):
                        "l2": "256 MB flush between steps; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
                        "scene_load_s": round(load_s, 3), "scene_parse_s": round(info["parse_ms"] * 1e-3, 3), "bvh8_build_ms": round(info["bvh8_build_ms"], 3),
                        "bvh8_build_launches": info["bvh8_build_launches"],
-                       "scene_load_note": "first load in this process: bvh8_build_ms includes CUDA module loading and the build's cudaMallocs; repeated loads: parse 0.13 s (16 host threads) + build 7.4 ms for 871k triangles (profiles/r1_scene_load_breakdown.txt)"},
+                       "scene_load_note": "first load in this process: bvh8_build_ms includes CUDA module loading and the build's cudaMallocs; repeated loads: parse 0.06 s (16 host threads) + build 7 ms for 871k triangles (profiles/r1_scene_load_breakdown.txt)"},
             "paths_per_s": tot_paths / (max_dev_ms * 1e-3), "rays_per_path": tot_rays / max(1.0, tot_paths),
             "wall_ms_per_step": max_wall_ms / args.steps,
             "e2e": {"value": float(e2e_t.item()) / e2e_wall / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 112 + 200,

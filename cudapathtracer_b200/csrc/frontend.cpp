@@ -17,6 +17,10 @@
 #include <fstream>
 #include <sstream>
 #include <atomic>
+#include <fcntl.h>
+#include <memory>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <string>
 #include <thread>
 #include <vector>
@@ -215,10 +219,19 @@ void makeCamera(const NovumRenderConfig* cfg, NovumCamera* c) {
 }
 
 // ---- OBJ (main.cu:936-1068) ---------------------------------------------------------------------------
+// resize() of these arrays leaves new elements unwritten (default-initialised PODs): the loader fills them from several threads, a
+// zero-fill by the calling thread first would touch - page-fault - every new page serially (45 ms for the 871k-triangle dragon)
+template <class T> struct DefaultInitAlloc : std::allocator<T> {
+    template <class U> struct rebind { using other = DefaultInitAlloc<U>; };
+    using std::allocator<T>::allocator;
+    template <class U> void construct(U* p) noexcept { ::new ((void*)p) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+};
+template <class T> using RawVec = std::vector<T, DefaultInitAlloc<T>>;
 struct HostMesh {
-    std::vector<NovumFloat4> pos, nrm;
-    std::vector<NovumFloat2> uv;
-    std::vector<NovumTriangle> tris;
+    RawVec<NovumFloat4> pos, nrm;
+    RawVec<NovumFloat2> uv;
+    RawVec<NovumTriangle> tris;
     int numLights = 0;
 };
 
@@ -321,7 +334,7 @@ static void objSweepA(ObjChunk& c, float yOffset) {
     });
 }
 
-static void objSweepB(ObjChunk& c, const std::vector<NovumFloat4>& allPos, int startIndex, int nStart, int uvStart,
+static void objSweepB(ObjChunk& c, const NovumFloat4* allPos, int startIndex, int nStart, int uvStart,
                       const float emission[3], int materialID) {
     std::vector<int> vi, ti, ni;
     int posSeen = startIndex + c.posBase;        // M.pos.size() of the sequential loader at the current line
@@ -408,16 +421,28 @@ template <class F> static void runChunks(int nChunks, int threads, F f) {
 }
 
 int loadObj(const std::string& file, HostMesh& M, const float emission[3], int materialID, float yOffset, int threads = 0, size_t chunkBytes = 0) {
-    FILE* fp = fopen(file.c_str(), "rb");
-    if (!fp) return NOVUM_E_IO;
-    std::string buf;
+    // The text is read by several threads (pread, 4 MiB pieces) into a buffer that is not zero-filled first; one byte more than the
+    // file so that the last line can be NUL-terminated in place like the others. (A private copy-on-write mapping of the file instead
+    // was 4x SLOWER with threads: every page is written once - the line ends - and the copy-on-write faults serialise in the kernel.)
+    struct Text { char* base = nullptr; size_t size = 0; RawVec<char> owned; } text;
     {
-        fseek(fp, 0, SEEK_END); long sz = ftell(fp); fseek(fp, 0, SEEK_SET);
-        if (sz < 0) { fclose(fp); return NOVUM_E_IO; }
-        buf.resize((size_t)sz);
-        size_t got = sz ? fread(&buf[0], 1, (size_t)sz, fp) : 0;
-        fclose(fp);
-        buf.resize(got);
+        int fd = open(file.c_str(), O_RDONLY);
+        if (fd < 0) return NOVUM_E_IO;
+        struct stat sb;
+        if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode)) { close(fd); return NOVUM_E_IO; }
+        const size_t sz = (size_t)sb.st_size, piece = (size_t)4 << 20;
+        text.owned.resize(sz + 1);
+        std::atomic<bool> bad(false);
+        int readers = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+        if (readers > 8) readers = 8;
+        runChunks((int)((sz + piece - 1) / piece), readers, [&](int i) {
+            size_t off = (size_t)i * piece, end = std::min(sz, off + piece);
+            while (off < end) { ssize_t r = pread(fd, &text.owned[off], end - off, (off_t)off); if (r <= 0) { bad = true; break; } off += (size_t)r; }
+        });
+        close(fd);
+        if (bad) return NOVUM_E_IO;
+        text.owned[sz] = 0;
+        text.base = sz ? text.owned.data() : nullptr; text.size = sz;
     }
     const bool timing = getenv("NOVUM_OBJ_TIMING") != nullptr;
     auto tick = std::chrono::steady_clock::now();
@@ -431,13 +456,13 @@ int loadObj(const std::string& file, HostMesh& M, const float emission[3], int m
     if (threads <= 0) { threads = (int)std::thread::hardware_concurrency(); if (threads < 1) threads = 1; if (threads > 16) threads = 16; }
     // chunks of 256 KiB .. 1 MiB handed out from a queue, about eight per thread: positions sit at the start of a file and faces at its
     // end, so the two sweeps load different chunks; files below 256 KiB are one chunk, i.e. the sequential loader
-    if (chunkBytes == 0) chunkBytes = std::min<size_t>(std::max<size_t>(buf.size() / ((size_t)threads * 8) + 1, (size_t)256 << 10), (size_t)1 << 20);
+    if (chunkBytes == 0) chunkBytes = std::min<size_t>(std::max<size_t>(text.size / ((size_t)threads * 8) + 1, (size_t)256 << 10), (size_t)1 << 20);
     const int startIndex = (int)M.pos.size(), nStart = (int)M.nrm.size(), uvStart = (int)M.uv.size();
     const bool isLight = emission[0] * emission[0] + emission[1] * emission[1] + emission[2] * emission[2] > 0.f;
     std::vector<ObjChunk> chunks;
-    if (!buf.empty()) {
-        char* const base = &buf[0];
-        char* const endAll = base + buf.size();
+    if (text.size) {
+        char* const base = text.base;
+        char* const endAll = base + text.size;
         char* cur = base;
         while (cur < endAll) {
             char* want = (size_t)(endAll - cur) > chunkBytes ? cur + chunkBytes : endAll;
@@ -456,7 +481,7 @@ int loadObj(const std::string& file, HostMesh& M, const float emission[3], int m
     M.pos.resize((size_t)startIndex + addPos);
     runChunks(nc, threads, [&](int i) { if (!chunks[i].pos.empty()) memcpy(&M.pos[(size_t)startIndex + chunks[i].posBase], chunks[i].pos.data(), chunks[i].pos.size() * sizeof(NovumFloat4)); });
     lap("gatherPos");
-    runChunks(nc, threads, [&](int i) { objSweepB(chunks[i], M.pos, startIndex, nStart, uvStart, emission, materialID); });
+    runChunks(nc, threads, [&](int i) { objSweepB(chunks[i], M.pos.data(), startIndex, nStart, uvStart, emission, materialID); });
     lap("sweepB");
     // fix-up: only the first chunk (in file order) that needed the shared zero uv keeps its copy
     int firstZero = -1;
