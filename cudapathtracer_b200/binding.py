@@ -148,6 +148,7 @@ def _declare(L):
     L.novum_hashgrid_build_device.argtypes = [vp, vp, vp, vp, ci, C.POINTER(cf * 3), cf, ci]
     L.novum_hashgrid_query_count.argtypes = [vp, vp, vp, vp, ci, vp]
     L.novum_hashgrid_last_ms.argtypes = [vp, C.POINTER(cf)]
+    L.novum_hashgrid_build_static.argtypes = [vp, vp, vp, ci, ci, C.POINTER(cf * 3), cf, vp, vp, vp, vp, vp]
     L.novum_vcm_create.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), Shard, C.c_uint64, C.POINTER(vp)]
     L.novum_vcm_destroy.argtypes = [vp]
     L.novum_vcm_light_pass.argtypes = [vp, ci, vp]
@@ -449,6 +450,19 @@ class HashGrid:
         ms = C.c_float()
         _check(lib().novum_hashgrid_last_ms(self.h, C.byref(ms)), "novum_hashgrid_last_ms")
         return ms.value
+
+
+STATIC_GRID_MAX_PHOTONS = 1 << 20
+
+
+def hashgrid_build_static(d_px, d_py, d_pz, n, max_photons, scene_min, radius, d_sorted_hash, d_sorted_index, d_cell_start, d_cell_end,
+                          stream=None):
+    """novum_hashgrid_build_static: device pointers (ints) in and out, nothing allocated by the call; asynchronous on `stream`."""
+    mn = (C.c_float * 3)(*scene_min)
+    vp = C.c_void_p
+    _check(lib().novum_hashgrid_build_static(vp(d_px), vp(d_py), vp(d_pz), n, max_photons, C.byref(mn), radius, vp(d_sorted_hash),
+                                             vp(d_sorted_index), vp(d_cell_start), vp(d_cell_end), vp(stream or 0)),
+           "novum_hashgrid_build_static")
 
 
 class _DevBuf:

@@ -6,6 +6,7 @@
 #include "hashgrid.cuh"
 #include "../../include/novum_b200.h"
 #include <cmath>
+#include <mutex>
 #include <vector>
 
 namespace nv {
@@ -298,3 +299,77 @@ int novum_hashgrid_last_ms(NovumHashGrid* h, float* ms) {
 }
 
 }  // extern "C"
+
+// ---- allocation-free grid build -------------------------------------------------------------------------------------
+// novum_hashgrid_build_static: the same hash -> radix sort -> cell table pipeline as novum_hashgrid_build_device for callers that
+// may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). No counterpart in the reference.
+// Inputs and outputs are the caller's device buffers; the sort's ping-pong buffers,
+// per-tile digit histograms and digit totals live in ONE file-scope device array that every GPU loading this library holds until
+// exit (8.25 MiB), which bounds the size: n <= maxPhotons <= NOVUM_STATIC_GRID_MAX_PHOTONS (2^20, the SPPM configuration's 1 M
+// photons per iteration). Every call shares the array and finds the previous call's contents in it. Nothing in it has to start
+// at zero — the histogram rows, digit totals and alternates are written in full for the tiles a call uses before they are read —
+// and the caller's cellStart table is reset to 0xFFFFFFFF inside the call. Two calls that overlap on the GPU (different streams,
+// or different host threads on one device) race on the array: serialise them.
+namespace {
+
+constexpr int kStaticGridMaxPhotons = NOVUM_STATIC_GRID_MAX_PHOTONS;
+constexpr size_t kStaticGridScratchBytes = 2 * sizeof(uint32_t) * (size_t)kStaticGridMaxPhotons      // keysAlt, valsAlt
+                                           + sizeof(uint32_t) * 256 * (size_t)(kStaticGridMaxPhotons / nv::kSortTile)   // hist
+                                           + sizeof(uint32_t) * 256;                                   // digit totals
+static __device__ __align__(256) unsigned char g_staticGridScratch[kStaticGridScratchBytes];
+
+constexpr int kMaxDevices = 64;
+struct StaticGridSlot { bool ready = false; nv::RadixSortPlan plan; };
+StaticGridSlot g_staticGridSlots[kMaxDevices];      // one per device: the symbol has a different address on every GPU
+std::mutex g_staticGridMutex;
+
+// In host code `g_staticGridScratch` is only a handle for the runtime, not a device address: the address valid on the CURRENT
+// device is asked for once per device and kept.
+int staticGridPlan(nv::RadixSortPlan** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return NOVUM_E_UNSUPPORTED;
+    StaticGridSlot& s = g_staticGridSlots[dev];
+    std::lock_guard<std::mutex> lock(g_staticGridMutex);
+    if (!s.ready) {
+        void* ptr = nullptr;
+        if ((e = cudaGetSymbolAddress(&ptr, g_staticGridScratch)) != cudaSuccess) return (int)e;
+        if ((e = nv::radixSortPlanBind(s.plan, ptr, kStaticGridScratchBytes, kStaticGridMaxPhotons)) != cudaSuccess) return (int)e;
+        s.ready = true;
+    }
+    *out = &s.plan;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int novum_hashgrid_build_static(const float* d_px, const float* d_py, const float* d_pz, int n, int maxPhotons,
+                                           const float sceneMin[3], float mergeRadius, uint32_t* d_sortedHash, uint32_t* d_sortedIndex,
+                                           uint32_t* d_cellStart, uint32_t* d_cellEnd, void* stream) {
+    if (!sceneMin || !d_cellStart || !d_cellEnd || n < 0 || maxPhotons <= 0 || n > maxPhotons) return NOVUM_E_ARG;
+    if (maxPhotons > kStaticGridMaxPhotons) return NOVUM_E_TOOBIG;
+    if (n > 0 && (!d_px || !d_py || !d_pz || !d_sortedHash || !d_sortedIndex)) return NOVUM_E_ARG;
+    if (!(mergeRadius > 0.0f) || !std::isfinite(mergeRadius)) return NOVUM_E_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return NOVUM_E_NOGPU;
+    nv::RadixSortPlan* plan = nullptr;
+    int rc = staticGridPlan(&plan);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned tableSize = (unsigned)nv::nextPrime(maxPhotons * 2);          // as novum_hashgrid_create (deviceCode.cu:3283)
+    cudaError_t e = cudaMemsetAsync(d_cellStart, 0xFF, sizeof(uint32_t) * (size_t)tableSize, st);
+    if (e != cudaSuccess) return (int)e;
+    if (n == 0) return 0;
+    nv::GridParams gp;
+    gp.minX = sceneMin[0]; gp.minY = sceneMin[1]; gp.minZ = sceneMin[2]; gp.cell = mergeRadius; gp.tableSize = tableSize;
+    const int T = 256;
+    nv::hashKernel<<<(n + T - 1) / T, T, 0, st>>>(d_px, d_py, d_pz, 1, n, gp, 1.0f / mergeRadius, 0xFFFFFFFFFFFFFFFFull / tableSize + 1ull,
+                                                  d_sortedHash, d_sortedIndex);
+    int bits = 1;
+    while (bits < 32 && (1ull << bits) < (unsigned long long)tableSize) ++bits;
+    if ((e = nv::radixSortPairs(*plan, d_sortedHash, d_sortedIndex, n, bits, st, nullptr)) != cudaSuccess) return (int)e;
+    // tableKernel also records the keys for the next build's selective clear; here that copy goes to the (now free) alternate
+    nv::tableKernel<<<(n + 4 * T - 1) / (4 * T), T, 0, st>>>(d_sortedHash, n, d_cellStart, d_cellEnd, plan->keysAlt);
+    return (int)cudaGetLastError();
+}

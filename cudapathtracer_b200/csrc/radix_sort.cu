@@ -280,6 +280,40 @@ cudaError_t radixSortPlanCreate(RadixSortPlan& plan, int maxN) {
     return cudaSuccess;
 }
 
+static void planLayout(int maxN, int& numTilesMax, size_t& nb, size_t& histBytes, size_t& sumsBytes) {
+    numTilesMax = (maxN + kSortTile - 1) / kSortTile;
+    if (numTilesMax < 1) numTilesMax = 1;
+    const size_t histEntries = (size_t)256 * numTilesMax;
+    size_t scanBlocks = (histEntries + kScanTile - 1) / kScanTile + 1;
+    if (scanBlocks < 256) scanBlocks = 256;
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    nb = up((size_t)(maxN > 0 ? maxN : 1) * sizeof(uint32_t));
+    histBytes = up(histEntries * sizeof(uint32_t));
+    sumsBytes = up(scanBlocks * sizeof(uint32_t));
+}
+
+size_t radixSortScratchBytes(int maxN) {
+    int t; size_t nb, hb, sb;
+    planLayout(maxN, t, nb, hb, sb);
+    return 2 * nb + hb + sb;
+}
+
+cudaError_t radixSortPlanBind(RadixSortPlan& plan, void* d_scratch, size_t scratchBytes, int maxN) {
+    if (!d_scratch || ((uintptr_t)d_scratch & 255) || scratchBytes < radixSortScratchBytes(maxN)) return cudaErrorInvalidValue;
+    cudaError_t ea = cudaFuncSetAttribute(scatterPass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScatterSmem));
+    if (ea != cudaSuccess) return ea;
+    size_t nb, hb, sb;
+    planLayout(maxN, plan.numTilesMax, nb, hb, sb);
+    unsigned char* p = static_cast<unsigned char*>(d_scratch);
+    plan.maxN = maxN;
+    plan.keysAlt = reinterpret_cast<uint32_t*>(p);
+    plan.valsAlt = reinterpret_cast<uint32_t*>(p + nb);
+    plan.hist = reinterpret_cast<uint32_t*>(p + 2 * nb);
+    plan.blockSums = reinterpret_cast<uint32_t*>(p + 2 * nb + hb);
+    plan.bytes = 2 * nb + hb + sb;
+    return cudaSuccess;
+}
+
 void radixSortPlanDestroy(RadixSortPlan& plan) {
     cudaFree(plan.keysAlt); cudaFree(plan.valsAlt); cudaFree(plan.hist); cudaFree(plan.blockSums);
     plan = RadixSortPlan();

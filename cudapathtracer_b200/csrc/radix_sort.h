@@ -23,6 +23,10 @@ constexpr int kSortTile = 4096;     // keys per block per pass
 
 cudaError_t radixSortPlanCreate(RadixSortPlan& plan, int maxN);
 void radixSortPlanDestroy(RadixSortPlan& plan);
+// Bytes of scratch a plan for maxN pairs needs, and a plan laid over caller-owned device scratch of at least that many bytes
+// (256-byte aligned). Nothing is allocated; such a plan must NOT be passed to radixSortPlanDestroy.
+size_t radixSortScratchBytes(int maxN);
+cudaError_t radixSortPlanBind(RadixSortPlan& plan, void* d_scratch, size_t scratchBytes, int maxN);
 
 // Sorts keys[0..n) ascending on bits [0, numBits) (rounded up to whole 8-bit digits), stable.
 // On return the sorted data is in `keys`/`vals` (the plan's alternates are scratch).

@@ -42,6 +42,7 @@ extern "C" {
 #define NOVUM_E_NOSCENE    (-3)
 #define NOVUM_E_NOGPU      (-4)
 #define NOVUM_E_UNSUPPORTED (-5)
+#define NOVUM_E_TOOBIG     (-6)   /* size beyond a fixed built-in limit (novum_hashgrid_build_static) */
 
 typedef struct NovumFloat4 { float x, y, z, w; } NovumFloat4;   /* 16 B, 16-aligned in device arrays */
 typedef struct NovumFloat2 { float x, y; } NovumFloat2;
@@ -285,6 +286,19 @@ int  novum_hashgrid_build(NovumHashGrid* g, const float* px, const float* py, co
 int  novum_hashgrid_query_count(NovumHashGrid* g, const float* qx, const float* qy, const float* qz, int nq,
                                 uint32_t* counts);
 int  novum_hashgrid_last_ms(NovumHashGrid* g, float* ms);
+/* Allocation-free grid build. No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same pipeline and same results as
+ * novum_hashgrid_create(maxPhotons) + novum_hashgrid_build_device, but it owns no object and calls no cudaMalloc / cudaFree / allocating
+ * library routine: all buffers are the caller's DEVICE buffers (positions in; d_sortedHash / d_sortedIndex: n entries each out;
+ * d_cellStart / d_cellEnd: nextPrime(2 * maxPhotons) entries each out, cellStart = 0xFFFFFFFF for empty slots, cellEnd defined only
+ * where cellStart is set), and the radix sort's scratch is a file-scope device array of the library (8.25 MiB held by every GPU that
+ * loads it, until exit). Limit: n <= maxPhotons <= NOVUM_STATIC_GRID_MAX_PHOTONS, otherwise NOVUM_E_TOOBIG. Asynchronous on `stream`
+ * (a cudaStream_t, NULL = default stream). Every call on a device shares the one scratch array: calls that overlap on the GPU race;
+ * serialise them (one stream, or events). */
+#define NOVUM_STATIC_GRID_MAX_PHOTONS (1 << 20)
+int  novum_hashgrid_build_static(const float* d_px, const float* d_py, const float* d_pz, int n, int maxPhotons,
+                                 const float sceneMin[3], float mergeRadius, uint32_t* d_sortedHash, uint32_t* d_sortedIndex,
+                                 uint32_t* d_cellStart, uint32_t* d_cellEnd, void* stream);
 
 /* ---- multi-GPU phase API (one process per GPU; the exchange itself is done by the caller with
  *      NCCL / torch.distributed on the device pointers returned here) --------------------------
