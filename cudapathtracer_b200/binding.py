@@ -57,6 +57,10 @@ class Constants(C.Structure):
                                          "vcmDoMerge", "doSPPM", "bdptDrawPath", "bdptDoMis", "bdptPaintWeight")]
 
 
+class LaunchCacheStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("launches", "hits", "rebinds", "sceneBuilds", "enginesMoved", "progressiveSaves")]
+
+
 class Shard(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32)]
 
@@ -108,6 +112,7 @@ def _declare(L):
     L.novum_scene_counts.argtypes = [vp] + [C.POINTER(ci)] * 5
     L.novum_scene_download.argtypes = [vp, vp, vp, vp, vp, vp]
     L.novum_scene_timings.argtypes = [vp, C.POINTER(cf), C.POINTER(cf), C.POINTER(ci)]
+    L.novum_scene_bvh_depth.argtypes = [vp]
     L.novum_parse_double.restype = C.c_double
     L.novum_parse_double.argtypes = [C.c_char_p, C.POINTER(ci)]
     L.novum_material_table.argtypes = [vp]
@@ -148,6 +153,9 @@ def _declare(L):
     L.novum_hashgrid_build_device.argtypes = [vp, vp, vp, vp, ci, C.POINTER(cf * 3), cf, ci]
     L.novum_hashgrid_query_count.argtypes = [vp, vp, vp, vp, ci, vp]
     L.novum_hashgrid_last_ms.argtypes = [vp, C.POINTER(cf)]
+    L.novum_launch_cache_stats.argtypes = [C.POINTER(LaunchCacheStats)]
+    L.novum_launch_cache_clear.restype = None
+    L.novum_launch_set_progressive.argtypes = [cf, C.c_char_p]
     L.novum_hashgrid_build_static.argtypes = [vp, vp, vp, ci, ci, C.POINTER(cf * 3), cf, vp, vp, vp, vp, vp]
     L.novum_vcm_create.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), Shard, C.c_uint64, C.POINTER(vp)]
     L.novum_vcm_destroy.argtypes = [vp]
@@ -157,6 +165,7 @@ def _declare(L):
     L.novum_vcm_eye_pass.argtypes = [vp, ci, vp]
     L.novum_vcm_stats.argtypes = [vp, C.POINTER(RenderStats)]
     L.novum_vcm_stream.argtypes = [vp, C.POINTER(vp)]
+    L.novum_vcm_reset_stats.argtypes = [vp]
     L.novum_vcm_ipc_export.argtypes = [vp, vp]
     L.novum_vcm_ipc_attach.argtypes = [vp, ci, vp]
     L.novum_vcm_peer_write.argtypes = [vp, ci]
@@ -248,7 +257,8 @@ class Scene:
         pm, bm, bl = C.c_float(), C.c_float(), C.c_int()
         _check(lib().novum_scene_timings(self.h, C.byref(pm), C.byref(bm), C.byref(bl)), "novum_scene_timings")
         return {"tris": nt.value, "lights": nl.value, "bvh8_nodes": nn.value, "min": list(mn), "max": list(mx), "radius": r.value,
-                "parse_ms": pm.value, "bvh8_build_ms": bm.value, "bvh8_build_launches": bl.value}
+                "parse_ms": pm.value, "bvh8_build_ms": bm.value, "bvh8_build_launches": bl.value,
+                "bvh8_depth": lib().novum_scene_bvh_depth(self.h)}
 
     def download(self):
         c = [C.c_int() for _ in range(5)]
@@ -508,6 +518,9 @@ class VcmSession:
         st = RenderStats()
         _check(lib().novum_vcm_stats(self.h, C.byref(st)), "novum_vcm_stats")
         return st
+
+    def reset_stats(self):
+        _check(lib().novum_vcm_reset_stats(self.h), "novum_vcm_reset_stats")
 
     def stream(self):
         s = C.c_void_p()

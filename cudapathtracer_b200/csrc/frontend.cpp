@@ -564,6 +564,7 @@ const char* novum_error_string(int code) {
         case NOVUM_E_NOSCENE: return "null scene handle";
         case NOVUM_E_NOGPU: return "no CUDA device";
         case NOVUM_E_UNSUPPORTED: return "unsupported";
+        case NOVUM_E_TOODEEP: return "BVH deeper than the traversal stack";
         case NOVUM_E_TOOBIG: return "size beyond the entry point's built-in limit";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
     }
@@ -600,13 +601,17 @@ int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene
     // textures (main.cu:371-391): missing files give empty images, like the reference
     std::vector<NovumFloat4> texels; int ts[4], tw[4], th[4];
     const char* texNames[4] = {"textures/enkidutexture.bmp", "textures/enkiduchibitexture.bmp", "textures/leaftex2.bmp", "textures/leafautumn.bmp"};
-    for (int i = 0; i < 4; ++i) { ts[i] = (int)texels.size(); loadBmpTexture(texNames[i], texels, tw[i], th[i]); }
-    NovumMaterial mats[24];
-    buildMaterialTable(mats, ts, tw, th);
     // paths in the config are relative to the working directory in the reference; also try the config's directory
     std::string cfgDir = configPath;
     size_t slash = cfgDir.find_last_of('/');
     cfgDir = slash == std::string::npos ? std::string(".") : cfgDir.substr(0, slash);
+    for (int i = 0; i < 4; ++i) {
+        ts[i] = (int)texels.size();
+        if (!loadBmpTexture(texNames[i], texels, tw[i], th[i]) && !loadBmpTexture(cfgDir + "/" + texNames[i], texels, tw[i], th[i]))
+            loadBmpTexture(cfgDir + "/../" + texNames[i], texels, tw[i], th[i]);
+    }
+    NovumMaterial mats[24];
+    buildMaterialTable(mats, ts, tw, th);
     HostMesh M;
     const auto parseT0 = std::chrono::steady_clock::now();
     for (const MeshCfg& m : meshes) {

@@ -41,9 +41,19 @@ __global__ void compactMaterialsKernel(const NovumMaterial* __restrict__ in, DMa
     d.absorption[0] = m.absorption.x; d.absorption[1] = m.absorption.y; d.absorption[2] = m.absorption.z;
     d.transmission = m.transmission;
     d.texStart = m.startInd; d.texW = m.width; d.texH = m.height;
-    d.flags = (m.hasTexture ? MF_TEXTURE : 0u) | (m.hasTransMap ? MF_TRANSMAP : 0u) | (m.isSpecular ? MF_SPECULAR : 0u) |
-              (m.boundary ? MF_BOUNDARY : 0u) | (m.thinWalled ? MF_THINWALLED : 0u);
-    d.priority = m.priority; d.pad[0] = d.pad[1] = d.pad[2] = 0;
+    // The reference's Material() constructor initialises none of hasTexture / hasTransMap / isSpecular / boundary / thinWalled /
+    // absorption / priority, and each factory sets only some of them (objects.cuh:640-790): a table built by the reference's own
+    // initRender arrives with indeterminate bytes in the rest. They are read here as the factories' evident intent - zero:
+    //   hasTransMap is defined by Leaf and Mirror only; priority by SmoothDielectric only; Mirror leaves boundary / thinWalled /
+    //   absorption unset; a texture of zero size (a missing file, imageUtil.cu:146-149) cannot be sampled (modulo by zero, reflectors.cuh:393).
+    const bool leafOrMirror = m.type == NOVUM_MAT_LEAF || m.type == NOVUM_MAT_DELTAMIRROR;
+    const bool mirror = m.type == NOVUM_MAT_DELTAMIRROR;
+    const bool texOk = m.hasTexture && m.width > 0 && m.height > 0;
+    if (!texOk) { d.texStart = 0; d.texW = 0; d.texH = 0; }
+    if (mirror || m.type == NOVUM_MAT_LEAF) { d.absorption[0] = d.absorption[1] = d.absorption[2] = 0.0f; }
+    d.flags = (texOk ? MF_TEXTURE : 0u) | ((leafOrMirror && m.hasTransMap && texOk) ? MF_TRANSMAP : 0u) | (m.isSpecular ? MF_SPECULAR : 0u) |
+              ((!mirror && m.boundary) ? MF_BOUNDARY : 0u) | ((!mirror && m.thinWalled) ? MF_THINWALLED : 0u);
+    d.priority = m.type == NOVUM_MAT_SMOOTHDIELECTRIC ? m.priority : 0; d.pad[0] = d.pad[1] = d.pad[2] = 0;
     out[i] = d;
 }
 
@@ -78,6 +88,9 @@ int sceneFinalize(NovumScene* s) {
     if ((e = cudaMalloc(&s->d_queueCounter, 4 * sizeof(int))) != cudaSuccess) return (int)e;
     e = buildBvh8(s->d_positions, s->d_tris, s->nTri, s->d_mats, s->stream, s->bvh);
     if (e != cudaSuccess) return (int)e;
+    // A traversal pushes at most one entry (the rest of a node's hit group) per BVH8 level it descends, so the tree's depth bounds the
+    // stack: a tree deeper than the stack (12 shared + 40 local entries) would silently lose subtrees - refuse it here instead.
+    if (s->bvh.levels > kSmemStack + kLocalStack) return NOVUM_E_TOODEEP;
     if ((e = cudaMalloc(&s->d_shadeTris, sizeof(float4) * kShadeTriWords * (size_t)s->nTri)) != cudaSuccess) return (int)e;
     shadeTriKernel<<<(s->nTri + 127) / 128, 128, 0, s->stream>>>(s->d_tris, s->d_normals, s->d_uvs, s->nTri, s->d_shadeTris);
     // main.cu:532-535: centre / radius / min of the root box
@@ -234,6 +247,8 @@ int novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs, 
     if (bvhLaunches) *bvhLaunches = s->bvh.kernelLaunches;
     return 0;
 }
+
+int novum_scene_bvh_depth(const NovumScene* s) { return s ? s->bvh.levels : NOVUM_E_NOSCENE; }
 
 int novum_scene_counts(const NovumScene* s, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights) {
     if (!s) return NOVUM_E_NOSCENE;

@@ -48,4 +48,7 @@ namespace nv {
 int sceneFinalize(NovumScene* s);     // compact materials, BVH8 build, bounds, stream/events
 int ensureStage(NovumScene* s, size_t bytes);
 int smCount();
+int renderDeviceMis(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample, NovumShard shard,
+                    uint64_t seed, NovumFloat4* d_colors, NovumRenderStats* stats, int useMIS);      // wavefront.cu
+void bdRebindScene(void* bdEngine, NovumScene* s);                                                    // vcm.cu: engine buffers outlive a scene rebuild
 }

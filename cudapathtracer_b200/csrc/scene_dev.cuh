@@ -141,7 +141,7 @@ struct ShadowTrav {
                     V3 n = V3(__ldg(sc.normals + tr.na)) * w + V3(__ldg(sc.normals + tr.nb)) * u + V3(__ldg(sc.normals + tr.nc)) * v;
                     float cosT = fabsf(dot(r.d, normalize(n)));
                     float F = schlick(cosT, 1.0f, m.ior);
-                    thr *= m.albedo * (m.transmission * (1.0f - F));
+                    thr *= (m.albedo * m.transmission) * (1.0f - F);     // the reference's association (integratorUtilities.cuh:232)
                     if (maxComp(thr) < 0.01f) { thr = V3(0.0f); return true; }
                 } else {
                     thr = V3(0.0f); return true;

@@ -316,6 +316,14 @@ static void bdResetStats(BdEngine& e) {
 
 static void bdEngineFree(void* p) { BdEngine* e = (BdEngine*)p; bdFree(*e); delete e; }
 
+// the engine's buffers depend on (w, h, depths, mode) only: when the launch boundary rebuilds its scene (new geometry behind the same
+// call, main.cu:925-933 re-renders 75 times) the engine moves to the new scene instead of being freed and re-allocated (16 GB at 4K)
+void bdRebindScene(void* p, NovumScene* s) {
+    BdEngine* e = (BdEngine*)p;
+    if (!e) return;
+    e->scene = s;
+}
+
 static bool bdMatches(const BdEngine& e, const NovumRenderConfig& cfg, NovumShard shard) {
     return e.w == cfg.width && e.h == cfg.height && e.eyeDepth == cfg.bdptEyeDepth && e.lightDepth == cfg.bdptLightDepth &&
            e.mode == bdModeOf(cfg.integrator) && e.rank == shard.rank && e.world == shard.world;
@@ -406,6 +414,9 @@ int novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats) {
     if (!v || !stats) return NOVUM_E_ARG;
     cudaError_t err = cudaStreamSynchronize(v->e.scene->stream);
     if (err != cudaSuccess) return (int)err;
+    nv::BdEngine& e = v->e;
+    for (size_t i = 1; i < e.evUsed; ++i) { float ms = 0; cudaEventElapsedTime(&ms, e.evs[i - 1], e.evs[i]); e.stageMs[e.evCls[i]] += ms; }
+    e.evUsed = 0;
     nv::bdFillStats(v->e, stats);
     stats->photons = (uint64_t)v->e.photonCount;      // photons in the last grid (all ranks)
     return 0;
@@ -451,6 +462,13 @@ int novum_vcm_peer_write(NovumVcmState* v, int enable) {
         for (int r = 0; r < v->e.world; ++r)
             if (r != v->e.rank && !v->e.peerBase[r]) return NOVUM_E_ARG;      // every peer must be attached first
     v->e.peerWrite = enable != 0;
+    return 0;
+}
+
+/* zeroes the session's counters and re-reads the scene's profile flags (novum_set_profile): stage times in novum_vcm_stats */
+int novum_vcm_reset_stats(NovumVcmState* v) {
+    if (!v) return NOVUM_E_ARG;
+    nv::bdResetStats(v->e);
     return 0;
 }
 

@@ -161,6 +161,15 @@ int novum_update_constants(const NovumConstants* c) {
 
 int novum_render_device(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
                         NovumShard shard, uint64_t seed, NovumFloat4* d_colors, NovumRenderStats* stats) {
+    return nv::renderDeviceMis(s, cfg, cam, firstSample, numSample, shard, seed, d_colors, stats, 1);
+}
+
+}  // extern "C"
+
+// novum_render_device with the unidirectional launcher's `useMIS` argument (deviceCode.cu:285-286, :442, :456) exposed: main.cu:565
+// always passes true, the launch shims forward what they are given
+int nv::renderDeviceMis(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                        NovumShard shard, uint64_t seed, NovumFloat4* d_colors, NovumRenderStats* stats, int useMIS) {
     if (!s) return NOVUM_E_NOSCENE;
     if (!cfg || !cam || !d_colors || numSample < 0 || cfg->width <= 0 || cfg->height <= 0) return NOVUM_E_ARG;
     if (shard.world < 1 || shard.rank < 0 || shard.rank >= shard.world) return NOVUM_E_ARG;
@@ -175,13 +184,15 @@ int novum_render_device(NovumScene* s, const NovumRenderConfig* cfg, const Novum
             if (rc) { nv::wfFree(*e); delete e; return rc; }
             s->wfEngine = e; s->wfEngineFree = nv::wfEngineFree;
         }
-        return nv::wfRender(s, *(nv::WfEngine*)s->wfEngine, *cam, cfg->width, cfg->height, cfg->maxDepth, 1,
+        return nv::wfRender(s, *(nv::WfEngine*)s->wfEngine, *cam, cfg->width, cfg->height, cfg->maxDepth, useMIS != 0,
                             integ == NOVUM_NAIVE_UNIDIRECTIONAL, firstSample, numSample, shard, seed, (float4*)d_colors, stats);
     }
     if (integ == NOVUM_VCM || integ == NOVUM_SPPM || integ == NOVUM_BIDIRECTIONAL)
         return nv::vcmRenderDevice(s, cfg, cam, firstSample, numSample, shard, seed, (float4*)d_colors, stats);
     return NOVUM_E_UNSUPPORTED;
 }
+
+extern "C" {
 
 int novum_render(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
                  NovumShard shard, uint64_t seed, NovumFloat4* colors, NovumRenderStats* stats) {

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define NOVUM_ABI_VERSION 4
+#define NOVUM_ABI_VERSION 5
 
 /* error codes (negative; positive return values are cudaError_t) */
 #define NOVUM_OK             0
@@ -42,6 +42,7 @@ extern "C" {
 #define NOVUM_E_NOSCENE    (-3)
 #define NOVUM_E_NOGPU      (-4)
 #define NOVUM_E_UNSUPPORTED (-5)
+#define NOVUM_E_TOODEEP    (-7)   /* the BVH8 built from the scene is deeper than the traversal stack (52 levels): degenerate geometry */
 #define NOVUM_E_TOOBIG     (-6)   /* size beyond a fixed built-in limit (novum_hashgrid_build_static) */
 
 typedef struct NovumFloat4 { float x, y, z, w; } NovumFloat4;   /* 16 B, 16-aligned in device arrays */
@@ -199,6 +200,9 @@ int  novum_scene_info(const NovumScene* s, int* nTri, int* nLights, int* nBvh8No
 /* the step before the path: host time of the config / OBJ front end (main.cu:936-1068 equivalent; 0 unless the scene came
  * from novum_scene_load_config) and CUDA-event time + launch count of the device BVH8 build that replaces main.cu:20-233 */
 int  novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs, int* bvhLaunches);
+/* depth of the BVH8 (levels of 8-wide nodes, root = 1). The traversal stack holds 52 entries, one per level at most: scene creation
+ * fails with NOVUM_E_TOODEEP beyond that instead of losing subtrees silently. Negative = error code. */
+int  novum_scene_bvh_depth(const NovumScene* s);
 /* the OBJ front end's number reader (what sscanf("%lf") / operator>> return in main.cu:936-1068, i.e. strtod): exported so that its
  * fast path can be held to strtod by the CPU tests. *consumed = characters read (0: no number). */
 double novum_parse_double(const char* text, int* consumed);
@@ -244,30 +248,54 @@ int  novum_render_device(NovumScene* s, const NovumRenderConfig* cfg, const Novu
 int  novum_render(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
                   NovumShard shard, uint64_t seed, NovumFloat4* colors, NovumRenderStats* stats);
 
-/* Reference-signature shims (device pointers exactly as main.cu passes them; deviceCode.cuh:8-18).
- * BVH / BVHindices are accepted and ignored. PathVertices / VCMPathVertices / Photons scratch of the
- * reference is accepted as void* and ignored: this core owns its own compact light-vertex cache. */
+/* The reference's launch boundary (deviceCode.cuh:8-18; device pointers exactly as main.cu:565, 641, 677, 786 pass them) + `numGpus`.
+ * Blocking; `colors` receives the SUM over samples (the caller divides, main.cu:862). BVH / BVHindices are accepted and ignored (a BVH8 is
+ * built on the device from `scene` + `vertices`). PathVertices / VCMPathVertices / Photons scratch of the reference is accepted as void* and
+ * ignored: this core owns its own compact light-vertex cache. The strategy toggles are the ones novum_update_constants stored.
+ *
+ * Scene cache: the reference calls one launcher per render, 75 times (main.cu:925-933), re-uploading the scene each time. The boundary
+ * keeps the last scene: a call with the same buffers and the same content (64-bit checksum of positions / triangles / lights / materials /
+ * referenced normals + uvs, computed on the device) reuses BVH8 + engines without allocating; new content rebuilds the scene part and
+ * moves the engines over (novum_launch_cache_stats counts both; novum_launch_cache_clear frees everything).
+ * sceneCenter / sceneRadius / sceneMin are the caller's root-box values and are used as given (merge radius schedule, grid origin).
+ * overlay: read by the progressive save and cleared after it (deviceCode.cu:1931, 3466); the reference writes it only in its debug path
+ * drawing (BDPT_DRAWPATH), which this core lacks: with that constant set the bidirectional launchers return NOVUM_E_UNSUPPORTED.
+ * Progressive output: every 5 s (novum_launch_set_progressive) "render.bmp" is written in the working directory from colors / overlay
+ * (cleanAndFormatImage + saveImageBMP, deviceCode.cu:240-267, 1893-1934, 3447-3468), without stalling the sample loop; no CSV side file.
+ * numGpus <= 1: the current device. numGpus > 1: devices 0..numGpus-1 of this process (peer access required), see DESIGN.md 6. */
 int  novum_launch_unidirectional(int maxDepth, NovumCamera camera, NovumMaterial* materials, NovumFloat4* textures,
                                  NovumBVHnode* BVH, int* BVHindices, NovumVertices* vertices, int vertNum,
                                  NovumTriangle* scene, int triNum, NovumTriangle* lights, int lightNum, int numSample,
-                                 int useMIS, int w, int h, NovumFloat4* colors);
+                                 int useMIS, int w, int h, NovumFloat4* colors, int numGpus);
 int  novum_launch_naive_unidirectional(int maxDepth, NovumCamera camera, NovumMaterial* materials, NovumFloat4* textures,
                                  NovumBVHnode* BVH, int* BVHindices, NovumVertices* vertices, int vertNum,
                                  NovumTriangle* scene, int triNum, NovumTriangle* lights, int lightNum, int numSample,
-                                 int useMIS, int w, int h, NovumFloat4* colors);
+                                 int useMIS, int w, int h, NovumFloat4* colors, int numGpus);
 int  novum_launch_bidirectional(int eyeDepth, int lightDepth, NovumCamera camera, void* eyePath, void* lightPath,
                                  NovumMaterial* materials, NovumFloat4* textures, NovumBVHnode* BVH, int* BVHindices,
                                  NovumVertices* vertices, int vertNum, NovumTriangle* scene, int triNum,
                                  NovumTriangle* lights, int lightNum, int numSample, int w, int h,
                                  NovumFloat4 sceneCenter, float sceneRadius, NovumFloat4* colors, NovumFloat4* overlay,
-                                 int postProcess);
+                                 int postProcess, int numGpus);
 int  novum_launch_vcm(int eyeDepth, int lightDepth, NovumCamera camera, void* lightPath, void* photons,
                                  void* photons_sorted, NovumMaterial* materials, NovumFloat4* textures, NovumBVHnode* BVH,
                                  int* BVHindices, NovumVertices* vertices, int vertNum, NovumTriangle* scene, int triNum,
                                  NovumTriangle* lights, int lightNum, int numSample, int w, int h,
                                  NovumFloat4 sceneCenter, float sceneRadius, NovumFloat4 sceneMin, NovumFloat4* colors,
                                  NovumFloat4* overlay, int postProcess, float mergeRadiusPower,
-                                 float initialRadiusMultiplier);
+                                 float initialRadiusMultiplier, int numGpus);
+typedef struct NovumLaunchCacheStats {
+    uint64_t launches;          /* novum_launch_* calls that ran */
+    uint64_t hits;              /* same buffers, same content: nothing built, nothing allocated */
+    uint64_t rebinds;           /* same content in new allocations: borrowed pointers refreshed, nothing built */
+    uint64_t sceneBuilds;       /* BVH8 + shading data built from the call's buffers */
+    uint64_t enginesMoved;      /* scene rebuilds that kept the integrator engines' buffers */
+    uint64_t progressiveSaves;  /* render.bmp files written by the launchers */
+} NovumLaunchCacheStats;
+int  novum_launch_cache_stats(NovumLaunchCacheStats* out);
+void novum_launch_cache_clear(void);
+/* seconds <= 0 disables the progressive save; path NULL keeps the current one ("render.bmp") */
+int  novum_launch_set_progressive(float seconds, const char* path);
 
 /* ---- photon hash grid (deviceCode.cu:3067-3198; integratorUtilities.cuh:382-412) -------- */
 typedef struct NovumHashGrid NovumHashGrid;
@@ -322,6 +350,7 @@ int  novum_vcm_cache_buffer(NovumVcmState* v, void** d_cacheBase, uint64_t* slab
 int  novum_vcm_build_grid(NovumVcmState* v, int iter);
 int  novum_vcm_eye_pass(NovumVcmState* v, int iter, NovumFloat4* d_colors);
 int  novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats);
+int  novum_vcm_reset_stats(NovumVcmState* v);     /* zero the counters; picks up novum_set_profile's flags for the stage timers */
 /* the CUDA stream (cudaStream_t) the passes are enqueued on, so the caller can order its collective after the light pass */
 int  novum_vcm_stream(NovumVcmState* v, void** stream);
 /* Peer-write exchange (the fused form of "light pass -> all-gather"): every rank exports its slab buffer as a 64-byte CUDA

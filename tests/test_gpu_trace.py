@@ -218,3 +218,34 @@ def test_full_size_closest_and_any_hit_agree(full_dragon, rng):
     assert np.all((skipped[:, :3] == 0.0) | (skipped[:, :3] == 1.0))
     assert np.all(skipped[~h, :3] == 1.0)
     assert (skipped[h, 0] == 1.0).mean() > 0.5              # most rays meet nothing else within 1e-4 t of the hit
+
+
+def test_degenerate_scene_of_coincident_triangles_stays_inside_the_stack_bound(rng):
+    """10^5 coincident triangles (one Morton code for all of them) + a floor: the LBVH splits equal codes by index, so the BVH8 stays
+    shallow; the depth the builder reports is what bounds the traversal stack (a deeper tree is refused with NOVUM_E_TOODEEP instead of
+    dropping subtrees), and the hit is still the lowest triangle id on bit-equal t."""
+    from cudapathtracer_b200.binding import TRI_DTYPE
+    n = 100_000
+    pos = np.array([[0, 0, 0, 0], [1, 0, 0, 0], [0, 1, 0, 0], [-5, -5, -1, 0], [5, -5, -1, 0], [5, 5, -1, 0], [-5, 5, -1, 0]], np.float32)
+    nrm = np.array([[0, 0, 1, 0]], np.float32)
+    uv = np.zeros((1, 2), np.float32)
+    tris = np.zeros(n + 2, TRI_DTYPE)
+    tris["aInd"][:n], tris["bInd"][:n], tris["cInd"][:n] = 0, 1, 2
+    tris["aInd"][n:], tris["bInd"][n:], tris["cInd"][n:] = [3, 3], [4, 5], [5, 6]
+    tris["materialID"] = 2
+    tris["lightInd"] = -51
+    tris["triInd"] = np.arange(n + 2)
+    s = nb.Scene.from_arrays(pos, nrm, uv, tris, nb.material_table())
+    try:
+        depth = s.info()["bvh8_depth"]
+        assert 1 <= depth <= 52, depth
+        rays = np.zeros((64, 8), np.float32)
+        rays[:, 0:2] = rng.random((64, 2)).astype(np.float32) * 0.4 + 0.05      # above the stack of coincident triangles
+        rays[:, 2] = 1.0
+        rays[:, 6] = -1.0
+        rays[32:, 0] += 2.0                                                      # beside it: only the floor
+        hits = s.trace_closest(rays)
+        assert (hits["tri"][:32] == 0).all() and np.allclose(hits["t"][:32], 1.0)
+        assert (hits["tri"][32:] >= n).all() and np.allclose(hits["t"][32:], 2.0)
+    finally:
+        s.close()
