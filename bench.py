@@ -37,7 +37,7 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 UNI, BDPT, NAIVE, VCM, SPPM = 0, 1, 2, 3, 4
 WORKLOADS = {
     "dragon_nee": dict(gen="dragon", integ=UNI, w=1920, h=1080, spp=32, desc="configs[1]: dragon stand-in (~871k tris, glass) 1920x1080 NEE+MIS"),
-    "rainbow_vcm": dict(gen="rainbow", integ=VCM, w=3840, h=2160, spp=1, desc="configs[4]: rainbow dragon stand-in (~871k tris) 3840x2160 VCM, eye 16 / light 10"),
+    "rainbow_vcm": dict(gen="rainbow", integ=VCM, w=3840, h=2160, spp=4, desc="configs[4]: rainbow dragon stand-in (~871k tris) 3840x2160 VCM, eye 16 / light 10"),
     "water_bdpt": dict(gen="water", integ=BDPT, w=1920, h=1080, spp=2, desc="configs[2]: water caustic stand-in 1920x1080 BDPT, all strategies + MIS"),
     "water_sppm": dict(gen="water_sppm", integ=SPPM, w=1024, h=1024, spp=4, desc="configs[3]: water caustic stand-in SPPM, 1024x1024 light paths per iteration"),
     "cornell": dict(gen="cornell", integ=UNI, w=512, h=512, spp=64, desc="configs[0]: Cornell box 512x512 NEE+MIS"),
@@ -86,13 +86,14 @@ class ClockSampler:
 
 
 def scene_dir_for(workload, detail, rank, dist):
-    """Rank 0 generates the stand-in scene once per box; other ranks wait for it."""
+    """Rank 0 generates the stand-in scene once per box with the standalone command-line tool (a subprocess: neither arm has to load
+    the product library for this); other ranks wait for it."""
     gen = WORKLOADS[workload]["gen"]
     d = os.path.join(tempfile.gettempdir(), f"novum_bench_{gen}_{detail}")
-    import cudapathtracer_b200 as nb
     marker = os.path.join(d, ".done")
     if rank == 0 and not os.path.exists(marker):
-        nb.make_scene(gen, d, detail)
+        tool = os.path.join(REPO, "cudapathtracer_b200", "novum")
+        subprocess.check_call([tool, "--make-scene", gen, "--out", d, "--detail", str(detail)], stdout=subprocess.DEVNULL)
         open(marker, "w").write("ok")
     if dist is not None:
         dist.barrier()
@@ -102,8 +103,8 @@ def scene_dir_for(workload, detail, rank, dist):
 def cpu_oracle_baseline(sdir, workload, target_s=12.0):
     """The CPU restatement of the reference's path (oracle/, kind "port") on the host cores, on a bounded sample: the same
     scene and camera at reduced resolution through the oracle's NEE+MIS walk (closest-hit + shadow rays of the reference's
-    BVHSceneIntersect / BVHShadowRay restatement), sized for ~10-20 s. For the bidirectional workloads the ray mix differs
-    (no CPU VCM exists); the figure is the host's Mrays/s on this scene's geometry."""
+    BVHSceneIntersect / BVHShadowRay restatement), sized for ~10-20 s. NOT the headline's ray mix for the bidirectional workloads
+    (no CPU VCM exists, and the reference has no CPU path at all): the figure is the host's Mrays/s on this scene's geometry."""
     import cudapathtracer_b200 as nb
     from oracle.oracle_binding import OracleScene
     scene = nb.Scene.from_config(os.path.join(sdir, "configs", "config.rendertron"))
@@ -126,12 +127,48 @@ def cpu_oracle_baseline(sdir, workload, target_s=12.0):
         img, counts = ora.render_unidirectional(bytes(cam), sw, sh, cfg.maxDepth, 1, spp)
         dt = time.time() - t0
     rays = float(counts[0] + counts[1])
+    mix = "" if wl["integ"] == UNI else " - a DIFFERENT ray mix from this workload's bidirectional integrator, which has no CPU form"
     return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": f"{sw}x{sh} px x {spp} spp of the same scene/camera through the oracle's NEE+MIS walk, OpenMP on all host cores ({dt:.1f} s)",
+            "sample": f"{sw}x{sh} px x {spp} spp of the same scene/camera through the oracle's NEE+MIS walk, OpenMP on all host cores ({dt:.1f} s){mix}",
             "paths_per_s": sw * sh * spp / dt, "rays_per_path": rays / (sw * sh * spp)}
 
 
+def kernel_counters():
+    """Per-kernel figures read off committed ncu --set full captures of the SHIPPED kernels (profiles/r2_kernel_counters.json, written by
+    tools/profile.sh + tools/ncu_extract.py): dram bytes per launch, warp instructions per launch. None when the file is absent."""
+    p = os.path.join(REPO, "profiles", "r2_kernel_counters.json")
+    return json.load(open(p)) if os.path.exists(p) else None
+
+
+def block_means(img, k):
+    h, w, c = img.shape
+    return img[:h - h % k, :w - w % k].reshape(h // k, k, w // k, k, c).mean(axis=(1, 3))
+
+
+def relmse_vs_reference(scene, nb):
+    """The headline scene against a frame of the REFERENCE: tests/golden/rainbow1080_vcm_blocks.npz holds the 8x8-block means of novum_ref's
+    own 1920x1080, 64-iteration VCM render of the same scene files (tests/golden/make_golden_materials.py). Ours: same resolution and
+    iteration count through novum_render."""
+    import numpy as np
+    p = os.path.join(REPO, "tests", "golden", "rainbow1080_vcm_blocks.npz")
+    if not os.path.exists(p):
+        return None
+    z = np.load(p)
+    cfg = nb.RenderConfig.from_buffer_copy(bytes(scene.cfg))
+    cfg.width, cfg.height, cfg.integrator = int(z["w"]), int(z["h"]), VCM
+    cam = nb.camera_make(cfg)
+    spp = int(z["spp"])
+    img, _ = scene.render(cfg, cam, 0, spp)
+    img = img[..., :3] / spp
+    b = block_means(img, 8)
+    ref = z["blocks"]
+    return {"relmse_8x8_blocks": float(np.mean((b - ref) ** 2 / (ref ** 2 + 1e-2))), "mean_ratio": float(img.mean() / float(z["mean"])),
+            "mean_ours": float(img.mean()), "mean_reference": float(z["mean"]), "width": cfg.width, "height": cfg.height, "iterations": spp,
+            "fixture": "tests/golden/rainbow1080_vcm_blocks.npz (novum_ref, same scene files)", "test_bar": "mean within 3 %, block relMSE <= 0.05 (tests/test_gpu_materials.py)"}
+
+
 def run_ours(args):
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")      # lanes x ranks never alias a hardware queue
     import numpy as np
     import torch
     import cudapathtracer_b200 as nb
@@ -159,29 +196,47 @@ def run_ours(args):
     w, h, integ = wl["w"], wl["h"], wl["integ"]
     cfg.width, cfg.height, cfg.integrator = w, h, integ
     bidir = integ in (BDPT, VCM, SPPM)
-    tiles = bidir and args.sharding == "tiles"
+    sharding = args.sharding or ("tiles" if (bidir and world > 1) else "striped")
+    tiles = bidir and sharding == "tiles"
     cam = nb.camera_make(cfg)
     info = scene.info()
     S = args.spp_per_step or wl["spp"]
     colors = torch.zeros((h, w, 4), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > L2 (126 MB)
-    tiler = nd.TileRenderer(scene, cfg, cam, dist, exchange=args.exchange) if tiles else None
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tiler = None
+    if tiles:
+        tiler = (nd.TileRenderer(scene, cfg, cam, dist, lanes=args.lanes) if args.exchange == "p2p"
+                 else nd.PhaseTileRenderer(scene, cfg, cam, dist, exchange="nccl"))
+    pinned = torch.empty((h, w, 4), dtype=torch.float32, pin_memory=True)     # the caller's page-locked frame, reused every step
 
-    def step(i, profile=0):
-        """One step: S passes per GPU. Returns (stats, device ms)."""
+    # Which iterations a step renders:
+    #   tiles   (strong scaling): step i = iterations [i*S, (i+1)*S) of the full frame, all ranks together (rows sharded, photons exchanged)
+    #   striped (weak scaling)  : step i = the SAME iterations [i*S, (i+1)*S) on every rank, rank r with seed base + r - equal work per GPU
+    #                             whatever N is (the VCM merge radius shrinks with the iteration index, so striding the indices over
+    #                             ranks would make an N-GPU step cheaper than a 1-GPU step); the frames are N independent estimates, summed
+    def step(i, profile=0, to_host=False, do_flush=True):
+        """One step. Returns (stats, device ms of the render)."""
         scene.set_profile(profile)
-        flush.fill_(i & 0xff)          # evict L2 between steps (the working set of a step, >0.4 GB, also exceeds L2)
-        torch.cuda.synchronize()
-        if tiles:                      # all ranks work on the same S*world iterations, each on its pixel rows
-            ext = tiler.ext_stream
-            ev0.record(ext)
-            st = tiler.render(i * S * world, S * world, colors)
-            ev1.record(ext)
+        if do_flush:
+            flush.fill_(i & 0xff)      # evict L2 between steps (the working set of a step, >0.4 GB, also exceeds L2)
             torch.cuda.synchronize()
-            return st, ev0.elapsed_time(ev1)
-        st = scene.render_device(cfg, cam, i * S * world, S * world, colors.data_ptr(), rank=rank, world=world)
-        return st, st.deviceMs          # CUDA events on the library's own stream around the whole call
+        if to_host and world == 1 and not tiles:
+            _, st = scene.render(cfg, cam, i * S, S, out=pinned.numpy())      # novum_render: renders, copies w*h*16 B to the caller's buffer
+            return st, st.deviceMs
+        if to_host:
+            colors.zero_()
+        if tiles:
+            st = tiler.render(i * S, S, colors)
+            ms = st.deviceMs
+        else:
+            st = scene.render_device(cfg, cam, i * S, S, colors.data_ptr(), seed=103033 + rank)
+            ms = st.deviceMs          # CUDA events on the library's own streams around the whole call
+        if to_host:
+            nd.reduce_frames(colors, dist, 0)
+            if rank == 0:
+                pinned.copy_(colors)
+            torch.cuda.synchronize()
+        return st, ms
 
     for i in range(args.warmup):
         step(i)
@@ -194,154 +249,180 @@ def run_ours(args):
     wall0 = time.time()
     dev_ms, rays, paths, launches, stage_ms, closest, photons = 0.0, 0, 0, 0, [0.0] * 4, 0, 0
     merge_cand, merge_acc, merge_q = 0, 0, 0
-    before = tiler.session.stats() if tiles else None       # the session's counters are cumulative
     for i in range(args.steps):
-        st, ms = step(args.warmup + i, profile=0 if tiles else 1)
+        st, ms = step(args.warmup + i, profile=1)
         dev_ms += ms
         photons = st.photons
-        if not tiles:
-            rays += st.closestRays + st.shadowRays; closest += st.closestRays; paths += st.paths; launches += st.kernelLaunches
-            merge_cand += st.mergeCandidates; merge_acc += st.mergeAccepted; merge_q += st.mergeQueries
-            for k in range(4):
-                stage_ms[k] += st.stageMs[k]
-    if tiles:
-        rays = (st.closestRays + st.shadowRays) - (before.closestRays + before.shadowRays)
-        closest = st.closestRays - before.closestRays; paths = st.paths - before.paths; launches = st.kernelLaunches - before.kernelLaunches
+        rays += st.closestRays + st.shadowRays; closest += st.closestRays; paths += st.paths; launches += st.kernelLaunches
+        merge_cand += st.mergeCandidates; merge_acc += st.mergeAccepted; merge_q += st.mergeQueries
+        for k in range(4):
+            stage_ms[k] += st.stageMs[k]
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     wall = time.time() - wall0
-    clk = clocks.stop() if rank == 0 else None
-    tot = torch.tensor([float(rays), float(paths), float(launches), float(closest)], dtype=torch.float64, device=dev)
-    mx = torch.tensor([dev_ms, wall * 1e3, stage_ms[0]], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(rays), float(paths), float(launches), float(closest), float(merge_cand), float(merge_acc), float(merge_q)], dtype=torch.float64, device=dev)
+    mx = torch.tensor([dev_ms, wall * 1e3], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    tot_rays, tot_paths, tot_launch, tot_closest = [float(x) for x in tot.tolist()]
-    max_dev_ms, max_wall_ms, max_extend_ms = [float(x) for x in mx.tolist()]
+    tot_rays, tot_paths, tot_launch, tot_closest, tot_cand, tot_acc, tot_q = [float(x) for x in tot.tolist()]
+    max_dev_ms, max_wall_ms = [float(x) for x in mx.tolist()]
 
-    # ---- end-to-end through the host-facing call: render + D2H of the framebuffer (+ NCCL reduce for N > 1) ----
-    e2e_rays = 0
-    host_img = None
-    pinned = torch.empty((h, w, 4), dtype=torch.float32, pin_memory=True)     # the caller's page-locked frame, reused every step
-    scene.set_profile(0)
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    e0 = time.time()
-    base_i = args.warmup + args.steps
+    # ---- end to end: the SAME steps (iteration indices, L2 flush before each) through the host-facing call: render, (N > 1: NCCL sum of
+    # the frames,) framebuffer copied to the caller's page-locked buffer; wall clock around each step, the flush outside it ----
+    e2e_rays, e2e_s = 0, 0.0
     for i in range(args.steps):
-        if world == 1 and not tiles:
-            host_img, st = scene.render(cfg, cam, (base_i + i) * S, S, out=pinned.numpy())      # renders, copies w*h*16 B to host
-            e2e_rays += st.closestRays + st.shadowRays
-        else:
-            colors.zero_()
-            if tiles:
-                before = tiler.session.stats()
-                st = tiler.render((base_i + i) * S * world, S * world, colors)
-                e2e_rays += (st.closestRays + st.shadowRays) - (before.closestRays + before.shadowRays)
-            else:
-                st = scene.render_device(cfg, cam, (base_i + i) * S * world, S * world, colors.data_ptr(), rank=rank, world=world)
-                e2e_rays += st.closestRays + st.shadowRays
-            nd.reduce_frames(colors, dist, 0)
-            if rank == 0:
-                pinned.copy_(colors); host_img = pinned.numpy()
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    e2e_wall = time.time() - e0
+        flush.fill_((args.warmup + i) & 0xff)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        t0 = time.time()
+        st, _ = step(args.warmup + i, profile=0, to_host=True, do_flush=False)
+        if dist is not None:
+            dist.barrier()
+        e2e_s += time.time() - t0
+        e2e_rays += st.closestRays + st.shadowRays
+    clk = clocks.stop() if rank == 0 else None
+    host_img = pinned.numpy() if rank == 0 else None
     e2e_t = torch.tensor([float(e2e_rays)], dtype=torch.float64, device=dev)
+    e2e_mx = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.SUM)
+        dist.all_reduce(e2e_mx, op=dist.ReduceOp.MAX)
 
-    # ---- roofline of the dominant kernel class (by live CUDA-event stage time) ----
-    # closest-hit traversal (wfExtend / bdExtend): per ray 32 B ray + 16 B hit + 80 B x nodes + 48 B x triangles;
-    # photon merge (bdMergeLambert / bdMerge): per query 80 B record + 27 x 8 B cell ranges + 16 B pixel RMW, 16 B per photon
-    # scanned (position word) + 16 B per photon inside the radius (second word) — SURVEY 8d's "27 x 8 B + record x scanned".
-    roof = None
-    if not tiles:
-        st, _ = step(10_000, profile=3)       # one counted step (slower kernel, not timed): nodes / triangles per ray
-        vn = st.bvhNodeVisits / max(1, st.closestRays); vt = st.triTests / max(1, st.closestRays)
-        bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt
-        peak, peak_src = peaks()
-        names = ({"extend": 0, "step+grid": 1, "resolve": 2, "merge": 3} if bidir else {"extend": 0, "shade": 1, "shadow": 2, "other": 3})
-        ext = {"kernel": "bdExtend (BVH8 closest hit)" if bidir else "wfExtend (BVH8 closest hit)",
-               "achieved": (closest * bytes_per_ray) / (stage_ms[0] * 1e-3) / 1e9 if stage_ms[0] > 0 else 0.0,
-               "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
-               "closest_rays_per_s": closest / (stage_ms[0] * 1e-3) if stage_ms[0] > 0 else None,
-               "ms_share": stage_ms[0] / dev_ms if dev_ms else None}
-        dom = ext
-        if bidir and stage_ms[3] > stage_ms[0] and merge_q > 0:
-            mbytes = merge_q * (80 + 27 * 8 + 16) + 16 * merge_cand + 16 * merge_acc
-            dom = {"kernel": "bdMergeLambert + bdMerge (photon gather over 27 hash-grid cells)",
-                   "achieved": mbytes / (stage_ms[3] * 1e-3) / 1e9, "bytes_per_query": mbytes / merge_q,
-                   "photons_scanned_per_query": merge_cand / merge_q, "photons_merged_per_query": merge_acc / merge_q,
-                   "photons_scanned_per_s": merge_cand / (stage_ms[3] * 1e-3), "ms_share": stage_ms[3] / dev_ms if dev_ms else None,
-                   "note": "every photon record is re-read by ~10^3 queries, so these bytes are served by L1/L2, not HBM: achieved/peak can "
-                           "exceed 1; the kernel is instruction-issue bound (profiles/)"}
-        # dram bytes per launch of the dominant kernel from the committed ncu --set full captures (profiles/README.md), default sizes only
-        traffic = None
-        if args.detail == 100 and not args.spp_per_step:
-            if dom is not ext and args.workload == "rainbow_vcm":
-                traffic = 1.0e9          # bdMergeLambert, primary-hit queue launch: the photon set read once (r1_bdMergeLambert_g4.txt)
-            elif dom is ext and args.workload == "dragon_nee":
-                traffic = 4.3e8          # wfExtend steady-state launch: 325-370 MB read + 85-89 MB written (r1_wfExtend_streaming.txt)
-        roof = {"bound": "hbm", **dom, "peak": peak, "unit": "GB/s", "frac": dom["achieved"] / peak, "traffic": traffic, "peak_source": peak_src,
-                "stage_ms": {k: stage_ms[v] for k, v in names.items()}}
-        if dom is not ext:
-            roof["extend"] = {**ext, "frac": ext["achieved"] / peak}
+    # ---- roofline ----
+    # Top level = the closest-hit traversal (wfExtend / bdExtend), the kernel north_star's memory-bound roofline is about: per ray 32 B ray
+    # + 16 B hit + 80 B x nodes + 48 B x triangles visited, nodes / triangles per ray counted live by a counted step. With
+    # several lanes in flight the stages of different iterations overlap, so a stage's time is its share of the summed stage times
+    # applied to the step's device time.
+    st, _ = step(10_000, profile=3)       # one counted step (slower kernel, not timed): nodes / triangles per ray
+    vn = st.bvhNodeVisits / max(1, st.closestRays); vt = st.triTests / max(1, st.closestRays)
+    bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt
+    peak, peak_src = peaks()
+    names = ({"extend": 0, "step+grid": 1, "resolve": 2, "merge": 3} if bidir else {"extend": 0, "shade": 1, "shadow": 2, "other": 3})
+    ssum = sum(stage_ms) or 1.0
+    eff_ms = [dev_ms * x / ssum for x in stage_ms]          # this rank's wall share of each stage
+    kc = kernel_counters() or {}
+    ext_name = "bdExtend" if bidir else "wfExtend"
+    ext_kc = kc.get(args.workload, {}).get(ext_name)
+    roof = {"bound": "hbm", "kernel": f"{ext_name} (BVH8 closest hit)",
+            "achieved": (closest * bytes_per_ray) / (eff_ms[0] * 1e-3) / 1e9 if eff_ms[0] > 0 else 0.0,
+            "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+            "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
+            "closest_rays_per_s": closest / (eff_ms[0] * 1e-3) if eff_ms[0] > 0 else None, "ms_share": stage_ms[0] / ssum,
+            "traffic": ext_kc["dram_bytes_per_launch"] if ext_kc else None,
+            "traffic_source": ext_kc["source"] if ext_kc else None,
+            "stage_ms_share": {k: stage_ms[v] / ssum for k, v in names.items()},
+            "note": "DRAM traffic is far below the algorithmic bytes (the BVH8 is L2-resident): the kernel is bound by dependent-load latency under "
+                    "SIMT divergence, the HBM fraction is the figure north_star asks for, not its limiter (profiles/README.md)"}
+    roof["frac"] = roof["achieved"] / peak
+    if bidir and merge_q > 0 and eff_ms[3] > 0:
+        # photon merge: L1/L2-resident photon streams (every record is re-read by ~10^3 queries), so HBM is not its bound; what it does per
+        # second is (vertex, photon) pair tests, at a fixed number of warp instructions per 32 pairs (ncu of the shipped kernel)
+        mkc = kc.get(args.workload, {}).get("bdMergeLambert")
+        sm_hz = (clk["sm_mhz"] if clk and clk.get("sm_mhz") else 1965) * 1e6
+        issue_peak = 148 * 4 * sm_hz                                         # warp instructions per second
+        pairs_s = merge_cand / (eff_ms[3] * 1e-3)
+        m = {"bound": "issue", "kernel": "bdMergeLambert + bdMerge (photon gather over 27 hash-grid cells)", "pairs_per_s": pairs_s,
+             "photons_scanned_per_query": merge_cand / merge_q, "photons_merged_per_query": merge_acc / merge_q,
+             "scanned_per_merged": merge_cand / max(1, merge_acc), "ms_share": stage_ms[3] / ssum,
+             "issue_peak_warp_inst_per_s": issue_peak}
+        if mkc:
+            ipp = mkc["warp_inst_per_launch"] / max(1.0, mkc["pairs_per_launch"]) * 32.0
+            m.update({"warp_inst_per_32_pairs": ipp, "achieved_warp_inst_per_s": pairs_s / 32.0 * ipp, "frac": pairs_s / 32.0 * ipp / issue_peak,
+                      "traffic": mkc["dram_bytes_per_launch"], "source": mkc["source"]})
+        roof["merge"] = m
 
     if rank == 0:
+        n_iter = args.steps * S * (1 if tiles else world)
         line = {
             "metric": "Mrays/s", "value": tot_rays / (max_dev_ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": max_dev_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong" if tiles else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "scene": args.workload, "tris": info["tris"], "bvh8_nodes": info["bvh8_nodes"],
-                       "width": w, "height": h, "passes_per_step_per_gpu": S, "max_depth": cfg.maxDepth,
+                       "width": w, "height": h, "passes_per_step": S, "max_depth": cfg.maxDepth,
                        "eye_depth": cfg.bdptEyeDepth, "light_depth": cfg.bdptLightDepth,
-                       "sharding": (f"pixel rows striped over ranks, photons exchanged every iteration ({tiler.exchange_mode}), frames sum-reduced at the end"
-                                    if tiles else "sample passes / iterations striped over ranks, frames sum-reduced (NCCL) at the end"),
-                       "l2": "256 MB flush between steps; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
+                       "iterations_timed": f"{args.warmup * S}..{(args.warmup + args.steps) * S - 1}",
+                       "sharding": (f"tiles: pixel rows y % N == rank, {getattr(tiler, 'lanes', 1)} iterations in flight per rank, photons stored into the peers' slabs "
+                                    f"inside the light pass ({tiler.exchange_mode}), device-side rendezvous, frames sum-reduced (NCCL) at the end"
+                                    if tiles else
+                                    ("striped: every rank renders the same iteration indices with its own seed (equal work per GPU), frames sum-reduced (NCCL) at the end"
+                                     if world > 1 else f"one GPU; NOVUM_LANES={os.environ.get('NOVUM_LANES', '3')} iterations in flight")),
+                       "l2": "256 MB flush before every step; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
                        "scene_load_s": round(load_s, 3), "scene_parse_s": round(info["parse_ms"] * 1e-3, 3), "bvh8_build_ms": round(info["bvh8_build_ms"], 3),
-                       "bvh8_build_launches": info["bvh8_build_launches"],
-                       "scene_load_note": "first load in this process: bvh8_build_ms includes CUDA module loading and the build's cudaMallocs; repeated loads: parse 0.06 s (16 host threads) + build 7 ms for 871k triangles (profiles/r1_scene_load_breakdown.txt)"},
+                       "bvh8_build_launches": info["bvh8_build_launches"]},
+            "ms_per_pass": max_dev_ms / max(1, args.steps * S),
             "paths_per_s": tot_paths / (max_dev_ms * 1e-3), "rays_per_path": tot_rays / max(1.0, tot_paths),
             "wall_ms_per_step": max_wall_ms / args.steps,
-            "e2e": {"value": float(e2e_t.item()) / e2e_wall / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 112 + 200,
-                    "d2h_bytes_per_step": w * h * 16,
-                    "note": "novum_render: camera/config in, render, framebuffer (w*h float4) copied to page-locked host memory every step"},
+            "e2e": {"value": float(e2e_t.item()) / float(e2e_mx.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 112 + 200,
+                    "d2h_bytes_per_step": w * h * 16, "ms_per_step": float(e2e_mx.item()) * 1e3 / args.steps,
+                    "note": "the same steps (same iteration indices, L2 flushed before each) through the host-facing call: camera/config in, render, "
+                            + ("NCCL sum of the ranks' frames, " if world > 1 else "")
+                            + "framebuffer (w*h float4) copied to page-locked host memory every step; wall clock"},
             "gpu_launches": int(tot_launch),
             "clocks": clk,
+            "roofline": roof,
         }
-        if roof:
-            line["roofline"] = roof
         if bidir:
-            line["photons_per_iteration"] = int(photons) if tiles else int(photons // max(1, S))
-            line["merge"] = {"queries_per_step": merge_q // max(1, args.steps), "candidates_per_step": merge_cand // max(1, args.steps),
-                             "merged_per_step": merge_acc // max(1, args.steps)}
+            line["photons_per_iteration"] = int(photons // max(1, S)) * (world if tiles else 1)
+            line["merge"] = {"queries_per_step": int(tot_q) // max(1, args.steps), "candidates_per_step": int(tot_cand) // max(1, args.steps),
+                             "merged_per_step": int(tot_acc) // max(1, args.steps)}
         if tiles:
             line["exchange_bytes_per_iteration_per_gpu"] = int(tiler.last_exchange_bytes)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_oracle_baseline(sdir, args.workload)
         if host_img is not None:
-            line["image_mean"] = float(host_img[..., :3].mean() / max(1, S * world))
+            line["image_mean"] = float(host_img[..., :3].mean() / max(1, S * (1 if tiles else world)))
+        if args.workload == "rainbow_vcm" and args.detail == 100 and not args.no_relmse:
+            line["relmse_vs_reference"] = relmse_vs_reference(scene, nb)
+        if world == 1 and args.workload == "rainbow_vcm" and not args.no_secondary:
+            line["secondary"] = secondary_dragon_nee(args, nb)
         print(json.dumps(line))
     if tiler:
         tiler.close()
     scene.close()
     if dist is not None:
+        dist.barrier()
         dist.destroy_process_group()
 
 
+def secondary_dragon_nee(args, nb):
+    """north_star's other stated target (>= 5x the reference build's Mrays/s on the dragon NEE scene, configs[1]) measured in the same run:
+    2 timed steps of 32 spp at 1920x1080 after 1 warm-up step; the reference arm prints the matching figure under the same key."""
+    wl = WORKLOADS["dragon_nee"]
+    sdir = scene_dir_for("dragon_nee", args.detail, 0, None)
+    scene = nb.Scene.from_config(os.path.join(sdir, "configs", "config.rendertron"))
+    try:
+        cfg = scene.cfg
+        cfg.width, cfg.height, cfg.integrator = wl["w"], wl["h"], wl["integ"]
+        cam = nb.camera_make(cfg)
+        import torch
+        colors = torch.zeros((wl["h"], wl["w"], 4), dtype=torch.float32, device="cuda")
+        S = wl["spp"]
+        scene.render_device(cfg, cam, 0, S, colors.data_ptr())
+        ms, rays = 0.0, 0
+        for i in (1, 2):
+            st = scene.render_device(cfg, cam, i * S, S, colors.data_ptr())
+            ms += st.deviceMs; rays += st.closestRays + st.shadowRays
+        return {"workload": wl["desc"], "metric": "Mrays/s", "value": rays / (ms * 1e-3) / 1e6, "ms_per_step": ms / 2, "passes_per_step": S,
+                "steps": 2, "warmup": 1, "paths_per_s": wl["w"] * wl["h"] * S * 2 / (ms * 1e-3)}
+    finally:
+        scene.close()
+
+
 def run_reference(args):
-    """The reference's own CUDA build (unmodified sources, oracle/_ref/novum_ref) on ONE B200 of this box: it is GPU-only,
-    so this is the baseline north_star names. Its rays per pass come from the counting build of the same sources
-    (oracle/_ref/novum_ref_count, run once on one pass, never timed)."""
+    """The reference's own CUDA build (unmodified sources, oracle/_ref/novum_ref) on ONE B200 of this box: it is GPU-only, so this is the
+    baseline north_star names. Nothing of the product is imported here: the scene comes from the standalone generator, the work runs in
+    novum_ref subprocesses. Its rays per pass come from the counting build of the same sources (novum_ref_count, one pass, never timed).
+    `value` is the STOCK code path, whose BDPT / VCM launchers stop every >= 5 s to write render.bmp + an 8.3 M-value CSV
+    (deviceCode.cu:1893-1934, 3447-3468); `nosave` is the same sources with that switch read as false (novum_ref_nosave)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     ref = os.path.join(REPO, "oracle", "_ref", "novum_ref")
     refc = os.path.join(REPO, "oracle", "_ref", "novum_ref_count")
+    refn = os.path.join(REPO, "oracle", "_ref", "novum_ref_nosave")
     wl = WORKLOADS[args.workload]
     sdir = scene_dir_for(args.workload, args.detail, 0, None)
     w, h = wl["w"], wl["h"]
@@ -355,21 +436,28 @@ def run_reference(args):
         print(json.dumps(line))
         return
 
-    def run(binary, spp):
-        out = subprocess.check_output([binary, "render", sdir, "--spp", str(spp), "--out", os.path.join(tempfile.gettempdir(), "ref.raw")],
+    def run(binary, scene_dir, spp):
+        out = subprocess.check_output([binary, "render", scene_dir, "--spp", str(spp), "--out", os.path.join(tempfile.gettempdir(), "ref.raw")],
                                       stderr=subprocess.STDOUT).decode()
         return json.loads(re.search(r"NOVUM_REF_JSON (\{.*\})", out).group(1))
 
-    a = run(ref, max(1, args.warmup * S))                     # includes curand_init, allocations: subtracted out below
-    b = run(ref, (args.warmup + args.steps) * S)
-    ms = b["launch_ms"] - a["launch_ms"]
     bidir = wl["integ"] in (BDPT, VCM, SPPM)
-    passes = args.steps * S
+    # bounded sample: the timed window is passes [W*S, W*S + P) with P = min(K*S, cap): the metric is a rate, and a 4K VCM pass costs
+    # the reference ~2.6 s
+    cap = {"rainbow_vcm": 24, "water_bdpt": 24, "water_sppm": 48, "dragon_nee": 64, "cornell": 256}[args.workload]
+    passes = max(1, min(args.steps * S, cap))
+    wpass = max(1, args.warmup * S)
+
+    def timed(binary):
+        a = run(binary, sdir, wpass)                          # includes curand_init, allocations: subtracted out below
+        b = run(binary, sdir, wpass + passes)
+        return b["launch_ms"] - a["launch_ms"], b
+
+    ms, b = timed(ref)
     paths = w * h * passes * (2 if bidir else 1)
-    rays_per_pass, how = None, None
     if os.path.exists(refc):
         nc = 1 if bidir else min(4, S)
-        c = run(refc, nc)
+        c = run(refc, sdir, nc)
         rays_per_pass = (c["closest_rays"] + c["shadow_rays"]) / nc
         how = f"device counters of the counting build of the same sources over {nc} pass(es)"
     else:
@@ -379,15 +467,33 @@ def run_reference(args):
     rays = rays_per_pass * passes
     val = rays / (ms * 1e-3) / 1e6
     line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["desc"], "scene": args.workload, "tris": b["tris"], "width": w, "height": h, "passes_per_step_per_gpu": S,
-                       "timing": "launch_* CUDA-event time at (W+K)*S passes minus at W*S passes (drops curand_init + allocation)",
+            "ms_per_step": ms / passes * S, "ms_per_pass": ms / passes, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "scene": args.workload, "tris": b["tris"], "width": w, "height": h, "passes_per_step": S,
+                       "passes_timed": f"{wpass}..{wpass + passes - 1}",
+                       "timing": "launch_* CUDA-event time at W*S + P passes minus at W*S passes (drops curand_init + allocation); stock code path",
                        "rays": how},
             "paths_per_s": paths / (ms * 1e-3), "rays_per_path": rays / paths,
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference",
-                             "sample": f"whole workload: {args.steps} steps x {S} passes at {w}x{h} on one B200 (the reference has no CPU path)"},
+                             "sample": f"{passes} passes at {w}x{h} on one B200 (the reference has no CPU path); bounded sample of the {args.steps} x {S} passes of the other arm"},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "reference_bvh_build_s": b["bvh_build_s"]}
+    if bidir and os.path.exists(refn):
+        ms_n, _ = timed(refn)
+        line["nosave"] = {"value": rays / (ms_n * 1e-3) / 1e6, "ms_per_pass": ms_n / passes,
+                          "note": "same sources with DO_PROGRESSIVERENDER (util.cuh:33) read as false inside deviceCode.cu: no 5-second render.bmp / renderCSV.csv "
+                                  "dump inside the timed launch; `value` above is the stock path, which the ratio is taken against"}
+    if args.workload == "rainbow_vcm" and not args.no_secondary:
+        wl2 = WORKLOADS["dragon_nee"]
+        sdir2 = scene_dir_for("dragon_nee", args.detail, 0, None)
+        S2 = wl2["spp"]
+        a2, b2 = run(ref, sdir2, S2), run(ref, sdir2, 3 * S2)
+        ms2 = b2["launch_ms"] - a2["launch_ms"]
+        sec = {"workload": wl2["desc"], "ms_per_step": ms2 / 2, "passes_per_step": S2, "steps": 2, "warmup": 1,
+               "paths_per_s": wl2["w"] * wl2["h"] * S2 * 2 / (ms2 * 1e-3)}
+        if os.path.exists(refc):
+            c2 = run(refc, sdir2, 2)
+            sec["metric"] = "Mrays/s"; sec["value"] = (c2["closest_rays"] + c2["shadow_rays"]) / 2 * S2 * 2 / (ms2 * 1e-3) / 1e6
+        line["secondary"] = sec
     print(json.dumps(line))
 
 
@@ -875,7 +981,11 @@ def main():
     ap.add_argument("--grid-full", action="store_true", help="hashgrid: add the 82.9 M-photon worst case of a 4K VCM iteration")
     ap.add_argument("--rays-side", type=int, default=2048, help="trace_batch: the primary batch is rays_side^2 rays (2048 -> 4.19 M)")
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
-    ap.add_argument("--sharding", default="striped", choices=["striped", "tiles"])
+    ap.add_argument("--sharding", default=None, choices=["striped", "tiles"],
+                    help="default: tiles for the bidirectional workloads at N > 1 (strong scaling: rows sharded, photons exchanged every iteration), striped otherwise")
+    ap.add_argument("--lanes", type=int, default=2, help="tiles sharding: iterations in flight per rank")
+    ap.add_argument("--no-relmse", action="store_true", help="skip the 1080p frame against the reference's (rainbow_vcm only)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the dragon-NEE secondary measurement (rainbow_vcm, N = 1)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="tiles sharding: photon exchange by peer stores fused into the light pass, or by an NCCL all-gather")
     ap.add_argument("--detail", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")

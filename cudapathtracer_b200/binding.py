@@ -166,6 +166,15 @@ def _declare(L):
     L.novum_vcm_stats.argtypes = [vp, C.POINTER(RenderStats)]
     L.novum_vcm_stream.argtypes = [vp, C.POINTER(vp)]
     L.novum_vcm_reset_stats.argtypes = [vp]
+    L.novum_tiles_create.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), Shard, C.c_uint64, ci, C.POINTER(vp)]
+    L.novum_tiles_destroy.argtypes = [vp]
+    L.novum_tiles_destroy.restype = None
+    L.novum_tiles_lanes.argtypes = [vp]
+    L.novum_tiles_ipc_export.argtypes = [vp, vp]
+    L.novum_tiles_ipc_attach.argtypes = [vp, ci, vp]
+    L.novum_tiles_bases.argtypes = [vp, C.POINTER(vp)]
+    L.novum_tiles_attach_pointers.argtypes = [vp, ci, C.POINTER(vp)]
+    L.novum_tiles_render.argtypes = [vp, ci, ci, vp, C.POINTER(RenderStats)]
     L.novum_vcm_ipc_export.argtypes = [vp, vp]
     L.novum_vcm_ipc_attach.argtypes = [vp, ci, vp]
     L.novum_vcm_peer_write.argtypes = [vp, ci]
@@ -550,3 +559,47 @@ class VcmSession:
 
     def my_slab_tensor(self):
         return self.slabs_tensor()[self.rank * self.slab_bytes:(self.rank + 1) * self.slab_bytes]
+
+
+class TileRank:
+    """One rank of the tile renderer (include/novum_b200.h, novum_tiles_*): `lanes` iterations in flight, photon exchange by peer
+    stores fused into the light pass, device-side rendezvous. Every rank calls render() with the same iteration range."""
+
+    def __init__(self, scene, cfg, cam, rank=0, world=1, seed=103033, lanes=2):
+        self.h = C.c_void_p()
+        self.scene, self.rank, self.world, self.lanes = scene, rank, world, lanes
+        _check(lib().novum_tiles_create(scene.h, C.byref(cfg), C.byref(cam), Shard(rank, world), seed, lanes, C.byref(self.h)), "novum_tiles_create")
+
+    def close(self):
+        if self.h:
+            lib().novum_tiles_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def ipc_export(self):
+        buf = (C.c_ubyte * (64 * self.lanes))()
+        _check(lib().novum_tiles_ipc_export(self.h, buf), "novum_tiles_ipc_export")
+        return bytes(buf)
+
+    def ipc_attach(self, peer_rank, handles):
+        buf = (C.c_ubyte * (64 * self.lanes)).from_buffer_copy(handles)
+        _check(lib().novum_tiles_ipc_attach(self.h, peer_rank, buf), "novum_tiles_ipc_attach")
+
+    def bases(self):
+        arr = (C.c_void_p * self.lanes)()
+        _check(lib().novum_tiles_bases(self.h, arr), "novum_tiles_bases")
+        return list(arr)
+
+    def attach_pointers(self, peer_rank, bases):
+        arr = (C.c_void_p * self.lanes)(*bases)
+        _check(lib().novum_tiles_attach_pointers(self.h, peer_rank, arr), "novum_tiles_attach_pointers")
+
+    def render(self, first, count, d_colors):
+        st = RenderStats()
+        _check(lib().novum_tiles_render(self.h, first, count, C.c_void_p(d_colors), C.byref(st)), "novum_tiles_render")
+        return st

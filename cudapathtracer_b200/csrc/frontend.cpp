@@ -564,6 +564,7 @@ const char* novum_error_string(int code) {
         case NOVUM_E_NOSCENE: return "null scene handle";
         case NOVUM_E_NOGPU: return "no CUDA device";
         case NOVUM_E_UNSUPPORTED: return "unsupported";
+        case NOVUM_E_TIMEOUT: return "timed out waiting for a peer rank";
         case NOVUM_E_TOODEEP: return "BVH deeper than the traversal stack";
         case NOVUM_E_TOOBIG: return "size beyond the entry point's built-in limit";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";

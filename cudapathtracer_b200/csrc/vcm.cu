@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <vector>
+#include <thread>
 
 namespace nv {
 
@@ -912,13 +913,39 @@ __global__ void bdMergeBinScatter(MergeQueue mq, MergeBins b, GridParams g, uint
         order[atomicAdd(&binStart[mergeBinOf(b, g, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u)] = i;
 }
 
-// end of a peer-write light pass: publish this rank's photon count in every peer's copy of the slab header
+// end of a light pass: publish this rank's photon count in every peer's copy of the slab header and then, behind a system-scope
+// fence, the stamp that says "the records and the count of light pass `stamp` are all there" - in the peers' copies and in its own.
+// Header = two 16 B words: {count, 0, 0, 0} {stamp, 0, 0, 0}.
 __global__ void bdPushHeader(BdParams P) {
-    if (threadIdx.x < P.numPeers) {
-        uint4 h = *P.slab;
-        *P.peerSlab[threadIdx.x] = h;
+    __threadfence_system();
+    const int t = threadIdx.x;
+    if (t < P.numPeers) {
+        const uint4 h = *P.slab;
+        *P.peerSlab[t] = h;
         __threadfence_system();
+        *reinterpret_cast<volatile unsigned*>(P.peerSlab[t] + 1) = P.stamp;
+    } else if (t == P.numPeers) {
+        __threadfence();
+        *reinterpret_cast<volatile unsigned*>(P.slab + 1) = P.stamp;
     }
+}
+
+// A lane engine's rendezvous with its peers, on the device: spins until every rank's slab header in this buffer carries `stamp`
+// (the peers store it over NVLink, bdPushHeader). Replaces a host-issued collective per iteration. Gives up after ~4 s
+// (a peer that died must not hang this GPU) and reports through flag[0].
+__global__ void bdWaitSlabs(const uint4* __restrict__ slabs, size_t slabWords, int world, unsigned stamp, int* __restrict__ flag) {
+    const int r = threadIdx.x;
+    if (r >= world) return;
+    const volatile unsigned* p = reinterpret_cast<const volatile unsigned*>(slabs + (size_t)r * slabWords + 1);
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (*p != stamp) {
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 4000000000ull) { atomicExch(flag, 1 + r); return; }
+        __nanosleep(200);
+    }
+    __threadfence_system();
 }
 
 // ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------

@@ -104,6 +104,7 @@ struct BdParams {
     // when the light pass is (no separate collective; only a stream-ordered barrier before the grid build).
     uint4* peerSlab[kMaxPeers];
     int numPeers;
+    unsigned stamp;                    // written behind the count in the slab headers when the light pass is complete (lane engines wait on it)
     PhotonSoA photons;                 // records in cell order (eye pass), merge-ready
     const uint32_t* cellStart; const uint32_t* cellEnd;
     GridParams grid;

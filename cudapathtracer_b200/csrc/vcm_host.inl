@@ -15,6 +15,11 @@ struct BdEngine {
     NovumRenderConfig cfg{};
     // photons: `world` slabs (this rank appends into slab `rank`), compacted copy, cell-ordered copy
     uint4* slabs = nullptr; size_t slabWords = 0; int slabCap = 0;
+    int slabBuffers = 1, slabBuf = 0;     // lane engines double-buffer their slabs: buffer (seq & 1) holds iteration seq's photons
+    unsigned seq = 0;                     // light passes run by a lane engine (the same number on every rank): stamp = seq + 1
+    cudaStream_t stream = nullptr;        // the scene's stream, or the lane's own
+    bool ownStream = false;
+    int device = 0;
     void* peerBase[16] = {nullptr};       // other ranks' slab buffers (index = rank), null = not attached
     bool peerIpc[16] = {false};           // opened through CUDA IPC here (to be closed), else a pointer the caller owns
     bool peerWrite = false;               // light pass stores photons into the peers as it appends them
@@ -40,7 +45,7 @@ static void bdTick(BdEngine& e, int cls) {
     if (!e.prof) return;
     if (e.evUsed == e.evs.size()) { cudaEvent_t ev; cudaEventCreate(&ev); e.evs.push_back(ev); e.evCls.push_back(0); }
     e.evCls[e.evUsed] = cls;
-    cudaEventRecord(e.evs[e.evUsed++], e.scene->stream);
+    cudaEventRecord(e.evs[e.evUsed++], e.stream);
 }
 
 static void bdFree(BdEngine& e) {
@@ -54,14 +59,21 @@ static void bdFree(BdEngine& e) {
     if (e.gridAllocated) hashGridFree(e.grid);
     if (e.ev0) { cudaEventDestroy(e.ev0); cudaEventDestroy(e.ev1); }
     for (cudaEvent_t ev : e.evs) cudaEventDestroy(ev);
+    if (e.ownStream && e.stream) cudaStreamDestroy(e.stream);
     e = BdEngine();
 }
 
 static int bdModeOf(int integrator) { return integrator == NOVUM_BIDIRECTIONAL ? BD_MODE_BDPT : BD_MODE_VCM; }
 
 static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg, const NovumCamera& cam, NovumShard shard,
-                   unsigned long long seed) {
+                   unsigned long long seed, bool lane = false) {
     e.scene = scene; e.cam = cam; e.cfg = cfg; e.seed = seed;
+    cudaGetDevice(&e.device);
+    if (lane) {          // a lane of a tile renderer: own stream, slabs double-buffered
+        cudaError_t se = cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking);
+        if (se != cudaSuccess) return (int)se;
+        e.ownStream = true; e.slabBuffers = 2;
+    } else e.stream = scene->stream;
     e.w = cfg.width; e.h = cfg.height; e.eyeDepth = cfg.bdptEyeDepth; e.lightDepth = cfg.bdptLightDepth;
     e.mode = bdModeOf(cfg.integrator);
     e.rank = shard.rank; e.world = shard.world;
@@ -97,21 +109,22 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     e.slabCap = rowsMax * e.w * e.lightDepth;
     e.slabWords = (size_t)kSlabHeaderBytes / 16 + (size_t)e.slabCap * 2;
     e.maxPhotons = e.w * e.h * e.lightDepth;                 // deviceCode.cu:3276
-    A((void**)&e.slabs, e.slabWords * 16 * e.world);
+    A((void**)&e.slabs, e.slabWords * 16 * e.world * e.slabBuffers);
     if (e.mode == BD_MODE_VCM) {
         if (e.world > 1) A((void**)&e.photonsAll, (size_t)e.maxPhotons * 32);
         A((void**)&e.photonsSorted, (((size_t)e.maxPhotons + 63) & ~(size_t)63) * 32);
     }
-    A((void**)&e.d_counts, 16 * sizeof(int));
+    A((void**)&e.d_counts, 32 * sizeof(int));        // [0, 16): photons per slab, [16]: bdWaitSlabs gave up (1 + rank it waited for)
     if (err != cudaSuccess) return (int)err;
-    if ((err = cudaHostAlloc((void**)&e.h_counts, 16 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    if ((err = cudaHostAlloc((void**)&e.h_counts, 32 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    cudaMemsetAsync(e.d_counts, 0, 32 * sizeof(int), e.stream);
     if (e.mode == BD_MODE_VCM) {
         int rc = hashGridAlloc(e.grid, e.maxPhotons);
         if (rc) return rc;
         e.gridAllocated = true;
     }
-    cudaMemsetAsync(s.stats, 0, 8 * sizeof(unsigned long long), scene->stream);
-    cudaMemsetAsync(e.slabs, 0, e.slabWords * 16 * e.world, scene->stream);
+    cudaMemsetAsync(s.stats, 0, 8 * sizeof(unsigned long long), e.stream);
+    cudaMemsetAsync(e.slabs, 0, e.slabWords * 16 * e.world * e.slabBuffers, e.stream);
     cudaEventCreate(&e.ev0); cudaEventCreate(&e.ev1);
     return 0;
 }
@@ -132,11 +145,12 @@ static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
     P.etaVcm = e.mode == BD_MODE_VCM ? (float)(e.w * e.h) * kPi * r * r : 0.0f;      // deviceCode.cu:1962
     P.seed = e.seed; P.iter = iter; P.rank = e.rank; P.world = e.world; P.nLocal = e.nLocal;
     P.colors = colors;
-    P.slab = e.slabs + (size_t)e.rank * e.slabWords; P.slabCap = e.slabCap;
-    P.numPeers = 0;
+    const size_t mySlab = ((size_t)e.slabBuf * e.world + e.rank) * e.slabWords;
+    P.slab = e.slabs + mySlab; P.slabCap = e.slabCap;
+    P.numPeers = 0; P.stamp = e.seq + 1u;
     if (e.peerWrite)
         for (int r = 0; r < e.world; ++r)
-            if (r != e.rank && e.peerBase[r]) P.peerSlab[P.numPeers++] = (uint4*)e.peerBase[r] + (size_t)e.rank * e.slabWords;
+            if (r != e.rank && e.peerBase[r]) P.peerSlab[P.numPeers++] = (uint4*)e.peerBase[r] + mySlab;
     for (int k = 0; k < 3; ++k) {
         float ext = e.scene->sceneMax[k] - e.scene->sceneMin[k];
         (&P.bins.minX)[k] = e.scene->sceneMin[k];
@@ -166,15 +180,16 @@ static void launchMergeLambert(bool mis, int grid, cudaStream_t s, const SceneVi
 // light pass of iteration `iter` for this rank's rows: fills the light-vertex cache, appends photons to this rank's slab,
 // splats the t = 1 connections into `colors`
 static int bdLightPass(BdEngine& e, int iter, float4* colors) {
-    cudaStream_t s = e.scene->stream;
+    cudaStream_t s = e.stream;
     BdState& st = e.st;
     BdParams P = bdParams(e, iter, colors);
     SceneView sc = e.scene->view();
     e.mergeRadius = P.mergeRadius;
     cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
     cudaMemsetAsync(P.slab, 0, kSlabHeaderBytes, s);                      // photon counter of this rank (deviceCode.cu:3330)
+    const bool publish = P.numPeers > 0 || e.slabBuffers > 1;       // lane engines stamp their own header too (bdWaitSlabs reads all of them)
     if (e.nLocal == 0 || sc.numLights == 0) {
-        if (P.numPeers > 0) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; }
+        if (publish) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; }
         return (int)cudaGetLastError();
     }
     const int numSteps = e.mode == BD_MODE_BDPT ? e.lightDepth - 1 : e.lightDepth;      // :1116 (depth 1..max-1) vs :2029 (0..max-1)
@@ -194,29 +209,31 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
         e.launches += 2;
     }
     if (numSteps == 0 && P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, st.counters); ++e.launches; bdTick(e, 2); }
-    if (P.numPeers > 0) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; bdTick(e, 1); }
+    if (publish) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; bdTick(e, 1); }
     return (int)cudaGetLastError();
 }
 
 // after the slabs of all ranks are in place: count, compact, hash, sort, cell table, reorder into cell order
 static int bdBuildGrid(BdEngine& e, int iter) {
     if (e.mode != BD_MODE_VCM) return 0;
-    cudaStream_t s = e.scene->stream;
+    cudaStream_t s = e.stream;
     BdParams P = bdParams(e, iter, nullptr);
     if (!P.doMerge || P.mergeRadius <= 0.0f) { e.photonCount = 0; return 0; }
-    bdSlabCounts<<<1, 32, 0, s>>>(e.slabs, e.slabWords, e.world, e.slabCap, e.d_counts);
+    const uint4* slabs = e.slabs + (size_t)e.slabBuf * e.world * e.slabWords;
+    bdSlabCounts<<<1, 32, 0, s>>>(slabs, e.slabWords, e.world, e.slabCap, e.d_counts);
     ++e.launches;
-    cudaMemcpyAsync(e.h_counts, e.d_counts, 16 * sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(e.h_counts, e.d_counts, 32 * sizeof(int), cudaMemcpyDeviceToHost, s);
     cudaError_t err = cudaStreamSynchronize(s);           // the reference blocks on the same counter (deviceCode.cu:3352)
     if (err != cudaSuccess) return (int)err;
+    if (e.h_counts[16]) return NOVUM_E_TIMEOUT;          // a peer never published its light pass
     long long total = 0;
     for (int r = 0; r < e.world; ++r) total += e.h_counts[r];
     if (total > e.maxPhotons) total = e.maxPhotons;
     e.photonCount = (int)total;
-    const uint4* src = e.slabs + kSlabHeaderBytes / 16;
+    const uint4* src = slabs + kSlabHeaderBytes / 16;
     if (e.world > 1) {
         dim3 g(256, e.world);
-        bdCompactSlabs<<<g, 256, 0, s>>>(e.slabs, e.slabWords, e.world, e.d_counts, e.photonsAll);
+        bdCompactSlabs<<<g, 256, 0, s>>>(slabs, e.slabWords, e.world, e.d_counts, e.photonsAll);
         ++e.launches;
         src = e.photonsAll;
     }
@@ -233,7 +250,7 @@ static int bdBuildGrid(BdEngine& e, int iter) {
 }
 
 static int bdEyePass(BdEngine& e, int iter, float4* colors) {
-    cudaStream_t s = e.scene->stream;
+    cudaStream_t s = e.stream;
     BdState& st = e.st;
     BdParams P = bdParams(e, iter, colors);
     SceneView sc = e.scene->view();
@@ -307,21 +324,11 @@ static void bdFillStats(BdEngine& e, NovumRenderStats* stats) {
 }
 
 static void bdResetStats(BdEngine& e) {
-    cudaMemsetAsync(e.st.stats, 0, 8 * sizeof(unsigned long long), e.scene->stream);
+    cudaMemsetAsync(e.st.stats, 0, 8 * sizeof(unsigned long long), e.stream);
     e.launches = 0; e.iterations = 0; e.deviceMs = 0.f; e.evUsed = 0;
     for (int k = 0; k < 4; ++k) { e.stageMs[k] = 0.f; e.stageLaunches[k] = 0; }
     e.prof = (e.scene->profileFlags & 1) != 0; e.profCount = (e.scene->profileFlags & 2) != 0;
-    if (e.profCount) cudaMemsetAsync(e.scene->d_counters, 0, 2 * sizeof(unsigned long long), e.scene->stream);
-}
-
-static void bdEngineFree(void* p) { BdEngine* e = (BdEngine*)p; bdFree(*e); delete e; }
-
-// the engine's buffers depend on (w, h, depths, mode) only: when the launch boundary rebuilds its scene (new geometry behind the same
-// call, main.cu:925-933 re-renders 75 times) the engine moves to the new scene instead of being freed and re-allocated (16 GB at 4K)
-void bdRebindScene(void* p, NovumScene* s) {
-    BdEngine* e = (BdEngine*)p;
-    if (!e) return;
-    e->scene = s;
+    if (e.profCount) cudaMemsetAsync(e.scene->d_counters, 0, 2 * sizeof(unsigned long long), e.stream);
 }
 
 static bool bdMatches(const BdEngine& e, const NovumRenderConfig& cfg, NovumShard shard) {
@@ -329,39 +336,243 @@ static bool bdMatches(const BdEngine& e, const NovumRenderConfig& cfg, NovumShar
            e.mode == bdModeOf(cfg.integrator) && e.rank == shard.rank && e.world == shard.world;
 }
 
-// Single-call form (novum_render_device): whole iterations are striped over the ranks of `shard` — iteration i runs all
-// light and eye paths on rank i % world, so no exchange is needed and the caller only sums the framebuffers at the end.
-int vcmRenderDevice(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
-                    NovumShard shard, unsigned long long seed, float4* d_colors, NovumRenderStats* stats) {
-    NovumShard whole = {0, 1};
-    BdEngine* e = (BdEngine*)s->vcmEngine;
-    if (e && !bdMatches(*e, *cfg, whole)) { bdEngineFree(e); s->vcmEngine = nullptr; e = nullptr; }
-    if (!e) {
-        e = new BdEngine();
-        int rc = bdAlloc(*e, s, *cfg, *cam, whole, seed);
-        if (rc) { bdFree(*e); delete e; return rc; }
-        s->vcmEngine = e; s->vcmEngineFree = bdEngineFree;
-    }
-    e->cam = *cam; e->cfg = *cfg; e->seed = seed;
-    bdResetStats(*e);
-    cudaEventRecord(e->ev0, s->stream);
-    for (int k = shard.rank; k < numSample; k += shard.world) {
-        int iter = firstSample + k;
-        int rc = bdLightPass(*e, iter, d_colors);
-        if (!rc) rc = bdBuildGrid(*e, iter);
-        if (!rc) rc = bdEyePass(*e, iter, d_colors);
+// ---- tile renderer: one rank of a row-sharded bidirectional render, `lanes` iterations in flight ----------------------------------
+// Why lanes: a depth-synchronous iteration is ~130 launches whose later ones (deep bounces, a few long rays inside the glass) are
+// latency chains that leave the GPU almost empty, and their length does not shrink when a rank owns 1/8 of the pixels - measured on
+// one B200 emulating rank 0 of 8 (tools/tile_phase_timing.py): 14.4 ms per 4K VCM iteration where 53.5 / 8 = 6.7 ms was the ideal.
+// Iterations are independent (the frame is a sum), so every rank runs `lanes` engines, lane k taking iterations first + k, first + k +
+// lanes, ..., each on its own stream with its own host thread: the tails of one lane's kernels overlap the bulk of another's, and the
+// one blocking read per iteration (the photon count) stalls only its own lane.
+// Exchange: every light pass stores its photons into the same lane's slab on every peer as it appends them (bdLightStep), then stamps
+// the headers (bdPushHeader); bdWaitSlabs spins ON THE DEVICE until all ranks' stamps for this light pass are in: no collective, no host.
+// Slabs are double-buffered by the lane's light-pass count: a rank can start light pass q + 1 while a peer still compacts the slabs
+// of q; it cannot reach q + 2 before that peer has stamped q + 1, which the peer does after its compaction of q (stream order).
+struct TileRank {
+    NovumScene* scene = nullptr;
+    int rank = 0, world = 1, lanes = 1, device = 0;
+    std::vector<BdEngine*> eng;
+    cudaEvent_t evStart = nullptr; std::vector<cudaEvent_t> evEnd;
+};
+
+// iterations firstIter + j, j = offset, offset + stride, ... < numIter (stride > 1: whole iterations striped over ranks, as
+// novum_render_device does); the lanes take them round-robin
+static int tileLaneRun(TileRank& t, int lane, int firstIter, int numIter, int offset, int stride, float4* d_colors) {
+    cudaSetDevice(t.device);
+    BdEngine& e = *t.eng[lane];
+    const bool exchange = e.world > 1 && e.mode == BD_MODE_VCM;
+    for (int j = offset + stride * lane; j < numIter; j += stride * t.lanes) {
+        const int iter = firstIter + j;
+        e.slabBuf = (int)(e.seq & 1u);
+        int rc = bdLightPass(e, iter, d_colors);
         if (rc) return rc;
+        if (exchange) {
+            const uint4* slabs = e.slabs + (size_t)e.slabBuf * e.world * e.slabWords;
+            bdWaitSlabs<<<1, 32, 0, e.stream>>>(slabs, e.slabWords, e.world, e.seq + 1u, e.d_counts + 16);
+            ++e.launches;
+        }
+        if ((rc = bdBuildGrid(e, iter)) != 0) return rc;
+        if ((rc = bdEyePass(e, iter, d_colors)) != 0) return rc;
+        ++e.seq;
     }
-    cudaEventRecord(e->ev1, s->stream);
-    cudaError_t err = cudaStreamSynchronize(s->stream);
-    if (err != cudaSuccess) return (int)err;
-    if ((err = cudaGetLastError()) != cudaSuccess) return (int)err;
-    cudaEventElapsedTime(&e->deviceMs, e->ev0, e->ev1);
-    for (size_t i = 1; i < e->evUsed; ++i) { float ms = 0; cudaEventElapsedTime(&ms, e->evs[i - 1], e->evs[i]); e->stageMs[e->evCls[i]] += ms; }
-    bdFillStats(*e, stats);
+    return (int)cudaGetLastError();
+}
+
+
+int tileRender(TileRank& t, int firstIter, int numIter, int offset, int stride, float4* d_colors, NovumRenderStats* stats) {
+    cudaSetDevice(t.device);
+    if (t.world > 1)
+        for (BdEngine* e : t.eng) {
+            for (int r = 0; r < t.world; ++r)
+                if (r != t.rank && !e->peerBase[r]) return NOVUM_E_ARG;          // every peer must be attached first
+            e->peerWrite = true;
+        }
+    for (BdEngine* e : t.eng) bdResetStats(*e);
+    cudaEventRecord(t.evStart, t.eng[0]->stream);
+    for (int k = 1; k < t.lanes; ++k) cudaStreamWaitEvent(t.eng[k]->stream, t.evStart, 0);
+    std::vector<int> rcs(t.lanes, 0);
+    std::vector<std::thread> th;
+    for (int k = 1; k < t.lanes; ++k) th.emplace_back([&, k]() { rcs[k] = tileLaneRun(t, k, firstIter, numIter, offset, stride, d_colors); });
+    rcs[0] = tileLaneRun(t, 0, firstIter, numIter, offset, stride, d_colors);
+    for (std::thread& x : th) x.join();
+    int rc = 0;
+    for (int k = 0; k < t.lanes; ++k) {
+        cudaEventRecord(t.evEnd[k], t.eng[k]->stream);
+        cudaError_t err = cudaStreamSynchronize(t.eng[k]->stream);
+        if (!rc && rcs[k]) rc = rcs[k];
+        if (!rc && err != cudaSuccess) rc = (int)err;
+        if (!rc && t.eng[k]->h_counts[16]) rc = NOVUM_E_TIMEOUT;
+    }
+    if (rc) return rc;
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        for (int k = 0; k < t.lanes; ++k) {
+            BdEngine& e = *t.eng[k];
+            float ms = 0; cudaEventElapsedTime(&ms, t.evStart, t.evEnd[k]);
+            for (size_t i = 1; i < e.evUsed; ++i) { float g = 0; cudaEventElapsedTime(&g, e.evs[i - 1], e.evs[i]); e.stageMs[e.evCls[i]] += g; }
+            NovumRenderStats one;
+            bdFillStats(e, &one);
+            stats->closestRays += one.closestRays; stats->shadowRays += one.shadowRays; stats->paths += one.paths;
+            stats->lightVertices += one.lightVertices; stats->kernelLaunches += one.kernelLaunches;
+            stats->mergeQueries += one.mergeQueries; stats->mergeCandidates += one.mergeCandidates; stats->mergeAccepted += one.mergeAccepted;
+            stats->bvhNodeVisits += one.bvhNodeVisits; stats->triTests += one.triTests;
+            for (int c = 0; c < 4; ++c) { stats->stageMs[c] += one.stageMs[c]; stats->stageLaunches[c] += one.stageLaunches[c]; }
+            stats->photons += one.photons;
+            if (ms > stats->deviceMs) stats->deviceMs = ms;
+        }
+    }
     return 0;
 }
 
+
+static void tileFree(TileRank* t) {
+    if (!t) return;
+    cudaSetDevice(t->device);
+    for (BdEngine* e : t->eng) { bdFree(*e); delete e; }
+    for (cudaEvent_t ev : t->evEnd) cudaEventDestroy(ev);
+    if (t->evStart) cudaEventDestroy(t->evStart);
+    delete t;
+}
+static void tileEngineFree(void* p) { tileFree((TileRank*)p); }
+
+static int tileCreate(NovumScene* s, const NovumRenderConfig& cfg, const NovumCamera& cam, NovumShard shard, unsigned long long seed, int lanes,
+                      TileRank** out) {
+    TileRank* t = new TileRank();
+    t->scene = s; t->rank = shard.rank; t->world = shard.world;
+    cudaGetDevice(&t->device);
+    int rc = 0;
+    for (int k = 0; k < lanes; ++k) {
+        BdEngine* e = new BdEngine();
+        rc = bdAlloc(*e, s, cfg, cam, shard, seed, /*lane=*/true);
+        if (rc) {
+            bdFree(*e); delete e;
+            // out of memory for this lane: run with the lanes that fit (world = 1 only: the ranks of a tile render must agree on the count)
+            if (rc == (int)cudaErrorMemoryAllocation && k > 0 && shard.world == 1) { cudaGetLastError(); rc = 0; break; }
+            tileFree(t);
+            return rc;
+        }
+        t->eng.push_back(e);
+        cudaEvent_t ev; cudaEventCreate(&ev); t->evEnd.push_back(ev);
+    }
+    t->lanes = (int)t->eng.size();
+    cudaEventCreate(&t->evStart);
+    for (BdEngine* e : t->eng) cudaStreamSynchronize(e->stream);          // slabs zeroed before a peer may store into them
+    *out = t;
+    return 0;
+}
+
+// iterations in flight of the single-call render (novum_render_device): NOVUM_LANES in the environment, default 3
+// (4K VCM on one B200: 49.6 / 45.1 / 44.1 / 43.8 ms per iteration with 1 / 2 / 3 / 4 lanes; a lane costs 16 GB there)
+static int defaultLanes() {
+    const char* e = getenv("NOVUM_LANES");
+    int n = e ? atoi(e) : 3;
+    return n < 1 ? 1 : (n > 8 ? 8 : n);
+}
+
+// the engines' buffers depend on (w, h, depths, mode) only: when the launch boundary rebuilds its scene (new geometry behind the same
+// call, main.cu:925-933 re-renders 75 times) they move to the new scene instead of being freed and re-allocated (16 GB per lane at 4K)
+void bdRebindScene(void* p, NovumScene* s) {
+    TileRank* t = (TileRank*)p;
+    if (!t) return;
+    t->scene = s;
+    for (BdEngine* e : t->eng) e->scene = s;
+}
+
+// Single-call form (novum_render_device): whole iterations are striped over the ranks of `shard` - iteration i runs all light and
+// eye paths on rank i % world, so no exchange is needed and the caller only sums the framebuffers at the end. On the rank, the
+// iterations go through the tile renderer's lanes (world = 1: the whole frame).
+int vcmRenderDevice(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample,
+                    NovumShard shard, unsigned long long seed, float4* d_colors, NovumRenderStats* stats) {
+    NovumShard whole = {0, 1};
+    TileRank* t = (TileRank*)s->vcmEngine;
+    if (t && !bdMatches(*t->eng[0], *cfg, whole)) { tileFree(t); s->vcmEngine = nullptr; t = nullptr; }
+    if (!t) {
+        int rc = tileCreate(s, *cfg, *cam, whole, seed, defaultLanes(), &t);
+        if (rc) return rc;
+        s->vcmEngine = t; s->vcmEngineFree = tileEngineFree;
+    }
+    for (BdEngine* e : t->eng) { e->cam = *cam; e->cfg = *cfg; e->seed = seed; }
+    return tileRender(*t, firstSample, numSample, shard.rank, shard.world, d_colors, stats);
+}
+
+}  // namespace nv
+
+// the opaque NovumTiles handle of the C ABI is a nv::TileRank
+static inline nv::TileRank* tr(NovumTiles* T) { return reinterpret_cast<nv::TileRank*>(T); }
+static inline const nv::TileRank* tr(const NovumTiles* T) { return reinterpret_cast<const nv::TileRank*>(T); }
+
+extern "C" {
+
+int novum_tiles_create(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, NovumShard shard, uint64_t seed, int lanes,
+                       NovumTiles** out) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (!cfg || !cam || !out || shard.world < 1 || shard.world > 16 || shard.rank < 0 || shard.rank >= shard.world) return NOVUM_E_ARG;
+    if (lanes < 1 || lanes > 8) return NOVUM_E_ARG;
+    if (cfg->integrator != NOVUM_VCM && cfg->integrator != NOVUM_SPPM && cfg->integrator != NOVUM_BIDIRECTIONAL) return NOVUM_E_ARG;
+    nv::TileRank* t = nullptr;
+    int rc = nv::tileCreate(s, *cfg, *cam, shard, seed, lanes, &t);
+    if (rc) return rc;
+    *out = reinterpret_cast<NovumTiles*>(t);
+    return 0;
+}
+
+void novum_tiles_destroy(NovumTiles* T) { nv::tileFree(tr(T)); }
+
+int novum_tiles_lanes(const NovumTiles* T) { return T ? tr(T)->lanes : NOVUM_E_ARG; }
+
+/* lanes x 64 bytes: the CUDA IPC handle of every lane's slab buffer, for the caller to carry to the other processes */
+int novum_tiles_ipc_export(NovumTiles* T, void* handles) {
+    if (!T || !handles) return NOVUM_E_ARG;
+    for (int k = 0; k < tr(T)->lanes; ++k) {
+        cudaIpcMemHandle_t h;
+        cudaError_t err = cudaIpcGetMemHandle(&h, tr(T)->eng[k]->slabs);
+        if (err != cudaSuccess) return (int)err;
+        memcpy((char*)handles + 64 * k, &h, 64);
+    }
+    return 0;
+}
+
+int novum_tiles_ipc_attach(NovumTiles* T, int peerRank, const void* handles) {
+    if (!T || !handles || peerRank < 0 || peerRank >= tr(T)->world || peerRank == tr(T)->rank) return NOVUM_E_ARG;
+    for (int k = 0; k < tr(T)->lanes; ++k) {
+        nv::BdEngine& e = *tr(T)->eng[k];
+        if (e.peerBase[peerRank]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)handles + 64 * k, 64);
+        void* p = nullptr;
+        cudaError_t err = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (err != cudaSuccess) { cudaGetLastError(); return (int)err; }
+        e.peerBase[peerRank] = p; e.peerIpc[peerRank] = true;
+    }
+    return 0;
+}
+
+/* same-process ranks (one per GPU with peer access enabled, or several on one GPU): lane k's slab buffer of the peer, from novum_tiles_bases */
+int novum_tiles_bases(NovumTiles* T, void** bases) {
+    if (!T || !bases) return NOVUM_E_ARG;
+    for (int k = 0; k < tr(T)->lanes; ++k) bases[k] = tr(T)->eng[k]->slabs;
+    return 0;
+}
+
+int novum_tiles_attach_pointers(NovumTiles* T, int peerRank, void* const* bases) {
+    if (!T || !bases || peerRank < 0 || peerRank >= tr(T)->world || peerRank == tr(T)->rank) return NOVUM_E_ARG;
+    for (int k = 0; k < tr(T)->lanes; ++k) {
+        nv::BdEngine& e = *tr(T)->eng[k];
+        if (!bases[k]) return NOVUM_E_ARG;
+        e.peerBase[peerRank] = bases[k]; e.peerIpc[peerRank] = false;
+    }
+    return 0;
+}
+
+/* Renders iterations [firstIter, firstIter + numIter) of this rank's rows into d_colors (full-frame SUM accumulator of this rank;
+ * t = 1 splats land anywhere). Every rank of the render must make the same call. Blocking. */
+int novum_tiles_render(NovumTiles* T, int firstIter, int numIter, NovumFloat4* d_colors, NovumRenderStats* stats) {
+    if (!T || !d_colors || numIter < 0) return NOVUM_E_ARG;
+    return nv::tileRender(*tr(T), firstIter, numIter, 0, 1, (float4*)d_colors, stats);
+}
+
+}  // extern "C"
+
+namespace nv {
 }  // namespace nv
 
 // ---- C ABI: multi-GPU phase API (tile-sharded: rank r owns pixel rows y % world == r for BOTH walks) -----------------------
@@ -412,7 +623,7 @@ int novum_vcm_eye_pass(NovumVcmState* v, int iter, NovumFloat4* d_colors) {
 
 int novum_vcm_stats(NovumVcmState* v, NovumRenderStats* stats) {
     if (!v || !stats) return NOVUM_E_ARG;
-    cudaError_t err = cudaStreamSynchronize(v->e.scene->stream);
+    cudaError_t err = cudaStreamSynchronize(v->e.stream);
     if (err != cudaSuccess) return (int)err;
     nv::BdEngine& e = v->e;
     for (size_t i = 1; i < e.evUsed; ++i) { float ms = 0; cudaEventElapsedTime(&ms, e.evs[i - 1], e.evs[i]); e.stageMs[e.evCls[i]] += ms; }
@@ -474,7 +685,7 @@ int novum_vcm_reset_stats(NovumVcmState* v) {
 
 int novum_vcm_stream(NovumVcmState* v, void** stream) {
     if (!v || !stream) return NOVUM_E_ARG;
-    *stream = (void*)v->e.scene->stream;
+    *stream = (void*)v->e.stream;
     return 0;
 }
 

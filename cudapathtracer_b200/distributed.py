@@ -67,8 +67,10 @@ def exchange_slabs(dist, slabs, rank, world, slab_bytes):
     return used
 
 
-class TileRenderer:
-    """Tile-sharded bidirectional render: keeps the per-rank session (buffers, slabs) alive across calls.
+class PhaseTileRenderer:
+    """Tile-sharded bidirectional render through the PHASE API (host-ordered light pass / exchange / grid build / eye pass, one iteration
+    at a time); kept for the NCCL all-gather exchange and as the fallback when CUDA IPC mapping is unavailable. Keeps the per-rank session
+    (buffers, slabs) alive across calls.
 
     exchange="p2p" (default for world > 1): the ranks swap CUDA IPC handles of their slab buffers once; every light pass
     then stores its photons into all peers over NVLink while it appends them (the all-gather is fused into the light-pass
@@ -142,14 +144,58 @@ class TileRenderer:
         s.eye_pass(it, colors.data_ptr())
 
     def render(self, first, count, colors):
+        """Returns the RenderStats of THIS call (the session's counters are cumulative: differences are taken here), deviceMs = CUDA-event
+        time on the engine's stream."""
+        torch = self.torch
+        before = self.session.stats()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.ext_stream)
         for it in range(first, first + count):
             self.iteration(it, colors)
+        e1.record(self.ext_stream)
         nb.lib().novum_sync()
         st = self.session.stats()
         if self.exchange_mode == "p2p":               # bytes stored into peers + received from them, last iteration
             self.last_exchange_bytes = PHOTON_BYTES * int(st.photons)
             self.exchanged_bytes += self.last_exchange_bytes * count
+        for f in ("closestRays", "shadowRays", "paths", "lightVertices", "kernelLaunches", "mergeQueries", "mergeCandidates", "mergeAccepted"):
+            setattr(st, f, getattr(st, f) - getattr(before, f))
+        st.deviceMs = e0.elapsed_time(e1)
         return st
+
+
+class TileRenderer:
+    """The tile renderer of the C ABI (novum_tiles_*), one rank per process: rank r owns pixel rows y % world == r; `lanes` iterations
+    are in flight per rank; every light pass stores its photons into the same lane's slab on every peer over NVLink (the slab buffers
+    are swapped once as CUDA IPC handles over the process group) and the per-iteration rendezvous is a device-side wait on stamps in
+    the slab headers. torch.distributed only carries the handles and the barriers around set-up and tear-down."""
+
+    def __init__(self, scene, cfg, cam, dist=None, seed=103033, lanes=2):
+        import torch
+        self.torch, self.dist = torch, dist
+        self.rank, self.world = shard_of(dist)
+        self.lanes = lanes
+        self.t = nb.TileRank(scene, cfg, cam, rank=self.rank, world=self.world, seed=seed, lanes=lanes)
+        self.exchange_mode = "none" if self.world == 1 else "p2p"
+        self.last_exchange_bytes = 0
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, self.t.ipc_export())
+            for r, h in enumerate(handles):
+                if r != self.rank:
+                    self.t.ipc_attach(r, h)
+            dist.barrier()
+
+    def render(self, first, count, colors):
+        st = self.t.render(first, count, colors.data_ptr())
+        # bytes this rank stored into its peers (its own photons, once per peer), per iteration
+        self.last_exchange_bytes = PHOTON_BYTES * int(st.photons) * (self.world - 1) // max(1, count)
+        return st
+
+    def close(self):
+        if self.dist is not None and self.dist.is_initialized() and self.world > 1:
+            self.dist.barrier()            # nobody frees slabs a peer may still be storing into
+        self.t.close()
 
 
 def frame_to_host(colors):

@@ -42,6 +42,7 @@ extern "C" {
 #define NOVUM_E_NOSCENE    (-3)
 #define NOVUM_E_NOGPU      (-4)
 #define NOVUM_E_UNSUPPORTED (-5)
+#define NOVUM_E_TIMEOUT    (-8)   /* a peer rank never published its light pass (tile renderer) */
 #define NOVUM_E_TOODEEP    (-7)   /* the BVH8 built from the scene is deeper than the traversal stack (52 levels): degenerate geometry */
 #define NOVUM_E_TOOBIG     (-6)   /* size beyond a fixed built-in limit (novum_hashgrid_build_static) */
 
@@ -363,6 +364,25 @@ int  novum_vcm_ipc_attach(NovumVcmState* v, int peerRank, const void* handle64);
 int  novum_vcm_attach_pointer(NovumVcmState* v, int peerRank, void* d_peerCacheBase);   /* same-process ranks: novum_vcm_cache_buffer's base of the peer */
 int  novum_vcm_peer_write(NovumVcmState* v, int enable);
 int  novum_sync(void);
+
+/* ---- tile renderer: the multi-GPU decomposition of the bidirectional integrators as ONE call per rank ---------------------------
+ * Rank r owns pixel rows y % world == r for both walks of every iteration (as the phase API above). Every rank runs `lanes` iterations
+ * concurrently (lane k: iterations first + k, first + k + lanes, ...; own stream + host thread each), which fills the latency-bound tails
+ * of a depth-synchronous iteration - they do not shrink with the rank's share of the pixels. The photon exchange is fused into the light
+ * pass (peer stores over NVLink into the same lane's slab on every peer) and the per-iteration rendezvous is a device-side wait on
+ * stamps in the slab headers: no collective and no host round trip between ranks. Setup: create on every rank, exchange the lanes' slab
+ * buffers (CUDA IPC handles across processes, pointers inside one process), then every rank calls novum_tiles_render with the same
+ * (firstIter, numIter); the full-frame accumulators are summed by the caller at the end. world = 1 is valid (one GPU, lanes in flight). */
+typedef struct NovumTiles NovumTiles;
+int  novum_tiles_create(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, NovumShard shard, uint64_t seed, int lanes,
+                        NovumTiles** out);
+void novum_tiles_destroy(NovumTiles* t);
+int  novum_tiles_lanes(const NovumTiles* t);
+int  novum_tiles_ipc_export(NovumTiles* t, void* handles /* lanes x 64 B */);
+int  novum_tiles_ipc_attach(NovumTiles* t, int peerRank, const void* handles /* lanes x 64 B */);
+int  novum_tiles_bases(NovumTiles* t, void** bases /* lanes */);
+int  novum_tiles_attach_pointers(NovumTiles* t, int peerRank, void* const* bases /* lanes */);
+int  novum_tiles_render(NovumTiles* t, int firstIter, int numIter, NovumFloat4* d_colors, NovumRenderStats* stats);
 
 /* ---- synthetic scene generator (stand-ins for the reference's LFS-pointer OBJ files) ----- */
 /* writes OBJ files + a .rendertron config under outDir; name in {cornell, dragon, water, rainbow}. */

@@ -257,3 +257,44 @@ def test_full_size_vcm_decompositions_agree(tmp_path):
         assert np.allclose(blocks(total), blocks(full), rtol=2e-3, atol=1e-3)
     finally:
         scene.close()
+
+
+@pytest.mark.parametrize("integ,world,lanes", [(3, 1, 2), (3, 2, 2), (3, 3, 1), (4, 2, 2), (1, 2, 2)])
+def test_tile_renderer_lanes_equal_single_gpu(integ, world, lanes, cornell):
+    """novum_tiles_*: `world` ranks x `lanes` iterations in flight (ranks are threads of this process on one GPU here; across
+    processes the slab buffers travel as CUDA IPC handles), photons exchanged by peer stores inside the light pass, rendezvous by
+    stamps in the slab headers that a device-side wait kernel polls. The sum of the ranks' frames is the single-GPU frame."""
+    import threading
+    import torch
+    cfg = _cfg(cornell, 48, 30, integ)
+    cam = nb.camera_make(cfg)
+    iters = 7
+    full, st_full = cornell.render(cfg, cam, 2, iters)
+    ranks = [nb.TileRank(cornell, cfg, cam, rank=r, world=world, lanes=lanes) for r in range(world)]
+    frames = [torch.zeros((cfg.height, cfg.width, 4), dtype=torch.float32, device="cuda") for _ in range(world)]
+    stats, errs = [None] * world, []
+    try:
+        for r, t in enumerate(ranks):
+            for q, o in enumerate(ranks):
+                if q != r:
+                    t.attach_pointers(q, o.bases())
+
+        def run(r, first, count):
+            try:
+                stats[r] = ranks[r].render(first, count, frames[r].data_ptr())
+            except Exception as ex:      # noqa: BLE001
+                errs.append(ex)
+
+        for first, count in ((2, 3), (5, 4)):          # two calls: the lanes' buffer parity and stamps carry over
+            th = [threading.Thread(target=run, args=(r, first, count)) for r in range(world)]
+            [t.start() for t in th]
+            [t.join() for t in th]
+            assert not errs, errs
+        total = sum(f.cpu().numpy() for f in frames)
+    finally:
+        for t in ranks:
+            t.close()
+    assert np.allclose(total, full, rtol=2e-3, atol=1e-4), float(np.abs(total - full).max())
+    assert sum(s.paths for s in stats) == 2 * cfg.width * cfg.height * 4       # the last call's 4 iterations
+    if integ != 1:
+        assert stats[0].photons > 0
