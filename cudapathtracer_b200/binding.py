@@ -170,6 +170,7 @@ def _declare(L):
     L.novum_tiles_destroy.argtypes = [vp]
     L.novum_tiles_destroy.restype = None
     L.novum_tiles_lanes.argtypes = [vp]
+    L.novum_tiles_set_view.argtypes = [vp, C.POINTER(RenderConfig), C.POINTER(Camera), C.c_uint64]
     L.novum_tiles_ipc_export.argtypes = [vp, vp]
     L.novum_tiles_ipc_attach.argtypes = [vp, ci, vp]
     L.novum_tiles_bases.argtypes = [vp, C.POINTER(vp)]

@@ -6,6 +6,8 @@
 #include <cstdio>
 #include <cstring>
 #include <cmath>
+#include <algorithm>
+#include <vector>
 
 using namespace nv;
 
@@ -77,8 +79,21 @@ int ensureStage(NovumScene* s, size_t bytes) {
     return 0;
 }
 
+// largest normal / uv index a triangle names (+1): the lengths of those arrays do not cross the launch boundary
+__global__ void attrCountKernel(const NovumTriangle* __restrict__ tris, int n, int* __restrict__ out) {
+    int mn = -1, mu = -1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const NovumTriangle& t = tris[i];
+        mn = max(mn, max(t.naInd, max(t.nbInd, t.ncInd)));
+        mu = max(mu, max(t.uvaInd, max(t.uvbInd, t.uvcInd)));
+    }
+    for (int o = 16; o > 0; o >>= 1) { mn = max(mn, __shfl_xor_sync(0xffffffffu, mn, o)); mu = max(mu, __shfl_xor_sync(0xffffffffu, mu, o)); }
+    if ((threadIdx.x & 31) == 0) { atomicMax(out, mn); atomicMax(out + 1, mu); }
+}
+
 int sceneFinalize(NovumScene* s) {
     cudaError_t e;
+    cudaGetDevice(&s->device);
     if (!s->stream && (e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
     if (!s->ev0) { cudaEventCreate(&s->ev0); cudaEventCreate(&s->ev1); }
     if ((e = cudaMalloc(&s->d_mats, sizeof(DMat) * (s->nMat > 0 ? s->nMat : 1))) != cudaSuccess) return (int)e;
@@ -209,12 +224,65 @@ int novum_scene_from_device(const NovumVertices* d_vertices, int vertNum, const 
     s->nPos = vertNum; s->nNorm = 0; s->nUV = 0; s->nTri = triNum; s->nLights = lightNum; s->nMat = nMat;
     int rc = sceneFinalize(s);
     if (rc) { novum_scene_destroy(s); return rc; }
+    {   // lengths of the normal / uv / texel arrays, as far as the scene uses them (needed to replicate the scene on another GPU)
+        int h[2] = {-1, -1};
+        cudaMemcpyAsync(s->d_queueCounter, h, sizeof(h), cudaMemcpyHostToDevice, s->stream);
+        attrCountKernel<<<smCount() * 4, 256, 0, s->stream>>>(s->d_tris, s->nTri, s->d_queueCounter);
+        cudaMemcpyAsync(h, s->d_queueCounter, sizeof(h), cudaMemcpyDeviceToHost, s->stream);
+        std::vector<NovumMaterial> hm((size_t)nMat);
+        cudaMemcpyAsync(hm.data(), d_materials, sizeof(NovumMaterial) * (size_t)nMat, cudaMemcpyDeviceToHost, s->stream);
+        if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) { novum_scene_destroy(s); return (int)e; }
+        s->nNorm = h[0] + 1; s->nUV = h[1] + 1;
+        long long texels = 0;
+        for (const NovumMaterial& m : hm)
+            if (m.hasTexture && m.width > 0 && m.height > 0 && m.startInd >= 0) texels = std::max(texels, (long long)m.startInd + (long long)m.width * m.height);
+        s->nTexels = d_textures ? (int)std::min(texels, (long long)0x7fffffff) : 0;
+    }
     *out = s;
     return 0;
 }
 
+}  // extern "C"
+
+int nv::sceneReplicate(const NovumScene* src, NovumScene** out) {
+    if (!src || !out) return NOVUM_E_ARG;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    NovumScene* s = new NovumScene();
+    s->nPos = src->nPos; s->nNorm = src->nNorm; s->nUV = src->nUV; s->nTri = src->nTri; s->nLights = src->nLights; s->nMat = src->nMat;
+    s->nTexels = src->nTexels;
+    cudaError_t e = cudaSuccess;
+    auto cp = [&](void** dst, const void* from, size_t bytes) {
+        if (e != cudaSuccess) return;
+        e = cudaMalloc(dst, bytes ? bytes : 16);
+        if (e == cudaSuccess && bytes) e = cudaMemcpyPeer(*dst, dev, from, src->device, bytes);
+    };
+    cp((void**)&s->d_positions, src->d_positions, sizeof(float4) * (size_t)s->nPos);
+    cp((void**)&s->d_normals, src->d_normals, sizeof(float4) * (size_t)s->nNorm);
+    cp((void**)&s->d_uvs, src->d_uvs, sizeof(float2) * (size_t)s->nUV);
+    cp((void**)&s->d_tris, src->d_tris, sizeof(NovumTriangle) * (size_t)s->nTri);
+    cp((void**)&s->d_lights, src->d_lights, sizeof(NovumTriangle) * (size_t)s->nLights);
+    cp((void**)&s->d_matsRef, src->d_matsRef, sizeof(NovumMaterial) * (size_t)s->nMat);
+    cp((void**)&s->d_textures, src->d_textures, sizeof(float4) * (size_t)s->nTexels);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { novum_scene_destroy(s); return (int)e; }
+    int rc = sceneFinalize(s);
+    if (rc) { novum_scene_destroy(s); return rc; }
+    // the caller's root-box values, if the launch boundary put them there, travel with the scene
+    for (int k = 0; k < 3; ++k) { s->sceneMin[k] = src->sceneMin[k]; s->sceneMax[k] = src->sceneMax[k]; s->sceneCenter[k] = src->sceneCenter[k]; }
+    s->sceneRadius = src->sceneRadius;
+    *out = s;
+    return 0;
+}
+
+extern "C" {
+
 void novum_scene_destroy(NovumScene* s) {
     if (!s) return;
+    if (s->multiGpu && s->multiGpuFree) s->multiGpuFree(s->multiGpu);
+    int prevDev = 0;
+    cudaGetDevice(&prevDev);
+    if (s->stream) cudaSetDevice(s->device);
     if (s->wfEngine && s->wfEngineFree) s->wfEngineFree(s->wfEngine);
     if (s->vcmEngine && s->vcmEngineFree) s->vcmEngineFree(s->vcmEngine);
     if (!s->borrowed) {
@@ -226,6 +294,7 @@ void novum_scene_destroy(NovumScene* s) {
     freeBvh8(s->bvh);
     if (s->ev0) { cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1); }
     if (s->stream) cudaStreamDestroy(s->stream);
+    cudaSetDevice(prevDev);
     delete s;
 }
 

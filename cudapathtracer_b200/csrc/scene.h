@@ -40,12 +40,16 @@ struct NovumScene {
     void* wfEngine = nullptr;  void (*wfEngineFree)(void*) = nullptr;
     void* vcmEngine = nullptr; void (*vcmEngineFree)(void*) = nullptr;
     void* d_frame = nullptr; size_t frameBytes = 0;     // device framebuffer of novum_render, kept across calls
+    int device = 0;                                     // the CUDA device the scene lives on
+    void* multiGpu = nullptr; void (*multiGpuFree)(void*) = nullptr;   // replicas + per-GPU engines of the in-process multi-GPU launch (multigpu.cu)
 
     nv::SceneView view() const;
 };
 
 namespace nv {
 int sceneFinalize(NovumScene* s);     // compact materials, BVH8 build, bounds, stream/events
+// an owned copy of `src` (which lives on device srcDevice) on the CURRENT device: arrays copied peer to peer, BVH8 built here
+int sceneReplicate(const NovumScene* src, NovumScene** out);
 int ensureStage(NovumScene* s, size_t bytes);
 int smCount();
 int renderDeviceMis(NovumScene* s, const NovumRenderConfig* cfg, const NovumCamera* cam, int firstSample, int numSample, NovumShard shard,

@@ -117,6 +117,7 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     A((void**)&e.d_counts, 32 * sizeof(int));        // [0, 16): photons per slab, [16]: bdWaitSlabs gave up (1 + rank it waited for)
     if (err != cudaSuccess) return (int)err;
     if ((err = cudaHostAlloc((void**)&e.h_counts, 32 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    memset(e.h_counts, 0, 32 * sizeof(int));               // page-locked memory arrives uninitialised; [16] is read as the time-out flag
     cudaMemsetAsync(e.d_counts, 0, 32 * sizeof(int), e.stream);
     if (e.mode == BD_MODE_VCM) {
         int rc = hashGridAlloc(e.grid, e.maxPhotons);
@@ -414,7 +415,7 @@ int tileRender(TileRank& t, int firstIter, int numIter, int offset, int stride, 
             stats->closestRays += one.closestRays; stats->shadowRays += one.shadowRays; stats->paths += one.paths;
             stats->lightVertices += one.lightVertices; stats->kernelLaunches += one.kernelLaunches;
             stats->mergeQueries += one.mergeQueries; stats->mergeCandidates += one.mergeCandidates; stats->mergeAccepted += one.mergeAccepted;
-            stats->bvhNodeVisits += one.bvhNodeVisits; stats->triTests += one.triTests;
+            stats->bvhNodeVisits = one.bvhNodeVisits; stats->triTests = one.triTests;       // the lanes count into the scene's one pair of counters
             for (int c = 0; c < 4; ++c) { stats->stageMs[c] += one.stageMs[c]; stats->stageLaunches[c] += one.stageLaunches[c]; }
             stats->photons += one.photons;
             if (ms > stats->deviceMs) stats->deviceMs = ms;
@@ -516,6 +517,15 @@ int novum_tiles_create(NovumScene* s, const NovumRenderConfig* cfg, const NovumC
 }
 
 void novum_tiles_destroy(NovumTiles* T) { nv::tileFree(tr(T)); }
+
+/* camera, strategy toggles, merge parameters and seed of the following renders; resolution, depths and integrator family are fixed at creation */
+int novum_tiles_set_view(NovumTiles* T, const NovumRenderConfig* cfg, const NovumCamera* cam, uint64_t seed) {
+    if (!T || !cfg || !cam) return NOVUM_E_ARG;
+    nv::TileRank& t = *tr(T);
+    if (!nv::bdMatches(*t.eng[0], *cfg, NovumShard{t.rank, t.world})) return NOVUM_E_ARG;
+    for (nv::BdEngine* e : t.eng) { e->cam = *cam; e->cfg = *cfg; e->seed = seed; }
+    return 0;
+}
 
 int novum_tiles_lanes(const NovumTiles* T) { return T ? tr(T)->lanes : NOVUM_E_ARG; }
 

@@ -378,6 +378,8 @@ int  novum_tiles_create(NovumScene* s, const NovumRenderConfig* cfg, const Novum
                         NovumTiles** out);
 void novum_tiles_destroy(NovumTiles* t);
 int  novum_tiles_lanes(const NovumTiles* t);
+/* camera, strategy toggles, merge parameters and seed of the following renders (resolution, depths, integrator family stay as created) */
+int  novum_tiles_set_view(NovumTiles* t, const NovumRenderConfig* cfg, const NovumCamera* cam, uint64_t seed);
 int  novum_tiles_ipc_export(NovumTiles* t, void* handles /* lanes x 64 B */);
 int  novum_tiles_ipc_attach(NovumTiles* t, int peerRank, const void* handles /* lanes x 64 B */);
 int  novum_tiles_bases(NovumTiles* t, void** bases /* lanes */);

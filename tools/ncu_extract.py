@@ -53,15 +53,21 @@ with open(os.path.join(P, f"r2_{W}_launches.txt"), "w") as f:
         f.write(f"{n[:44]:44s} {cnt[n]:8d} {tot[n] / 1e6:10.3f} {tot[n] / all_:7.3f}\n")
 print(open(os.path.join(P, f"r2_{W}_launches.txt")).read())
 # ---- full capture ----
-rep = os.path.join(G, f"r2_{W}_full.ncu-rep")
-out = subprocess.check_output(['ncu', '-i', rep, '--page', 'raw', '--csv'], stderr=subprocess.DEVNULL).decode()
-rows = list(csv.reader(out.splitlines()))
+rows = list(csv.reader(open(os.path.join(G, f"r2_{W}_full_raw.csv"))))       # `ncu -i <report> --page raw --csv`, exported on the GPU box (tools/profile.sh)
 hdr, units, data = rows[0], rows[1], rows[2:]
 kn = hdr.index('Kernel Name')
 col = {k: hdr.index(k) for k in KEYS if k in hdr}
+SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "ns": 1.0, "us": 1e3, "ms": 1e6, "s": 1e9}      # -> bytes, ns
+
+
+def val(r, k):
+    v = num(r[col[k]])
+    return None if v is None else v * SCALE.get(units[col[k]], 1.0)
+
+
 per = collections.defaultdict(list)
 for r in data:
-    per[short(r[kn])].append({k: num(r[i]) for k, i in col.items()})
+    per[short(r[kn])].append({k: val(r, k) for k in col})
 with open(os.path.join(P, f"r2_{W}_full.txt"), "w") as f:
     f.write(f"# ncu --profile-from-start off --set full --clock-control none --import-source on: python tools/profile_target.py {W} (SHIPPED kernels)\n")
     f.write(f"# step counters of the same program: {json.dumps(target)}\n")
@@ -69,7 +75,7 @@ with open(os.path.join(P, f"r2_{W}_full.txt"), "w") as f:
         f.write(f"\n== {name}: {len(launches)} launches ==\n")
         for k in col:
             vals = [l[k] for l in launches]
-            u = units[col[k]]
+            u = {"Kbyte": "byte", "Mbyte": "byte", "Gbyte": "byte", "us": "ns", "ms": "ns", "s": "ns"}.get(units[col[k]], units[col[k]])
             f.write(f"{k} [{u}]: " + " ".join("-" if v is None else (f"{v:.4g}") for v in vals) + "\n")
 print(open(os.path.join(P, f"r2_{W}_full.txt")).read()[:3000])
 # ---- counters for bench.py ----

@@ -12,6 +12,8 @@ python tools/profile_target.py "$W" > "gpurun_out/r2_${W}_target.log" 2>&1
 grep PROFILE_TARGET_JSON "gpurun_out/r2_${W}_target.log"
 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file "gpurun_out/r2_${W}_launches.csv" \
     python tools/profile_target.py "$W" > "gpurun_out/r2_${W}_launches.log" 2>&1
-ncu --profile-from-start off --set full --clock-control none --import-source on -k "regex:$K" -f -o "gpurun_out/r2_${W}_full" \
+ncu --profile-from-start off --set full --clock-control none --import-source on -k "regex:$K" -f -o "/tmp/r2_${W}_full" \
     python tools/profile_target.py "$W" > "gpurun_out/r2_${W}_full.log" 2>&1
-ls -la gpurun_out/r2_${W}_*
+# the report of ~60 launches is ~100 MB and gpurun_out/ carries 64 MiB: the counters travel as CSV (what `ncu -i ... --page raw --csv` prints)
+ncu -i "/tmp/r2_${W}_full.ncu-rep" --page raw --csv > "gpurun_out/r2_${W}_full_raw.csv"
+ls -la gpurun_out/r2_${W}_* /tmp/r2_${W}_full.ncu-rep
