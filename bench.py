@@ -37,7 +37,7 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 UNI, BDPT, NAIVE, VCM, SPPM = 0, 1, 2, 3, 4
 WORKLOADS = {
     "dragon_nee": dict(gen="dragon", integ=UNI, w=1920, h=1080, spp=32, desc="configs[1]: dragon stand-in (~871k tris, glass) 1920x1080 NEE+MIS"),
-    "rainbow_vcm": dict(gen="rainbow", integ=VCM, w=3840, h=2160, spp=4, desc="configs[4]: rainbow dragon stand-in (~871k tris) 3840x2160 VCM, eye 16 / light 10"),
+    "rainbow_vcm": dict(gen="rainbow", integ=VCM, w=3840, h=2160, spp=8, desc="configs[4]: rainbow dragon stand-in (~871k tris) 3840x2160 VCM, eye 16 / light 10"),
     "water_bdpt": dict(gen="water", integ=BDPT, w=1920, h=1080, spp=2, desc="configs[2]: water caustic stand-in 1920x1080 BDPT, all strategies + MIS"),
     "water_sppm": dict(gen="water_sppm", integ=SPPM, w=1024, h=1024, spp=4, desc="configs[3]: water caustic stand-in SPPM, 1024x1024 light paths per iteration"),
     "cornell": dict(gen="cornell", integ=UNI, w=512, h=512, spp=64, desc="configs[0]: Cornell box 512x512 NEE+MIS"),
@@ -214,22 +214,24 @@ def run_ours(args):
     #   striped (weak scaling)  : step i = the SAME iterations [i*S, (i+1)*S) on every rank, rank r with seed base + r - equal work per GPU
     #                             whatever N is (the VCM merge radius shrinks with the iteration index, so striding the indices over
     #                             ranks would make an N-GPU step cheaper than a 1-GPU step); the frames are N independent estimates, summed
-    def step(i, profile=0, to_host=False, do_flush=True):
-        """One step. Returns (stats, device ms of the render)."""
+    def step(i, profile=0, to_host=False, do_flush=True, first=None, count=None):
+        """One step (passes [i*S, (i+1)*S), or [first, first + count) when given). Returns (stats, device ms of the render)."""
+        first = i * S if first is None else first
+        count = S if count is None else count
         scene.set_profile(profile)
         if do_flush:
             flush.fill_(i & 0xff)      # evict L2 between steps (the working set of a step, >0.4 GB, also exceeds L2)
             torch.cuda.synchronize()
         if to_host and world == 1 and not tiles:
-            _, st = scene.render(cfg, cam, i * S, S, out=pinned.numpy())      # novum_render: renders, copies w*h*16 B to the caller's buffer
+            _, st = scene.render(cfg, cam, first, count, out=pinned.numpy())      # novum_render: renders, copies w*h*16 B to the caller's buffer
             return st, st.deviceMs
         if to_host:
             colors.zero_()
         if tiles:
-            st = tiler.render(i * S, S, colors)
+            st = tiler.render(first, count, colors)
             ms = st.deviceMs
         else:
-            st = scene.render_device(cfg, cam, i * S, S, colors.data_ptr(), seed=103033 + rank)
+            st = scene.render_device(cfg, cam, first, count, colors.data_ptr(), seed=103033 + rank)
             ms = st.deviceMs          # CUDA events on the library's own streams around the whole call
         if to_host:
             nd.reduce_frames(colors, dist, 0)
@@ -296,13 +298,24 @@ def run_ours(args):
     # + 16 B hit + 80 B x nodes + 48 B x triangles visited, nodes / triangles per ray counted live by a counted step. With
     # several lanes in flight the stages of different iterations overlap, so a stage's time is its share of the summed stage times
     # applied to the step's device time.
-    st, _ = step(10_000, profile=3)       # one counted step (slower kernel, not timed): nodes / triangles per ray
+    # The roofline figures come from their own passes, run ONE PER CALL after the timed region (the first timed step's passes again): a
+    # single pass keeps a single lane busy, so the per-stage CUDA-event times are exclusive (with several iterations in flight the
+    # stages of different iterations overlap and a stage's event time is not the time the GPU spent on it).
+    r_stage, r_closest, r_cand, r_acc, r_q, r_ms = [0.0] * 4, 0, 0, 0, 0, 0.0
+    passes_r = S if bidir else 1
+    for j in range(passes_r):
+        st, ms = (step(0, profile=1, first=args.warmup * S + j, count=1) if bidir else step(args.warmup, profile=1))
+        r_ms += ms; r_closest += st.closestRays; r_cand += st.mergeCandidates; r_acc += st.mergeAccepted; r_q += st.mergeQueries
+        for k in range(4):
+            r_stage[k] += st.stageMs[k]
+    st, _ = (step(0, profile=3, first=args.warmup * S, count=1) if bidir else step(args.warmup, profile=3))      # counted (slower) kernels: nodes / triangles per ray
     vn = st.bvhNodeVisits / max(1, st.closestRays); vt = st.triTests / max(1, st.closestRays)
     bytes_per_ray = 32 + 16 + 80 * vn + 48 * vt
     peak, peak_src = peaks()
     names = ({"extend": 0, "step+grid": 1, "resolve": 2, "merge": 3} if bidir else {"extend": 0, "shade": 1, "shadow": 2, "other": 3})
     ssum = sum(stage_ms) or 1.0
-    eff_ms = [dev_ms * x / ssum for x in stage_ms]          # this rank's wall share of each stage
+    eff_ms = r_stage
+    closest, merge_cand, merge_acc, merge_q = r_closest, r_cand, r_acc, r_q
     kc = kernel_counters() or {}
     ext_name = "bdExtend" if bidir else "wfExtend"
     ext_kc = kc.get(args.workload, {}).get(ext_name)
@@ -311,6 +324,7 @@ def run_ours(args):
             "peak": peak, "unit": "GB/s", "peak_source": peak_src,
             "bytes_per_ray": bytes_per_ray, "nodes_per_ray": vn, "tris_per_ray": vt,
             "closest_rays_per_s": closest / (eff_ms[0] * 1e-3) if eff_ms[0] > 0 else None, "ms_share": stage_ms[0] / ssum,
+            "kernel_ms_per_pass": eff_ms[0] / passes_r, "measured_on": f"{passes_r} pass(es) run one per call after the timed region (stages exclusive)",
             "traffic": ext_kc["dram_bytes_per_launch"] if ext_kc else None,
             "traffic_source": ext_kc["source"] if ext_kc else None,
             "stage_ms_share": {k: stage_ms[v] / ssum for k, v in names.items()},
@@ -348,7 +362,7 @@ def run_ours(args):
                                     f"inside the light pass ({tiler.exchange_mode}), device-side rendezvous, frames sum-reduced (NCCL) at the end"
                                     if tiles else
                                     ("striped: every rank renders the same iteration indices with its own seed (equal work per GPU), frames sum-reduced (NCCL) at the end"
-                                     if world > 1 else f"one GPU; NOVUM_LANES={os.environ.get('NOVUM_LANES', '3')} iterations in flight")),
+                                     if world > 1 else f"one GPU; NOVUM_LANES={os.environ.get('NOVUM_LANES', '4')} iterations in flight")),
                        "l2": "256 MB flush before every step; the per-step working set (path pool / vertex cache / queues, >0.4 GB) exceeds the 126 MB L2",
                        "scene_load_s": round(load_s, 3), "scene_parse_s": round(info["parse_ms"] * 1e-3, 3), "bvh8_build_ms": round(info["bvh8_build_ms"], 3),
                        "bvh8_build_launches": info["bvh8_build_launches"]},
@@ -983,7 +997,7 @@ def main():
     ap.add_argument("--spp-per-step", type=int, default=0, help="passes per step per GPU (0 = the workload's default)")
     ap.add_argument("--sharding", default=None, choices=["striped", "tiles"],
                     help="default: tiles for the bidirectional workloads at N > 1 (strong scaling: rows sharded, photons exchanged every iteration), striped otherwise")
-    ap.add_argument("--lanes", type=int, default=2, help="tiles sharding: iterations in flight per rank")
+    ap.add_argument("--lanes", type=int, default=4, help="tiles sharding: iterations in flight per rank")
     ap.add_argument("--no-relmse", action="store_true", help="skip the 1080p frame against the reference's (rainbow_vcm only)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the dragon-NEE secondary measurement (rainbow_vcm, N = 1)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="tiles sharding: photon exchange by peer stores fused into the light pass, or by an NCCL all-gather")

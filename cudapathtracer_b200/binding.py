@@ -113,6 +113,8 @@ def _declare(L):
     L.novum_scene_download.argtypes = [vp, vp, vp, vp, vp, vp]
     L.novum_scene_timings.argtypes = [vp, C.POINTER(cf), C.POINTER(cf), C.POINTER(ci)]
     L.novum_scene_bvh_depth.argtypes = [vp]
+    L.novum_scene_set_features.argtypes = [vp, ci]
+    L.novum_scene_set_environment.argtypes = [vp, C.POINTER(cf * 3)]
     L.novum_parse_double.restype = C.c_double
     L.novum_parse_double.argtypes = [C.c_char_p, C.POINTER(ci)]
     L.novum_material_table.argtypes = [vp]
@@ -269,6 +271,14 @@ class Scene:
         return {"tris": nt.value, "lights": nl.value, "bvh8_nodes": nn.value, "min": list(mn), "max": list(mx), "radius": r.value,
                 "parse_ms": pm.value, "bvh8_build_ms": bm.value, "bvh8_build_launches": bl.value,
                 "bvh8_depth": lib().novum_scene_bvh_depth(self.h)}
+
+    def set_features(self, nested_bidir=False, environment=None):
+        """Opt-in features (novum_scene_set_features): nested dielectrics in the bidirectional walks; a constant environment (rgb)."""
+        flags = (1 if nested_bidir else 0) | (2 if environment is not None else 0)
+        if environment is not None:
+            rgb = (C.c_float * 3)(*[float(x) for x in environment])
+            _check(lib().novum_scene_set_environment(self.h, C.byref(rgb)), "novum_scene_set_environment")
+        _check(lib().novum_scene_set_features(self.h, flags), "novum_scene_set_features")
 
     def download(self):
         c = [C.c_int() for _ in range(5)]

@@ -261,4 +261,29 @@ NV_D void bsdfSample(Rng& rng, const Shading& s, V3 wiToward, float etaI, bool b
     }
 }
 
+// ---- 16 x u8 medium stack held in four registers -----------------------------------------------------------
+struct MediumStack {
+    unsigned w[4]; int top;
+    NV_D int get(int i) const {
+        unsigned word = (i >> 2) == 0 ? w[0] : ((i >> 2) == 1 ? w[1] : ((i >> 2) == 2 ? w[2] : w[3]));
+        return (int)((word >> ((i & 3) * 8)) & 0xffu);
+    }
+    NV_D void set(int i, int v) {
+        unsigned sh = (i & 3) * 8, m = ~(0xffu << sh), b = ((unsigned)v & 0xffu) << sh;
+        switch (i >> 2) {
+            case 0: w[0] = (w[0] & m) | b; break;
+            case 1: w[1] = (w[1] & m) | b; break;
+            case 2: w[2] = (w[2] & m) | b; break;
+            default: w[3] = (w[3] & m) | b; break;
+        }
+    }
+    NV_D void push(int v) { if (top < 16) { set(top, v); ++top; } }
+    NV_D void remove(int mat) {           // integratorUtilities.cuh:414-434: searches down to index 1, never slot 0
+        int found = -1;
+        for (int i = top - 1; i > 0; --i) if (get(i) == mat) { found = i; break; }
+        if (found != -1) { for (int i = found; i < top - 1; ++i) set(i, get(i + 1)); --top; }
+    }
+};
+
+
 }  // namespace nv

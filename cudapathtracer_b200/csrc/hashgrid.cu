@@ -134,6 +134,15 @@ __global__ void gatherKernel(const float* __restrict__ in, const uint32_t* __res
 
 }  // namespace
 
+int hashGridPreload() {
+    cudaFuncAttributes a;
+    cudaError_t e;
+    if ((e = cudaFuncGetAttributes(&a, hashKernel)) != cudaSuccess) return (int)e;
+    if ((e = cudaFuncGetAttributes(&a, clearCellsKernel)) != cudaSuccess) return (int)e;
+    if ((e = cudaFuncGetAttributes(&a, tableKernel)) != cudaSuccess) return (int)e;
+    return (int)radixSortPreload();
+}
+
 int hashGridAlloc(HashGridDevice& g, int maxPhotons) {
     g.maxPhotons = maxPhotons;
     g.tableSize = (unsigned)nextPrime(maxPhotons * 2);     // deviceCode.cu:3283

@@ -41,6 +41,7 @@ void hashGridFree(HashGridDevice& g);
 // hashes + sorts + builds the cell tables for n photons given as SoA positions (device pointers)
 int hashGridBuild(HashGridDevice& g, const float* d_px, const float* d_py, const float* d_pz, int n, const float sceneMin[3],
                   float mergeRadius, cudaStream_t stream);
+int hashGridPreload();      // forces the module load of the grid build's kernels (and the radix sort's)
 int nextPrime(int n);
 float mergeRadiusAt(float initialRadius, float alpha, int currSample);
 

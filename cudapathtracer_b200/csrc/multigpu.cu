@@ -26,7 +26,7 @@ namespace nv {
 
 namespace {
 
-constexpr int kMultiLanes = 2;
+constexpr int kMultiLanes = 4;
 
 struct MultiGpu {
     int n = 0;

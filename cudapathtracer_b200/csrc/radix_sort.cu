@@ -171,6 +171,11 @@ __global__ void __launch_bounds__(kThreads, 2) scatterPass(const uint32_t* __res
     }
 }
 
+__global__ void copyPairs(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { kout[i] = kin[i]; vout[i] = vin[i]; }
+}
+
 // ---- exclusive scan, 2048 elements per block -------------------------------------------------
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
@@ -248,6 +253,18 @@ __global__ void __launch_bounds__(kScanThreads) scanApply(uint32_t* __restrict__
 }
 
 }  // namespace
+
+cudaError_t radixSortPreload() {
+    cudaFuncAttributes a;
+    cudaError_t e;
+    if ((e = cudaFuncGetAttributes(&a, digitHistogram)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, digitRowScan)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, scatterPass)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, copyPairs)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, scanReduce)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, scanSums)) != cudaSuccess) return e;
+    return cudaFuncGetAttributes(&a, scanApply);
+}
 
 cudaError_t exclusiveScanU32(uint32_t* data, int n, uint32_t* scratch, cudaStream_t stream, int* launches) {
     if (n <= 0) return cudaSuccess;
@@ -339,9 +356,9 @@ cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, 
         t = kin; kin = kout; kout = t;
         t = vin; vin = vout; vout = t;
     }
-    if (kin != keys) {   // odd number of passes: result sits in the alternates
-        cudaMemcpyAsync(keys, kin, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream);
-        cudaMemcpyAsync(vals, vin, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream);
+    if (kin != keys) {   // odd number of passes: result sits in the alternates (a kernel, not a copy-engine operation: see bdFillWords in vcm.cu)
+        copyPairs<<<(n + 255) / 256, 256, 0, stream>>>(kin, vin, keys, vals, n);
+        if (launches) *launches += 1;
     }
     return cudaGetLastError();
 }

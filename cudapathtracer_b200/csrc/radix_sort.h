@@ -34,6 +34,9 @@ cudaError_t radixSortPlanBind(RadixSortPlan& plan, void* d_scratch, size_t scrat
 cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, int n, int numBits,
                            cudaStream_t stream, int* launches);
 
+// forces the module load of every kernel of this file (see nv::bdPreloadKernels in vcm_host.inl)
+cudaError_t radixSortPreload();
+
 // exclusive prefix sum over u32, in place; scratch must hold >= ceil(n/2048)+1 entries
 cudaError_t exclusiveScanU32(uint32_t* data, int n, uint32_t* scratch, cudaStream_t stream, int* launches);
 

@@ -163,6 +163,8 @@ SceneView NovumScene::view() const {
     v.numTris = nTri; v.numLights = nLights; v.numMats = nMat;
     for (int k = 0; k < 3; ++k) { v.sceneMin[k] = sceneMin[k]; v.sceneCenter[k] = sceneCenter[k]; }
     v.sceneRadius = sceneRadius;
+    v.features = features;
+    for (int k = 0; k < 3; ++k) v.env[k] = envRadiance[k];
     return v;
 }
 
@@ -314,6 +316,20 @@ int novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs, 
     if (parseMs) *parseMs = s->parseMs;
     if (bvhBuildMs) *bvhBuildMs = s->bvh.buildMs;
     if (bvhLaunches) *bvhLaunches = s->bvh.kernelLaunches;
+    return 0;
+}
+
+int novum_scene_set_features(NovumScene* s, int features) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (features & ~(NOVUM_FEATURE_NESTED_BIDIR | NOVUM_FEATURE_ENVIRONMENT)) return NOVUM_E_ARG;
+    s->features = features;
+    return 0;
+}
+
+int novum_scene_set_environment(NovumScene* s, const float rgb[3]) {
+    if (!s) return NOVUM_E_NOSCENE;
+    if (!rgb || !(rgb[0] >= 0.0f && rgb[1] >= 0.0f && rgb[2] >= 0.0f) || !std::isfinite(rgb[0] + rgb[1] + rgb[2])) return NOVUM_E_ARG;
+    for (int k = 0; k < 3; ++k) s->envRadiance[k] = rgb[k];
     return 0;
 }
 

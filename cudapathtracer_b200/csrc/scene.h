@@ -41,6 +41,7 @@ struct NovumScene {
     void* vcmEngine = nullptr; void (*vcmEngineFree)(void*) = nullptr;
     void* d_frame = nullptr; size_t frameBytes = 0;     // device framebuffer of novum_render, kept across calls
     int device = 0;                                     // the CUDA device the scene lives on
+    int features = 0; float envRadiance[3] = {0.f, 0.f, 0.f};   // novum_scene_set_features / _set_environment
     void* multiGpu = nullptr; void (*multiGpuFree)(void*) = nullptr;   // replicas + per-GPU engines of the in-process multi-GPU launch (multigpu.cu)
 
     nv::SceneView view() const;

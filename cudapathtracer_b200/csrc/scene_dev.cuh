@@ -21,7 +21,11 @@ struct SceneView {
     float sceneMin[3];
     float sceneRadius;
     float sceneCenter[3];
+    // opt-in features beyond what the reference implements (novum_scene_set_features; all off by default)
+    int features;
+    float env[3];                               // constant environment radiance (FEAT_ENVIRONMENT)
 };
+enum : int { FEAT_NESTED_BIDIR = 1, FEAT_ENVIRONMENT = 2 };
 
 // what BVHSceneIntersect fills into `Intersection` (objects.cuh:550-568), minus the unused colour
 struct Surface {

@@ -96,14 +96,24 @@ struct BdPath {
     V3 o, d, beta, prevP;
     float pdfPrevSA, prevCos, pdfOneBefore, d_vcm, d_vc, d_vm, aux;
     bool prevDelta;
+    int nReal;                 // FEAT_NESTED_BIDIR: surface vertices this walk has made so far (a false hit consumes a step, not a vertex)
+    MediumStack ms;            // FEAT_NESTED_BIDIR: dielectric media the walk is inside of (material ids; slot 0 = air)
     Rng rng;
 };
+// FEAT_NESTED_BIDIR state: 15 stack entries + the height in the top byte of the fourth word
+NV_D void loadBdMedium(const BdState& st, int l, BdPath& p) {
+    const uint4 m = st.medium[l];
+    p.ms.w[0] = m.x; p.ms.w[1] = m.y; p.ms.w[2] = m.z; p.ms.w[3] = m.w & 0x00ffffffu; p.ms.top = (int)(m.w >> 24);
+}
+NV_D void storeBdMedium(const BdState& st, int l, const BdPath& p) {
+    st.medium[l] = make_uint4(p.ms.w[0], p.ms.w[1], p.ms.w[2], (p.ms.w[3] & 0x00ffffffu) | ((unsigned)p.ms.top << 24));
+}
 NV_D void loadBdPath(const BdState& st, int l, BdPath& p) {
     float4 a = st.rayO[l], b = st.rayD[l], c = st.beta[l], e = st.prevP[l], f = st.dv[l];
     p.o = V3(a.x, a.y, a.z); p.pdfPrevSA = a.w;
     p.d = V3(b.x, b.y, b.z); p.prevCos = b.w;
     p.beta = V3(c.x, c.y, c.z); p.pdfOneBefore = c.w;
-    p.prevP = V3(e.x, e.y, e.z); p.prevDelta = (__float_as_uint(e.w) & 1u) != 0;
+    p.prevP = V3(e.x, e.y, e.z); p.prevDelta = (__float_as_uint(e.w) & 1u) != 0; p.nReal = (int)((__float_as_uint(e.w) >> 8) & 0xffu);
     p.d_vcm = f.x; p.d_vc = f.y; p.d_vm = f.z; p.aux = f.w;
     p.rng.state = st.rng[l];
 }
@@ -111,7 +121,7 @@ NV_D void storeBdPath(const BdState& st, int l, const BdPath& p) {
     st.rayO[l] = make_float4(p.o.x, p.o.y, p.o.z, p.pdfPrevSA);
     st.rayD[l] = make_float4(p.d.x, p.d.y, p.d.z, p.prevCos);
     st.beta[l] = make_float4(p.beta.x, p.beta.y, p.beta.z, p.pdfOneBefore);
-    st.prevP[l] = make_float4(p.prevP.x, p.prevP.y, p.prevP.z, __uint_as_float(p.prevDelta ? 1u : 0u));
+    st.prevP[l] = make_float4(p.prevP.x, p.prevP.y, p.prevP.z, __uint_as_float((p.prevDelta ? 1u : 0u) | (((unsigned)p.nReal & 0xffu) << 8)));
     st.dv[l] = make_float4(p.d_vcm, p.d_vc, p.d_vm, p.aux);
     st.rng[l] = p.rng.state;
 }
@@ -229,8 +239,9 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStart(SceneView sc, BdState
             p.prevCos = fabsf(dot(normalize(dirW), n0));
             p.pdfPrevSA = P.mode == BD_MODE_BDPT ? p.prevCos / kPi : pdfSA;       // :1101 vs :2010
             p.pdfOneBefore = -1.0f; p.prevP = y0; p.prevDelta = false;
-            p.d_vcm = p.d_vc = p.d_vm = -1.0f; p.aux = pdfPos;
+            p.d_vcm = p.d_vc = p.d_vm = -1.0f; p.aux = pdfPos; p.nReal = 0;
             storeBdPath(st, l, p);
+            if (st.medium) st.medium[l] = make_uint4(0u, 0u, 0u, 1u << 24);          // in air (material 0), as Li_unidirectional starts (:308)
             active = true;
             if (P.mode == BD_MODE_BDPT && P.lightTrace) {      // s = 1, t = 1: the sampled light point seen directly by the camera (:1357-1389)
                 LightVtx v; v.p = y0; v.n = n0; v.wo = V3(0.0f); v.beta = p.beta; v.uv = make_float2(0.f, 0.f); v.delta = false; v.backface = false;
@@ -266,20 +277,48 @@ __global__ void __launch_bounds__(kBdThreads) bdExtend(SceneView sc, BdState st,
 // vertex processing shared by both walks: forward area pdf, BSDF sample, reverse pdf, d_vcm / d_vc / d_vm recurrences
 struct StepOut { Surface s; Shading sh; V3 woL, wiL, wiW, currBeta; float d_vcm, d_vc, d_vm; bool delta; };
 
-NV_D bool walkVertex(const SceneView& sc, const BdParams& P, BdPath& p, const float4 hf, bool lightWalk, bool first, StepOut& o) {
+// Returns WALK_END, WALK_VERTEX or - NESTED only - WALK_THROUGH: a false hit on a dielectric interface of lower priority than the medium
+// the walk is in (deviceCode.cu:413-425 in Li_unidirectional): the medium stack is updated, the ray goes on from the hit point, no vertex
+// is made. NESTED is FEAT_NESTED_BIDIR: the walk carries the medium stack, attenuates by the dominant medium's absorption along the
+// segment (:347-358), hands the dominant medium's index of refraction to the BSDFs as the incident one (:359) and pushes / pops media on
+// refraction (:484-497) - exactly what shadeMIS does for the unidirectional integrator. Without it the reference's placeholders stand
+// (etaI = etaT = 1, deviceCode.cu:851-852, 1177-1178, 2078-2079).
+enum : int { WALK_END = 0, WALK_VERTEX = 1, WALK_THROUGH = 2 };
+template <bool NESTED>
+NV_D int walkVertex(const SceneView& sc, const BdParams& P, BdPath& p, const float4 hf, bool lightWalk, bool first, StepOut& o) {
     HitRec h; h.tri = __float_as_int(hf.x); h.t = hf.y; h.u = hf.z; h.v = hf.w; h.flags = 0;
     o.s = makeSurface(sc, h, p.o, p.d);
     o.sh = resolveShading(sc.mats, o.s.mat, sc.textures, o.s.uv);
     o.delta = (o.sh.m.flags & MF_SPECULAR) != 0;
+    float etaI = 1.0f;
+    if (NESTED) {
+        int minId = p.ms.get(0);
+        int minPr = __ldg(&sc.mats[minId].priority);
+        for (int i = 1; i < p.ms.top; ++i) {
+            const int id = p.ms.get(i), pr = __ldg(&sc.mats[id].priority);
+            if (pr < minPr) { minPr = pr; minId = id; }
+        }
+        const MatView dom = loadMat(sc.mats, minId);
+        if (o.s.dist > kEps) p.beta *= V3(expf(-dom.absorption.x * o.s.dist), expf(-dom.absorption.y * o.s.dist), expf(-dom.absorption.z * o.s.dist));
+        etaI = dom.ior;
+        if ((o.sh.m.flags & MF_BOUNDARY) && o.sh.m.priority > minPr) {
+            if (!o.s.backface) { if (p.ms.top < 15) p.ms.push(o.s.mat); } else p.ms.remove(o.s.mat);
+            p.o = o.s.p + p.d * kRayEps;
+            return WALK_THROUGH;
+        }
+    }
     Frame fr(o.s.n);
     o.woL = fr.toLocal(p.d);
     float distSq = fmaxf(lengthSq(o.s.p - p.prevP), kRayEps);
     float pdfFwdArea = p.pdfPrevSA * fabsf(o.woL.z) / distSq;
     V3 f; float pdfFwdSA;
-    bsdfSample(p.rng, o.sh, o.woL, 1.0f, o.s.backface, lightWalk ? MODE_IMPORTANCE : MODE_RADIANCE, o.wiL, f, pdfFwdSA);
+    bsdfSample(p.rng, o.sh, o.woL, etaI, o.s.backface, lightWalk ? MODE_IMPORTANCE : MODE_RADIANCE, o.wiL, f, pdfFwdSA);
     o.wiW = fr.toWorld(o.wiL);
-    float pdfRevSA = bdPdf(o.sh, -o.wiL, -o.woL, 1.0f);
-    if (pdfFwdSA < kEps) return false;
+    float pdfRevSA = bdPdf(o.sh, -o.wiL, -o.woL, etaI);
+    if (NESTED && pdfFwdSA >= kEps && o.wiL.z < 0.0f) {        // refracted (or transmitted): enter / leave the medium
+        if (!o.s.backface) { if (p.ms.top < 15) p.ms.push(o.s.mat); } else p.ms.remove(o.s.mat);
+    }
+    if (pdfFwdSA < kEps) return WALK_END;
     o.currBeta = p.beta;
     p.beta = p.beta * f * (fabsf(o.wiL.z) / pdfFwdSA);
     const float eta = P.etaVcm;                   // 0 in BDPT mode
@@ -307,9 +346,10 @@ NV_D bool walkVertex(const SceneView& sc, const BdParams& P, BdPath& p, const fl
     p.pdfOneBefore = pdfRevSA;
     p.pdfPrevSA = pdfFwdSA;
     p.prevCos = fabsf(o.wiL.z);
-    return true;
+    return WALK_VERTEX;
 }
 
+template <bool NESTED>
 __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState st, BdParams P, int step, int numSteps,
                                                          const int* __restrict__ queue, int* __restrict__ nextQueue) {
     const int lane = bdLane();
@@ -334,14 +374,22 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState 
             float4 hf = st.hit[l];
             if (__float_as_int(hf.x) >= 0) {
                 BdPath p; loadBdPath(st, l, p);
+                if (NESTED) loadBdMedium(st, l, p);
                 V3 inDir = p.d;
                 StepOut o;
-                if (walkVertex(sc, P, p, hf, true, step == 0, o)) {
+                // vertex number of this path: the step, unless false hits (NESTED) have used up steps without making vertices
+                const int vi = NESTED ? st.pathLen[l] : step;
+                const int status = walkVertex<NESTED>(sc, P, p, hf, true, vi == 0, o);
+                if (NESTED && status == WALK_THROUGH) {
+                    cont = step + 1 < numSteps;
+                    if (cont) { storeBdPath(st, l, p); storeBdMedium(st, l, p); }
+                }
+                if (status == WALK_VERTEX) {
                     LightVtx v;
                     v.p = o.s.p; v.n = o.s.n; v.wo = normalize(-inDir); v.beta = o.currBeta; v.uv = o.s.uv;
                     v.delta = o.delta; v.backface = o.s.backface; v.mat = o.s.mat; v.d_vc = o.d_vc; v.d_vcm = o.d_vcm;
-                    storeLightVtx(st, (size_t)step * P.nLocal + l, v);           // v now holds the quantised values
-                    st.pathLen[l] = step + 1;
+                    storeLightVtx(st, (size_t)vi * P.nLocal + l, v);             // v now holds the quantised values
+                    st.pathLen[l] = vi + 1;
                     ++nVerts;
                     if (!o.delta && P.mode == BD_MODE_VCM && P.doMerge) {        // photon for merging (:2206-2221)
                         wantPhoton = true;
@@ -354,7 +402,7 @@ __global__ void __launch_bounds__(kBdThreads) bdLightStep(SceneView sc, BdState 
                     p.d = o.wiW;
                     p.prevDelta = o.delta; p.prevP = o.s.p;
                     cont = step + 1 < numSteps;
-                    if (cont) storeBdPath(st, l, p);
+                    if (cont) { storeBdPath(st, l, p); if (NESTED) storeBdMedium(st, l, p); }
                 }
             }
         }
@@ -421,13 +469,15 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStart(BdState st, BdParams P)
         p.beta = V3(1.0f); p.pdfOneBefore = -1.0f;
         p.prevP = camOrg(P.cam);
         p.prevDelta = P.mode == BD_MODE_VCM;        // :2719 (true) vs :792 (false)
-        p.d_vcm = p.d_vc = p.d_vm = -1.0f; p.aux = 0.f;
+        p.d_vcm = p.d_vc = p.d_vm = -1.0f; p.aux = 0.f; p.nReal = 0;
         storeBdPath(st, l, p);
+        if (st.medium) st.medium[l] = make_uint4(0u, 0u, 0u, 1u << 24);
     }
     int pos = bdWarpAppend(&st.counters[BC_QUEUE], active);
     if (active) st.queue[0][pos] = l;
 }
 
+template <bool NESTED>
 __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st, BdParams P, int step, int numSteps,
                                                        const int* __restrict__ queue, int* __restrict__ nextQueue, MergeQueue mq) {
     const int lane = bdLane();
@@ -447,12 +497,31 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
         if (i < n) {
             l = __ldg(queue + i);
             float4 hf = st.hit[l];
-            if (__float_as_int(hf.x) >= 0) {
+            if (__float_as_int(hf.x) < 0) {
+                // left the scene. FEAT_ENVIRONMENT: the escape is the s = 0 strategy for the constant environment and, as nothing samples
+                // the environment from the light side, the only one (weight 1); it is switched with the other implicit hits (BDPT_NAIVE)
+                if ((sc.features & FEAT_ENVIRONMENT) && P.naive) {
+                    const float4 b = st.beta[l];
+                    const V3 c = V3(b.x, b.y, b.z) * V3(sc.env[0], sc.env[1], sc.env[2]);
+                    int x, y;
+                    const int pix = localToPixel(P, l, x, y);
+                    if ((c.x != 0.0f || c.y != 0.0f || c.z != 0.0f) && isfinite(c.x) && isfinite(c.y) && isfinite(c.z))
+                        atomicAdd(&P.colors[pix], make_float4(c.x, c.y, c.z, 0.f));
+                }
+            } else {
                 BdPath p; loadBdPath(st, l, p);
+                if (NESTED) loadBdMedium(st, l, p);
                 const V3 inDir = p.d, prevP = p.prevP;
                 const bool prevDelta = p.prevDelta;
                 StepOut o;
-                if (walkVertex(sc, P, p, hf, false, step == 0, o)) {
+                const bool firstVertex = NESTED ? p.nReal == 0 : step == 0;
+                const int status = walkVertex<NESTED>(sc, P, p, hf, false, firstVertex, o);
+                if (NESTED && status == WALK_THROUGH) {
+                    cont = step + 1 < numSteps;
+                    if (cont) { storeBdPath(st, l, p); storeBdMedium(st, l, p); }
+                }
+                if (status == WALK_VERTEX) {
+                    if (NESTED) ++p.nReal;
                     int x, y;
                     const int pix = localToPixel(P, l, x, y);
                     const Surface& s = o.s;
@@ -478,7 +547,7 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                                 float cosLight = dot(s.n, normalize(prevP - s.p));
                                 float pdfConnect = prevDelta ? 0.0f : pdfChoose / area;
                                 w = 1.0f / (1.0f + pdfConnect * o.d_vcm + pdfConnect * (cosLight / kPi) * o.d_vc);
-                            } else if (step == 0) {                                              // t == 2 :1567-1595
+                            } else if (firstVertex) {                                            // t == 2 :1567-1595
                                 V3 lightToPrevU = normalize(-inDir);
                                 float cosThetaLight = fabsf(dot(s.n, lightToPrevU));
                                 float cosAtCamera = fabsf(dot(camFwd(P.cam), -lightToPrevU));
@@ -593,7 +662,7 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
                     p.d = vcm ? o.wiW : normalize(o.wiW);                                        // :3056 vs :944
                     p.prevDelta = o.delta; p.prevP = s.p;
                     cont = !endPath && step + 1 < numSteps;
-                    if (cont) storeBdPath(st, l, p);
+                    if (cont) { storeBdPath(st, l, p); if (NESTED) storeBdMedium(st, l, p); }
                 }
             }
         }
@@ -948,10 +1017,28 @@ __global__ void bdWaitSlabs(const uint4* __restrict__ slabs, size_t slabWords, i
     __threadfence_system();
 }
 
+// Clears inside an iteration are KERNELS, and the photon counts reach the host through mapped page-locked memory, not a copy: with
+// several lanes and ranks waiting on each other on the device (bdWaitSlabs), a cudaMemsetAsync / cudaMemcpyAsync of one lane can sit in
+// the copy engine's queue behind another lane's copy that waits for a peer, whose own clear sits behind ITS other lane's copy ...
+// (a cross-rank, cross-lane cycle that only the wait kernel's time-out broke: seen at 8 x 3 lanes and at 4 x 2 lanes).
+__global__ void bdFillWords(uint4* __restrict__ p, size_t n16, unsigned v) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) p[i] = make_uint4(v, v, v, v);
+}
+
+__global__ void bdZeroInts(int* __restrict__ p, int n) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = 0;
+}
+
 // ---- photon slabs -> contiguous array -> cell order -----------------------------------------------------------------------------
-__global__ void bdSlabCounts(const uint4* __restrict__ slabs, size_t slabWords, int world, int cap, int* __restrict__ counts) {
+// counts[0, 16): photons per slab; hostCounts (mapped page-locked memory) receives them and the wait kernel's time-out flag
+__global__ void bdSlabCounts(const uint4* __restrict__ slabs, size_t slabWords, int world, int cap, int* __restrict__ counts,
+                             int* __restrict__ hostCounts) {
     int r = threadIdx.x;
-    if (r < world) counts[r] = min(*reinterpret_cast<const int*>(slabs + (size_t)r * slabWords), cap);
+    int c = 0;
+    if (r < world) { c = min(*reinterpret_cast<const int*>(slabs + (size_t)r * slabWords), cap); counts[r] = c; }
+    if (r < 16) hostCounts[r] = c;
+    if (r == 16) hostCounts[16] = counts[16];
+    __threadfence_system();
 }
 __global__ void bdCompactSlabs(const uint4* __restrict__ slabs, size_t slabWords, int world, const int* __restrict__ counts,
                                uint4* __restrict__ out) {

@@ -73,6 +73,7 @@ struct BdState {
     float4* hit;       // bits tri, t, u, v
     int* queue[2];
     int* pathLen;      // surface vertices stored per light path
+    uint4* medium;     // FEAT_NESTED_BIDIR only (else null): per path, the 15 x u8 medium stack of the walk + its height in the top byte
     uint4 *lvA, *lvB, *lvC;
     BdShadowRec* shadowQ;
     BdMergeRec* mergeQ;         // (1 + kMergeGroup) * nLocal records: [0, nLocal) step 0, the rest the current group of deeper steps

@@ -27,7 +27,7 @@ struct BdEngine {
     int maxPhotons = 0, photonCount = 0;
     HashGridDevice grid;
     bool gridAllocated = false;
-    int* d_counts = nullptr; int* h_counts = nullptr;
+    int* d_counts = nullptr; int* h_counts = nullptr; int* h_countsDev = nullptr;      // h_counts: mapped page-locked, h_countsDev its device address
     float mergeRadius = 0.f;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     unsigned long long launches = 0, iterations = 0;
@@ -51,7 +51,7 @@ static void bdTick(BdEngine& e, int cls) {
 static void bdFree(BdEngine& e) {
     BdState& s = e.st;
     cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.dv); cudaFree(s.rng); cudaFree(s.hit);
-    cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
+    cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.medium); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
     cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.mergeOrder); cudaFree(s.mergeBinCount); cudaFree(s.counters); cudaFree(s.stats);
     for (int r = 0; r < 16; ++r) if (e.peerBase[r] && e.peerIpc[r]) cudaIpcCloseMemHandle(e.peerBase[r]);
     cudaFree(e.slabs); cudaFree(e.photonsAll); cudaFree(e.photonsSorted); cudaFree(e.d_counts);
@@ -116,7 +116,8 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     }
     A((void**)&e.d_counts, 32 * sizeof(int));        // [0, 16): photons per slab, [16]: bdWaitSlabs gave up (1 + rank it waited for)
     if (err != cudaSuccess) return (int)err;
-    if ((err = cudaHostAlloc((void**)&e.h_counts, 32 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess) return (int)err;
+    if ((err = cudaHostAlloc((void**)&e.h_counts, 32 * sizeof(int), cudaHostAllocMapped)) != cudaSuccess) return (int)err;
+    if ((err = cudaHostGetDevicePointer((void**)&e.h_countsDev, e.h_counts, 0)) != cudaSuccess) return (int)err;
     memset(e.h_counts, 0, 32 * sizeof(int));               // page-locked memory arrives uninitialised; [16] is read as the time-out flag
     cudaMemsetAsync(e.d_counts, 0, 32 * sizeof(int), e.stream);
     if (e.mode == BD_MODE_VCM) {
@@ -171,6 +172,7 @@ static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
 namespace nv {
 
 static inline int bdGrid() { return smCount() * 8; }
+static inline bool bdNested(const BdEngine& e) { return (e.scene->features & NOVUM_FEATURE_NESTED_BIDIR) != 0; }
 
 // bdMergeLambert<MIS>: 4 eye vertices per warp, register allocation held to 64 (8 resident CTAs of 128 threads per SM)
 static void launchMergeLambert(bool mis, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P, const MergeQueue& mq) {
@@ -186,10 +188,16 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
     BdParams P = bdParams(e, iter, colors);
     SceneView sc = e.scene->view();
     e.mergeRadius = P.mergeRadius;
-    cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
-    cudaMemsetAsync(P.slab, 0, kSlabHeaderBytes, s);                      // photon counter of this rank (deviceCode.cu:3330)
+    const bool nested = bdNested(e);
+    if (nested && !st.medium) {          // the walks' medium stacks exist only once the feature has been asked for
+        cudaError_t me = cudaMalloc((void**)&st.medium, sizeof(uint4) * (size_t)(e.nLocal > 0 ? e.nLocal : 1));
+        if (me != cudaSuccess) return (int)me;
+    }
+    bdFillWords<<<2, 256, 0, s>>>(reinterpret_cast<uint4*>(st.counters), (size_t)(kMaxBdDepth + 1) * BC_STRIDE * sizeof(int) / 16, 0u);
+    bdFillWords<<<1, 32, 0, s>>>(P.slab, kSlabHeaderBytes / 16, 0u);          // photon counter of this rank (deviceCode.cu:3330)
     const bool publish = P.numPeers > 0 || e.slabBuffers > 1;       // lane engines stamp their own header too (bdWaitSlabs reads all of them)
     if (e.nLocal == 0 || sc.numLights == 0) {
+        if (e.nLocal > 0) { bdZeroInts<<<bdGrid(), 256, 0, s>>>(st.pathLen, e.nLocal); ++e.launches; }      // no light: no light vertices to connect to
         if (publish) { bdPushHeader<<<1, 32, 0, s>>>(P); ++e.launches; }
         return (int)cudaGetLastError();
     }
@@ -204,7 +212,8 @@ static int bdLightPass(BdEngine& e, int iter, float4* colors) {
         if (e.profCount) bdExtend<true><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
         else bdExtend<false><<<grid, kBdThreads, 0, s>>>(sc, st, st.queue[step & 1], cnt, tc);
         bdTick(e, 0);
-        bdLightStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
+        if (nested) bdLightStep<true><<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
+        else bdLightStep<false><<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1]);
         bdTick(e, 1);
         if (P.lightTrace) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; bdTick(e, 2); }
         e.launches += 2;
@@ -221,9 +230,8 @@ static int bdBuildGrid(BdEngine& e, int iter) {
     BdParams P = bdParams(e, iter, nullptr);
     if (!P.doMerge || P.mergeRadius <= 0.0f) { e.photonCount = 0; return 0; }
     const uint4* slabs = e.slabs + (size_t)e.slabBuf * e.world * e.slabWords;
-    bdSlabCounts<<<1, 32, 0, s>>>(slabs, e.slabWords, e.world, e.slabCap, e.d_counts);
+    bdSlabCounts<<<1, 32, 0, s>>>(slabs, e.slabWords, e.world, e.slabCap, e.d_counts, e.h_countsDev);
     ++e.launches;
-    cudaMemcpyAsync(e.h_counts, e.d_counts, 32 * sizeof(int), cudaMemcpyDeviceToHost, s);
     cudaError_t err = cudaStreamSynchronize(s);           // the reference blocks on the same counter (deviceCode.cu:3352)
     if (err != cudaSuccess) return (int)err;
     if (e.h_counts[16]) return NOVUM_E_TIMEOUT;          // a peer never published its light pass
@@ -256,7 +264,8 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
     BdParams P = bdParams(e, iter, colors);
     SceneView sc = e.scene->view();
     if (e.nLocal == 0) return 0;
-    cudaMemsetAsync(st.counters, 0, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int), s);
+    const bool nested = bdNested(e) && st.medium != nullptr;
+    bdFillWords<<<2, 256, 0, s>>>(reinterpret_cast<uint4*>(st.counters), (size_t)(kMaxBdDepth + 1) * BC_STRIDE * sizeof(int) / 16, 0u);
     const int numSteps = e.mode == BD_MODE_BDPT ? e.eyeDepth - 1 : e.eyeDepth;          // :794 vs :2723
     bdTick(e, 1);
     bdEyeStart<<<(e.nLocal + kBdThreads - 1) / kBdThreads, kBdThreads, 0, s>>>(st, P);
@@ -279,13 +288,14 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
         mq.cap = grouped ? kMergeGroup * e.nLocal : e.nLocal;
         mq.cnt = st.counters + groupFirst * BC_STRIDE;
         mq.order = nullptr;
-        bdEyeStep<<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1], mq);
+        if (nested) bdEyeStep<true><<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1], mq);
+        else bdEyeStep<false><<<grid, kBdThreads, 0, s>>>(sc, st, P, step, numSteps, st.queue[step & 1], st.queue[(step + 1) & 1], mq);
         bdTick(e, 1);
         if (shadows) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; bdTick(e, 2); }
         const bool flush = !grouped || step == groupFirst + kMergeGroup - 1 || step == numSteps - 1;
         if (merging && flush) {
             if (!P.paintWeight) {      // every Lambert queue is binned: records of one cell become neighbours (primary hits: -10 % pairs scanned)
-                cudaMemsetAsync(st.mergeBinCount, 0, kMergeBins * sizeof(uint32_t), s);
+                bdFillWords<<<bdGrid(), 256, 0, s>>>(reinterpret_cast<uint4*>(st.mergeBinCount), (size_t)kMergeBins * sizeof(uint32_t) / 16, 0u);
                 bdMergeBinCount<<<grid, 256, 0, s>>>(mq, P.bins, P.grid, st.mergeBinCount);
                 int scanLaunches = 0;
                 exclusiveScanU32(st.mergeBinCount, kMergeBins, st.mergeBinCount + kMergeBins, s, &scanLaunches);
@@ -435,12 +445,30 @@ static void tileFree(TileRank* t) {
 }
 static void tileEngineFree(void* p) { tileFree((TileRank*)p); }
 
+// CUDA loads a kernel's code on its first launch, and that load may need every running kernel of the context to finish (lazy module
+// loading). A lane that spins in bdWaitSlabs while ANOTHER lane of the same GPU launches a kernel for the first time would then never
+// see that launch start: the lane behind it never publishes its light pass and the ranks waiting for it time out (seen in the first,
+// warm-up step at 4 x 3 and 8 x 4 lanes). So every kernel of an iteration is loaded before the first device-side wait can exist.
+static int bdPreloadKernels() {
+    cudaFuncAttributes a;
+    cudaError_t e = cudaSuccess;
+    auto L = [&](const void* f) { if (e == cudaSuccess) e = cudaFuncGetAttributes(&a, f); };
+    L((const void*)bdFillWords); L((const void*)bdZeroInts); L((const void*)bdLightStart); L((const void*)bdExtend<false>); L((const void*)bdExtend<true>);
+    L((const void*)bdLightStep<false>); L((const void*)bdLightStep<true>); L((const void*)bdResolve); L((const void*)bdPushHeader); L((const void*)bdWaitSlabs); L((const void*)bdSlabCounts);
+    L((const void*)bdCompactSlabs); L((const void*)bdReorderPhotons); L((const void*)bdEyeStart); L((const void*)bdEyeStep<false>); L((const void*)bdEyeStep<true>);
+    L((const void*)bdMergeBinCount); L((const void*)bdMergeBinScatter); L((const void*)bdMergeLambert<true>); L((const void*)bdMergeLambert<false>);
+    L((const void*)bdMerge);
+    if (e != cudaSuccess) return (int)e;
+    return hashGridPreload();
+}
+
 static int tileCreate(NovumScene* s, const NovumRenderConfig& cfg, const NovumCamera& cam, NovumShard shard, unsigned long long seed, int lanes,
                       TileRank** out) {
+    int rc = bdPreloadKernels();
+    if (rc) return rc;
     TileRank* t = new TileRank();
     t->scene = s; t->rank = shard.rank; t->world = shard.world;
     cudaGetDevice(&t->device);
-    int rc = 0;
     for (int k = 0; k < lanes; ++k) {
         BdEngine* e = new BdEngine();
         rc = bdAlloc(*e, s, cfg, cam, shard, seed, /*lane=*/true);
@@ -461,11 +489,12 @@ static int tileCreate(NovumScene* s, const NovumRenderConfig& cfg, const NovumCa
     return 0;
 }
 
-// iterations in flight of the single-call render (novum_render_device): NOVUM_LANES in the environment, default 3
-// (4K VCM on one B200: 49.6 / 45.1 / 44.1 / 43.8 ms per iteration with 1 / 2 / 3 / 4 lanes; a lane costs 16 GB there)
+// iterations in flight of the single-call render (novum_render_device): NOVUM_LANES in the environment, default 4
+// (4K VCM on one B200, 20 iterations per call: 49.6 / 45.1 / 44.1 / 43.8 ms per iteration with 1 / 2 / 3 / 4 lanes; a lane costs 16 GB
+// there; a call of k iterations keeps min(k, lanes) busy, so callers should hand over several iterations at a time)
 static int defaultLanes() {
     const char* e = getenv("NOVUM_LANES");
-    int n = e ? atoi(e) : 3;
+    int n = e ? atoi(e) : 4;
     return n < 1 ? 1 : (n > 8 ? 8 : n);
 }
 

@@ -77,7 +77,12 @@ __global__ void __launch_bounds__(256) wfBinScatter(WfState st, int* __restrict_
 // first iteration: every slot is handed to the regeneration class
 __global__ void wfInit(WfState st, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) st.classQ[CLS_REGEN * st.capacity + i] = i;
+    if (i < n) {
+        st.classQ[CLS_REGEN * st.capacity + i] = i;
+        // every slot starts in the regeneration class, which is also where a path that left the scene ends: a zero throughput says
+        // "nothing escaped from here" when the environment feature looks at the slot (wfShade)
+        st.slots[(size_t)i * kSlotWords + W_BETA] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     if (i == 0) {
         for (int c = 0; c < C_TOTAL; ++c) st.counters[c] = 0;
         st.counters[C_CLASS_COUNT + CLS_REGEN] = n;

@@ -6,30 +6,6 @@
 
 namespace nv {
 
-// ---- 16 x u8 medium stack held in four registers -----------------------------------------------------------
-struct MediumStack {
-    unsigned w[4]; int top;
-    NV_D int get(int i) const {
-        unsigned word = (i >> 2) == 0 ? w[0] : ((i >> 2) == 1 ? w[1] : ((i >> 2) == 2 ? w[2] : w[3]));
-        return (int)((word >> ((i & 3) * 8)) & 0xffu);
-    }
-    NV_D void set(int i, int v) {
-        unsigned sh = (i & 3) * 8, m = ~(0xffu << sh), b = ((unsigned)v & 0xffu) << sh;
-        switch (i >> 2) {
-            case 0: w[0] = (w[0] & m) | b; break;
-            case 1: w[1] = (w[1] & m) | b; break;
-            case 2: w[2] = (w[2] & m) | b; break;
-            default: w[3] = (w[3] & m) | b; break;
-        }
-    }
-    NV_D void push(int v) { if (top < 16) { set(top, v); ++top; } }
-    NV_D void remove(int mat) {           // integratorUtilities.cuh:414-434: searches down to index 1, never slot 0
-        int found = -1;
-        for (int i = top - 1; i > 0; --i) if (get(i) == mat) { found = i; break; }
-        if (found != -1) { for (int i = found; i < top - 1; ++i) set(i, get(i + 1)); --top; }
-    }
-};
-
 struct PathRegs {
     V3 o, d, beta, prevP;
     float pdf;
@@ -261,7 +237,13 @@ __global__ void __launch_bounds__(kWfThreads, NOVUM_SHADE_MINB) wfShade(SceneVie
             alive = P.naive ? shadeNaive(sc, P, p, h) : shadeMIS(sc, st, P, p, h, h.flags);
             if (!alive) ++finished;
         } else if (valid && cls == CLS_REGEN) {
-            // missed the scene: sampleSky is black (integratorUtilities.cuh:438); slots of the first iteration land here too
+            // missed the scene: sampleSky is black (integratorUtilities.cuh:438); slots of the first iteration land here too.
+            // FEAT_ENVIRONMENT: the escaping path collects the constant environment radiance. No strategy samples the environment from
+            // the light side, so this is the only way such a path is found: full weight.
+            if (sc.features & FEAT_ENVIRONMENT) {
+                const float4 b = st.slots[(size_t)slot * kSlotWords + W_BETA];
+                if (b.x != 0.0f || b.y != 0.0f || b.z != 0.0f) addColor(P.colors, __float_as_int(b.w), V3(b.x, b.y, b.z) * V3(sc.env[0], sc.env[1], sc.env[2]));
+            }
         }
         // regeneration: dead lanes pull new path ids until they get a pixel inside the image or the work runs out
         bool need = valid && !alive;

@@ -170,7 +170,7 @@ class TileRenderer:
     are swapped once as CUDA IPC handles over the process group) and the per-iteration rendezvous is a device-side wait on stamps in
     the slab headers. torch.distributed only carries the handles and the barriers around set-up and tear-down."""
 
-    def __init__(self, scene, cfg, cam, dist=None, seed=103033, lanes=2):
+    def __init__(self, scene, cfg, cam, dist=None, seed=103033, lanes=4):
         import torch
         self.torch, self.dist = torch, dist
         self.rank, self.world = shard_of(dist)

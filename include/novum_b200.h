@@ -201,6 +201,20 @@ int  novum_scene_info(const NovumScene* s, int* nTri, int* nLights, int* nBvh8No
 /* the step before the path: host time of the config / OBJ front end (main.cu:936-1068 equivalent; 0 unless the scene came
  * from novum_scene_load_config) and CUDA-event time + launch count of the device BVH8 build that replaces main.cu:20-233 */
 int  novum_scene_timings(const NovumScene* s, float* parseMs, float* bvhBuildMs, int* bvhLaunches);
+/* ---- opt-in features the reference only half-implements. All OFF by default: with them off every integrator
+ * reproduces the reference's behaviour (and the goldens); they change results, so a caller switches them on deliberately.
+ *   NOVUM_FEATURE_NESTED_BIDIR  the nested-dielectric priority stack (Beer-Lambert absorption through the dominant medium, false hits
+ *                               on lower-priority interfaces, incident index of refraction of the dominant medium) inside the BDPT / VCM /
+ *                               SPPM walks, as Li_unidirectional has it (deviceCode.cu:296-425, 484-497). The reference leaves
+ *                               `etaI = etaT = 1.0f // TEMPORARY` there (deviceCode.cu:851-852, 1177-1178, 2078-2079).
+ *   NOVUM_FEATURE_ENVIRONMENT   a constant-radiance environment (novum_scene_set_environment): a path that leaves the scene collects it,
+ *                               in every integrator. The reference's sampleSky returns black (integratorUtilities.cuh:436-461) and its
+ *                               bidirectional environment strategy is "currently unimplemented" (deviceCode.cu:1539-1542). No strategy
+ *                               samples the environment from the light side, so the escape is the only strategy for those paths (MIS weight 1). */
+#define NOVUM_FEATURE_NESTED_BIDIR 1
+#define NOVUM_FEATURE_ENVIRONMENT  2
+int  novum_scene_set_features(NovumScene* s, int features);
+int  novum_scene_set_environment(NovumScene* s, const float rgb[3]);
 /* depth of the BVH8 (levels of 8-wide nodes, root = 1). The traversal stack holds 52 entries, one per level at most: scene creation
  * fails with NOVUM_E_TOODEEP beyond that instead of losing subtrees silently. Negative = error code. */
 int  novum_scene_bvh_depth(const NovumScene* s);
