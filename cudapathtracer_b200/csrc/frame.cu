@@ -76,7 +76,8 @@ __device__ __forceinline__ ByteGuess guessByte(float cFast, const FrameTables* _
     // k = round(qa^(1/2.2) * 255) read from the low mantissa bits of (value + 2^23); qa in [0,1] -> k in [0,255]
     const int k = __float_as_int(fmaf(ex2ApproxF(lg2ApproxF(qa) * (1.0f / 2.2f)), 255.0f, 8388608.0f)) & 0xff;
     const float2 m = T->margin[k];
-    return {k, qa > m.x && qa < m.y};
+    // the margin proof assumes no cancellation in (2.51 c + 0.03): negative channels (FINAL mode keeps them) go to the exact path
+    return {k, cFast >= 0.0f && qa > m.x && qa < m.y};
 }
 
 __device__ __forceinline__ unsigned plainByte(float c) {     // imageUtil.cu:88-90
@@ -274,6 +275,7 @@ static int tablesOnDevice(const FrameTables** out) {
         for (int k = 0; k < 256; ++k) t.margin[k] = make_float2(t.steps[k] * (1.0f + d), t.steps[k + 1] * (1.0f - d));
         if ((e = cudaMalloc(&g_frame.dTables[dev], sizeof(FrameTables))) != cudaSuccess) return (int)e;
         if ((e = cudaMemcpy(g_frame.dTables[dev], &t, sizeof(FrameTables), cudaMemcpyHostToDevice)) != cudaSuccess) return (int)e;
+        if ((e = cudaDeviceSynchronize()) != cudaSuccess) return (int)e;      // pageable upload complete before a kernel on a non-blocking stream reads it
     }
     *out = g_frame.dTables[dev];
     return 0;

@@ -714,7 +714,9 @@ uint64_t fnv1a64(const void* data, size_t n) {
 }
 int readAccumHeader(FILE* f, AccumHeader& hd) {
     if (fread(&hd, sizeof(hd), 1, f) != 1) return NOVUM_E_IO;
-    if (memcmp(hd.magic, "NOVUMACC", 8) != 0 || hd.version != 1 || hd.w <= 0 || hd.h <= 0 || hd.sampleCount < 0) return NOVUM_E_IO;
+    if (memcmp(hd.magic, "NOVUMACC", 8) != 0 || (hd.version != 1 && hd.version != 2) || hd.w <= 0 || hd.h <= 0 || hd.sampleCount < 0) return NOVUM_E_IO;
+    // version 2: the last header word is a checksum of the 56 bytes before it (a flipped sampleCount or seed would resume at the wrong pass)
+    if (hd.version == 2 && hd.reserved1 != fnv1a64(&hd, 56)) return NOVUM_E_IO;
     if (hd.payloadBytes != (uint64_t)hd.w * (uint64_t)hd.h * sizeof(NovumFloat4)) return NOVUM_E_IO;
     return 0;
 }
@@ -725,14 +727,16 @@ int novum_accum_save(const char* path, const NovumFloat4* colors, int w, int h, 
     AccumHeader hd;
     memset(&hd, 0, sizeof(hd));
     memcpy(hd.magic, "NOVUMACC", 8);
-    hd.version = 1; hd.w = w; hd.h = h; hd.sampleCount = sampleCount; hd.integrator = integrator; hd.seed = seed;
+    hd.version = 2; hd.w = w; hd.h = h; hd.sampleCount = sampleCount; hd.integrator = integrator; hd.seed = seed;
     hd.payloadBytes = (uint64_t)w * (uint64_t)h * sizeof(NovumFloat4);
     hd.checksum = fnv1a64(colors, (size_t)hd.payloadBytes);
+    hd.reserved1 = fnv1a64(&hd, 56);
     // written under a temporary name and renamed: a crash during the write never leaves a truncated checkpoint under `path`
     std::string tmp = std::string(path) + ".part";
     FILE* f = fopen(tmp.c_str(), "wb");
     if (!f) return NOVUM_E_IO;
     bool ok = fwrite(&hd, sizeof(hd), 1, f) == 1 && fwrite(colors, 1, (size_t)hd.payloadBytes, f) == (size_t)hd.payloadBytes;
+    ok = ok && fflush(f) == 0 && fsync(fileno(f)) == 0;          // on disk before the rename makes it the checkpoint
     ok = (fclose(f) == 0) && ok;
     if (!ok || rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); return NOVUM_E_IO; }
     return 0;

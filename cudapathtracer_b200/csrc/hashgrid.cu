@@ -167,6 +167,7 @@ void hashGridFree(HashGridDevice& g) {
 static int hashGridBuildStrided(HashGridDevice& g, const float* px, const float* py, const float* pz, int stride, int n,
                                 const float sceneMin[3], float mergeRadius, cudaStream_t stream) {
     if (n < 0 || n > g.maxPhotons) return NOVUM_E_ARG;
+    if (!(mergeRadius > 0.0f) || !std::isfinite(mergeRadius)) return NOVUM_E_ARG;      // a cell size of 0 / inf / NaN would put every photon in one key
     g.params.minX = sceneMin[0]; g.params.minY = sceneMin[1]; g.params.minZ = sceneMin[2];
     g.params.cell = mergeRadius; g.params.tableSize = g.tableSize;
     g.launches = 0;

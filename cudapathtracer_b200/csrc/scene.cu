@@ -204,6 +204,8 @@ int novum_scene_create(const NovumFloat4* positions, int nPos, const NovumFloat4
     up((void**)&s->d_lights, lights.data(), sizeof(NovumTriangle) * lights.size());
     up((void**)&s->d_matsRef, mats, sizeof(NovumMaterial) * nMat);
     up((void**)&s->d_textures, textures, sizeof(float4) * (nTexels > 0 ? nTexels : 0));
+    // the uploads above are pageable copies on the legacy stream, what follows runs on the scene's own non-blocking stream
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { novum_scene_destroy(s); return (int)e; }
     int rc = sceneFinalize(s);
     if (rc) { novum_scene_destroy(s); return rc; }

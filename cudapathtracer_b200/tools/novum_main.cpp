@@ -43,21 +43,27 @@ int main(int argc, char** argv) {
     printf("scene: %d triangles, %d lights, %d BVH8 nodes, radius %g\n", nTri, nLights, nNodes, radius);
     std::vector<NovumFloat4> img((size_t)cfg.width * cfg.height);
     NovumRenderStats st; NovumShard shard = {0, 1};
+    int finalCount = cfg.sampleCount;
     if (checkpoint.empty()) {
         rc = novum_render(scene, &cfg, &cam, 0, cfg.sampleCount, shard, seed, img.data(), &st);
         if (rc) { fprintf(stderr, "render failed: %s\n", novum_error_string(rc)); return 1; }
     } else {
         // resumable run: the sums so far are loaded if the checkpoint exists, then `every` passes at a time are rendered, added and
         // written back (with a progressive .bmp beside them); killing the process loses at most one chunk
-        int done = 0, cw = 0, ch = 0; uint64_t cseed = seed;
+        int done = 0, cw = 0, ch = 0, cinteg = -1; uint64_t cseed = seed;
         memset(img.data(), 0, img.size() * sizeof(NovumFloat4));
-        if (novum_accum_info(checkpoint.c_str(), &cw, &ch, &done, &cseed, nullptr) == 0) {
+        if (novum_accum_info(checkpoint.c_str(), &cw, &ch, &done, &cseed, &cinteg) == 0) {
+            if (cinteg != cfg.integrator) {          // sums of another integrator must not be continued with this one
+                fprintf(stderr, "checkpoint %s was written by integrator %d, this render uses %d: refusing to resume\n", checkpoint.c_str(), cinteg, cfg.integrator);
+                return 1;
+            }
             rc = novum_accum_load(checkpoint.c_str(), img.data(), cfg.width, cfg.height, &done, &cseed);
             if (rc) { fprintf(stderr, "checkpoint %s does not fit this render: %s\n", checkpoint.c_str(), novum_error_string(rc)); return 1; }
             seed = cseed;
             printf("resuming at sample %d of %d (seed %llu)\n", done, cfg.sampleCount, (unsigned long long)seed);
         }
         if (every <= 0) every = 16;
+        finalCount = std::max(done, cfg.sampleCount);          // a checkpoint that already holds more passes than asked for is normalised by what it holds
         std::vector<NovumFloat4> part(img.size());
         memset(&st, 0, sizeof(st));
         while (done < cfg.sampleCount) {
@@ -79,7 +85,7 @@ int main(int argc, char** argv) {
            (unsigned long long)st.paths, (unsigned long long)st.closestRays, (unsigned long long)st.shadowRays, st.deviceMs,
            rays / (st.deviceMs * 1e3), (unsigned long long)st.kernelLaunches);
     // main.cu:855-907: / sampleCount, NaN / Inf marking, tonemap + gamma + BGR rows — one device kernel, 3 B/pixel read back
-    rc = novum_save_bmp((out + ".bmp").c_str(), img.data(), nullptr, cfg.width, cfg.height, cfg.sampleCount, NOVUM_FRAME_FINAL, cfg.postProcess);
+    rc = novum_save_bmp((out + ".bmp").c_str(), img.data(), nullptr, cfg.width, cfg.height, finalCount, NOVUM_FRAME_FINAL, cfg.postProcess);
     if (rc) fprintf(stderr, "bmp write failed: %s\n", novum_error_string(rc));
     if (raw) {
         FILE* f = fopen((out + ".raw").c_str(), "wb");
