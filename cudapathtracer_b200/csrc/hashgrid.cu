@@ -43,11 +43,6 @@ __device__ __forceinline__ int cellCoord(float v, float cell, float rcell) {
     return (int)f;
 }
 
-// n % p for 32-bit n and a fixed p with magic = floor((2^64 - 1) / p) + 1 (Lemire, Kaser, Kurz 2019: exact for every 32-bit n)
-__device__ __forceinline__ unsigned fastMod(unsigned n, unsigned p, unsigned long long magic) {
-    return (unsigned)__umul64hi(magic * (unsigned long long)n, (unsigned long long)p);
-}
-
 __global__ void hashKernel(const float* __restrict__ px, const float* __restrict__ py, const float* __restrict__ pz, int stride,
                            int n, GridParams g, float rcell, unsigned long long magic, uint32_t* __restrict__ keys, uint32_t* __restrict__ index) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -21,6 +21,16 @@ NV_HD unsigned hashCell(int3 c, unsigned tableSize) {                           
     return n % tableSize;
 }
 
+#ifdef __CUDACC__
+// n % p for 32-bit n and a fixed p with magic = floor((2^64 - 1) / p) + 1 (Lemire, Kaser, Kurz 2019: exact for every 32-bit n)
+__device__ __forceinline__ unsigned fastMod(unsigned n, unsigned p, unsigned long long magic) {
+    return (unsigned)__umul64hi(magic * (unsigned long long)n, (unsigned long long)p);
+}
+__device__ __forceinline__ unsigned hashCellMagic(int cx, int cy, int cz, unsigned tableSize, unsigned long long magic) {    // = hashCell
+    return fastMod((73856093u * (unsigned)cx) ^ (19349663u * (unsigned)cy) ^ (83492791u * (unsigned)cz), tableSize, magic);
+}
+#endif
+
 struct HashGridDevice {
     int maxPhotons = 0;
     unsigned tableSize = 0;

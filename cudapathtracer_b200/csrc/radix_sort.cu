@@ -19,8 +19,9 @@ constexpr int kHistThreads = 256;
 constexpr int kHistItems = kSortTile / kHistThreads;   // 16 keys per thread
 
 __global__ void __launch_bounds__(kHistThreads) digitHistogram(const uint32_t* __restrict__ keys, int n, int shift,
-                                                               uint32_t* __restrict__ hist, int numTiles) {
+                                                               uint32_t* __restrict__ hist, int numTiles, const int* __restrict__ nDev) {
     __shared__ uint32_t cnt[256];
+    if (nDev) n = min(max(__ldg(nDev), 0), n);              // the pair count lives on the device: the grid covers the capacity, tiles past the count report zeros
     cnt[threadIdx.x] = 0;
     const int base = blockIdx.x * kSortTile;
     uint32_t k[kHistItems];
@@ -81,8 +82,10 @@ struct ScatterSmem {
 __global__ void __launch_bounds__(kThreads, 2) scatterPass(const uint32_t* __restrict__ keysIn, const uint32_t* __restrict__ valsIn,
                                                            uint32_t* __restrict__ keysOut, uint32_t* __restrict__ valsOut, int n,
                                                            int shift, const uint32_t* __restrict__ histScanned, const uint32_t* __restrict__ rowTotal,
-                                                           int numTiles) {
+                                                           int numTiles, const int* __restrict__ nDev) {
     extern __shared__ __align__(16) unsigned char scatterSmemRaw[];
+    if (nDev) n = min(max(__ldg(nDev), 0), n);
+    if (blockIdx.x * kSortTile >= n) return;                 // (uniform per CTA)
     ScatterSmem& S = *reinterpret_cast<ScatterSmem*>(scatterSmemRaw);
     for (int i = threadIdx.x; i < kWarps * 256; i += kThreads) (&S.warpCnt[0][0])[i] = 0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -338,7 +341,13 @@ void radixSortPlanDestroy(RadixSortPlan& plan) {
 
 cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, int n, int numBits,
                            cudaStream_t stream, int* launches) {
-    if (n <= 1) return cudaSuccess;
+    return radixSortPairsDeviceCount(plan, keys, vals, n, nullptr, numBits, stream, launches);
+}
+
+cudaError_t radixSortPairsDeviceCount(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, int n, const int* d_n, int numBits,
+                                      cudaStream_t stream, int* launches) {
+    if (n <= 1 && !d_n) return cudaSuccess;
+    if (n < 1) return cudaSuccess;
     if (n > plan.maxN) return cudaErrorInvalidValue;
     int passes = (numBits + 7) / 8;
     if (passes < 1) passes = 1;
@@ -347,17 +356,17 @@ cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, 
     uint32_t *kin = keys, *vin = vals, *kout = plan.keysAlt, *vout = plan.valsAlt;
     for (int p = 0; p < passes; ++p) {
         int shift = p * 8;
-        digitHistogram<<<numTiles, kHistThreads, 0, stream>>>(kin, n, shift, plan.hist, numTiles);
+        digitHistogram<<<numTiles, kHistThreads, 0, stream>>>(kin, n, shift, plan.hist, numTiles, d_n);
         if (launches) *launches += 1;
         digitRowScan<<<256, 256, 0, stream>>>(plan.hist, numTiles, plan.blockSums);
-        scatterPass<<<numTiles, kThreads, sizeof(ScatterSmem), stream>>>(kin, vin, kout, vout, n, shift, plan.hist, plan.blockSums, numTiles);
+        scatterPass<<<numTiles, kThreads, sizeof(ScatterSmem), stream>>>(kin, vin, kout, vout, n, shift, plan.hist, plan.blockSums, numTiles, d_n);
         if (launches) *launches += 2;
         uint32_t* t;
         t = kin; kin = kout; kout = t;
         t = vin; vin = vout; vout = t;
     }
     if (kin != keys) {   // odd number of passes: result sits in the alternates (a kernel, not a copy-engine operation: see bdFillWords in vcm.cu)
-        copyPairs<<<(n + 255) / 256, 256, 0, stream>>>(kin, vin, keys, vals, n);
+        copyPairs<<<(n + 255) / 256, 256, 0, stream>>>(kin, vin, keys, vals, n);        // (with a device-side count: copies the capacity, harmless)
         if (launches) *launches += 1;
     }
     return cudaGetLastError();

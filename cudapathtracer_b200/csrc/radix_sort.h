@@ -37,6 +37,11 @@ cudaError_t radixSortPairs(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, 
 // forces the module load of every kernel of this file (see nv::bdPreloadKernels in vcm_host.inl)
 cudaError_t radixSortPreload();
 
+// The same with the pair count on the device: `n` is the capacity the launches are sized for, *d_n (clamped to [0, n]) the number of pairs
+// actually sorted - no host round trip to learn it. d_n == nullptr sorts n pairs.
+cudaError_t radixSortPairsDeviceCount(RadixSortPlan& plan, uint32_t* keys, uint32_t* vals, int n, const int* d_n, int numBits,
+                                      cudaStream_t stream, int* launches);
+
 // exclusive prefix sum over u32, in place; scratch must hold >= ceil(n/2048)+1 entries
 cudaError_t exclusiveScanU32(uint32_t* data, int n, uint32_t* scratch, cudaStream_t stream, int* launches);
 

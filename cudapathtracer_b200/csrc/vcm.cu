@@ -672,9 +672,7 @@ __global__ void __launch_bounds__(kBdThreads) bdEyeStep(SceneView sc, BdState st
 }
 
 // ---- merging (deviceCode.cu:2968-3048), one warp per eye vertex ----------------------------------------------------------------
-// Lanes 0..26 look up the 27 neighbour cells (same z, y, x order and the same per-cell lookups as the reference, so a table
-// slot shared by two neighbours is visited twice there and here). Photon records are read in the merge-ready form written by
-// bdReorderPhotons. Two kernels, because the eye vertex's material decides how much work one accepted photon is:
+// Photon records are read in the merge-ready form written by bdReorderPhotons; the cells looked at are described at kMergeFine below. Two kernels, because the eye vertex's material decides how much work one accepted photon is:
 //   bdMergeLambert  Lambert vertices (front of mergeQ): the reverse pdfs and the BSDF value reduce to one cosine, so the
 //                   accept path is ~20 instructions and is run in place, predicated, with no compaction;
 //   bdMerge         everything else (back of mergeQ): accepted candidates are compacted into a per-warp buffer so that the
@@ -683,21 +681,42 @@ constexpr int kMergeThreads = 128;
 constexpr int kMergeWarps = kMergeThreads / 32;
 constexpr int kMergeCtasPerSm = 8;        // 64 registers per thread; the 90-register build at 5 CTAs/SM was 14 % slower
 constexpr int kMergeGather = 4;           // eye vertices a warp gathers together
-#ifndef NOVUM_MERGE_CULL
-#define NOVUM_MERGE_CULL 0
-#endif
-constexpr bool kMergeCull = NOVUM_MERGE_CULL != 0;   // drop neighbour cells out of reach of the whole group before the sweep
 
-struct MergeCells { uint32_t cs, cc; };     // per lane (< 27): first photon and photon count of its neighbour cell
+// The photon grid of the engine has cells of r / kMergeFine (the reference's cells are r wide, integratorUtilities.cuh:382-388, with a
+// 27-cell walk, deviceCode.cu:2968-2995): a photon within r of a vertex then lies in one of the (2 kMergeFine + 1)^3 cells around the
+// vertex's own, and of those only the cells whose box comes within r of the vertex are looked at. On a surface the 27 r-cells cover
+// 9 r^2 of which the disc of radius r is pi r^2 (2.9 photons scanned per photon merged at best, 3.9 measured with the 4-vertex union);
+// the reachable r/2-cells cover ~5.3 r^2. The photon SET a vertex merges is unchanged - the distance test decides - so images differ
+// by summation order only.
+constexpr int kMergeFine = 2;
+constexpr int kMergeReach = kMergeFine;                       // cells on either side of the vertex's own cell
+constexpr int kMergeSide = 2 * kMergeReach + 1;               // 5
+constexpr int kMergeNbr = kMergeSide * kMergeSide * kMergeSide;   // 125
+constexpr int kMergeMaxBox = 512;                             // largest cell box a group of vertices may span and still be gathered together
+constexpr int kMergeMaxList = kMergeMaxBox;
 
-NV_D MergeCells mergeCells(const BdParams& P, V3 eyeP, int lane) {
-    const int3 c0 = gridIndex(eyeP.x, eyeP.y, eyeP.z, P.grid);
+// squared distance from p to the box of cell c (slightly shrunk distances: 1e-4 cell of slack absorbs the rounding of the cell function,
+// nothing within r is ever dropped)
+NV_D float cellDist2(const GridParams& g, int cx, int cy, int cz, V3 p) {
+    const float lx = g.minX + (float)cx * g.cell, ly = g.minY + (float)cy * g.cell, lz = g.minZ + (float)cz * g.cell;
+    const float slack = 1e-4f * g.cell;
+    const float dx = fmaxf(fmaxf(lx - p.x, p.x - (lx + g.cell)) - slack, 0.0f);
+    const float dy = fmaxf(fmaxf(ly - p.y, p.y - (ly + g.cell)) - slack, 0.0f);
+    const float dz = fmaxf(fmaxf(lz - p.z, p.z - (lz + g.cell)) - slack, 0.0f);
+    return fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+}
+
+// first photon and photon count of neighbour cell `i` (< kMergeNbr) of the vertex at eyeP, {0, 0} when the cell is empty or out of reach
+struct MergeCells { uint32_t cs, cc; };
+NV_D MergeCells mergeCellFine(const BdParams& P, V3 eyeP, int3 c0, int i, float r2) {
     MergeCells m{0u, 0u};
-    if (lane < 27) {
-        int dz = lane / 9 - 1, dy = (lane / 3) % 3 - 1, dx = lane % 3 - 1;
-        unsigned hsh = hashCell(make_int3(c0.x + dx, c0.y + dy, c0.z + dz), P.grid.tableSize);
-        uint32_t s0 = __ldg(P.cellStart + hsh);
-        if (s0 != 0xFFFFFFFFu) { m.cs = s0; m.cc = __ldg(P.cellEnd + hsh) - s0; }
+    if (i < kMergeNbr) {
+        const int dz = i / (kMergeSide * kMergeSide) - kMergeReach, dy = (i / kMergeSide) % kMergeSide - kMergeReach, dx = i % kMergeSide - kMergeReach;
+        if (cellDist2(P.grid, c0.x + dx, c0.y + dy, c0.z + dz, eyeP) <= r2) {
+            const unsigned hsh = hashCellMagic(c0.x + dx, c0.y + dy, c0.z + dz, P.grid.tableSize, P.gridMagic);
+            const uint32_t s0 = __ldg(P.cellStart + hsh);
+            if (s0 != 0xFFFFFFFFu) { m.cs = s0; m.cc = __ldg(P.cellEnd + hsh) - s0; }
+        }
     }
     return m;
 }
@@ -715,15 +734,21 @@ NV_D void mergeSplat(const BdParams& P, int pix, V3 sum, int lane) {
 // :644), so per photon   w = 1 / (1 + wEye + d_vcm/eta + max(cos(wi, n), eps)/pi * d_vm)   and the vertex's contribution is
 // (currBeta * albedo/pi / (pi r^2 w h)) * sum(beta_photon * w).
 //
-// One warp gathers G consecutive records TOGETHER: the union of their neighbour cells is swept once, every lane loads one
-// candidate photon (two coalesced 16 B words) and tests it against all G vertices, whose constants live in registers. With
-// G = 4 on the primary-hit queue (consecutive records = adjacent pixels, whose 27-cell neighbourhoods nearly coincide) each
-// photon load and its address arithmetic are shared by four (vertex, photon) pairs, which takes the kernel off the L1 / L2
-// bandwidth limit the one-vertex-per-warp form sits on. A photon within r of a vertex always lies in one of that vertex's own
-// 27 cells, so testing a vertex against the cells of its neighbours adds only rejected candidates; table slots are de-duplicated
-// across the union (the reference visits a slot twice when two of a vertex's neighbour cells collide in the table, p ~ 1e-6).
-template <bool MIS>
-__global__ void __launch_bounds__(kMergeThreads, kMergeCtasPerSm) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
+// One warp gathers G consecutive records TOGETHER (on the primary-hit queue and on the binned deeper queues consecutive records are
+// neighbours in space): every lane loads ONE candidate photon (two coalesced 16 B words) and tests it against all G vertices, whose
+// constants live in registers, so a load and its address arithmetic serve G (vertex, photon) pairs.
+//   list    the cells of the box spanned by the G neighbourhoods are enumerated across the lanes (distinct cells by construction);
+//           a cell is kept if its box comes within reach of the group (one sphere around the group: centre = mean vertex, radius =
+//           r + largest offset) and its table slot is not empty; kept cells are appended to a shared-memory list with ballot / popc,
+//           together with the running sum of their photon counts. Two distinct cells that collide in the hash table within one round
+//           of 32 are listed once; across rounds a colliding slot is swept twice, as the reference sweeps it once per colliding
+//           neighbour (deviceCode.cu:2968-2995; ~1e-6 of the pairs).
+//   sweep   the listed ranges are walked as ONE sequence: candidate j of the group belongs to lane j % 32, which finds its range by
+//           advancing a pointer through the prefix sums - every trip is a full warp whatever the sizes of the cells (per-cell strides
+//           left the last trip of each cell partly empty, which matters once cells hold ~40 photons instead of ~170).
+// A group whose vertices are so far apart that the box exceeds kMergeMaxBox cells is gathered one vertex at a time.
+template <bool MIS, int MINB>
+__global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView sc, BdState st, BdParams P, MergeQueue mq) {
     int* cnt = mq.cnt;
     const int lane = bdLane();
     const int n = min(cnt[BC_MERGE], mq.cap);
@@ -732,10 +757,14 @@ __global__ void __launch_bounds__(kMergeThreads, kMergeCtasPerSm) bdMergeLambert
     const float invEta = 1.0f / P.etaVcm;
     const PhotonSoA ph = P.photons;
     const unsigned ltMask = (1u << lane) - 1u;
-    __shared__ uint2 cellListAll[kMergeWarps][kMergeGather * 32];
-    __shared__ uint32_t cellKeyAll[kMergeWarps][kMergeGather * 32];
-    uint2* cellList = cellListAll[threadIdx.x >> 5];
-    uint32_t* cellKey = cellKeyAll[threadIdx.x >> 5];
+    __shared__ uint2 listAll[kMergeWarps][kMergeMaxList + 1];         // {first photon - candidates listed before this range, candidates listed up to its end}
+    __shared__ float4 vtxAll[kMergeWarps][kMergeGather];             // {n/pi, 1 + d_vcm/eta + eyeRev * d_vm} of the gathered vertices: warp-uniform, read where a photon is accepted
+    uint2* list = listAll[threadIdx.x >> 5];
+    float4* vtx = vtxAll[threadIdx.x >> 5];
+    // shared-memory addresses kept in registers (the asm keeps the compiler from recomputing them from %tid at every use in the sweep)
+    uint32_t listAddr, vtxAddr;
+    asm volatile("mov.u32 %0, %1;" : "=r"(listAddr) : "r"((uint32_t)__cvta_generic_to_shared(list)));
+    asm volatile("mov.u32 %0, %1;" : "=r"(vtxAddr) : "r"((uint32_t)__cvta_generic_to_shared(vtx)));
     unsigned long long nCand = 0;
     unsigned nAcc = 0;
     while (true) {
@@ -744,119 +773,170 @@ __global__ void __launch_bounds__(kMergeThreads, kMergeCtasPerSm) bdMergeLambert
         if (lane == 0) base = atomicAdd(&cnt[BC_FETCH_MERGE], kMergeGather);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n) break;
-        V3 eyeP[kMergeGather], nPi[kMergeGather], sum[kMergeGather];
-        float C[kMergeGather];
-        int recIdx[kMergeGather];
-        // the group's cell list lives in shared memory (entry g * 32 + lane = {first photon, count} of vertex g's neighbour
-        // `lane`), so the sweep below exists once in the code and walks the list with a dynamic index
+        const int real = min(kMergeGather, n - base);
+        V3 eyeP[kMergeGather], sum[kMergeGather];
+        int3 lo = make_int3(0x7fffffff, 0x7fffffff, 0x7fffffff), hi = make_int3(-0x7fffffff, -0x7fffffff, -0x7fffffff);
 #pragma unroll
         for (int g = 0; g < kMergeGather; ++g) {
             // a short last group repeats its last record (its result is dropped below)
             const int r = min(base + g, n - 1);
-            recIdx[g] = mq.order ? __ldg(mq.order + r) : r;
-            const float4* rp = reinterpret_cast<const float4*>(mq.recs + recIdx[g]);
-            const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2q = __ldg(rp + 2), r3 = __ldg(rp + 3);
+            const float4* rp = reinterpret_cast<const float4*>(mq.recs + (mq.order ? __ldg(mq.order + r) : r));
+            const float4 r0 = __ldg(rp);
             eyeP[g] = V3(r0.x, r0.y, r0.z);
-            nPi[g] = V3(r1.x, r1.y, r1.z) * (1.0f / kPi);                                        // cos/pi = dot(wi, n/pi)
-            C[g] = 1.0f + r2q.w * invEta + cosinePdf(V3(r2q.x, r2q.y, r2q.z)) * r3.w;           // 1 + d_vcm/eta + eyeRev * d_vm
             sum[g] = V3(0.0f);
+            const int3 c = gridIndex(eyeP[g].x, eyeP[g].y, eyeP[g].z, P.grid);
+            lo.x = min(lo.x, c.x); lo.y = min(lo.y, c.y); lo.z = min(lo.z, c.z);
+            hi.x = max(hi.x, c.x); hi.y = max(hi.y, c.y); hi.z = max(hi.z, c.z);
         }
+        const bool together = (long long)(hi.x - lo.x + kMergeSide) * (hi.y - lo.y + kMergeSide) * (hi.z - lo.z + kMergeSide) <= kMergeMaxBox;
+        const int passes = together ? 1 : real;
+#pragma unroll 1
+        for (int pass = 0; pass < passes; ++pass) {
+            // the vertices gathered in this pass: all of them, or vertex `pass` alone (the others are parked at NaN for the pass, so
+            // that every distance test on them fails; their positions wait in the list's tail slots of shared memory)
+            V3 ctr(0.0f);
+            int bx0, by0, bz0, nx, ny, nz;
+            float reach;
+            if (together) {
 #pragma unroll
-        for (int g = 0; g < kMergeGather; ++g) {
-            MergeCells mc = mergeCells(P, eyeP[g], lane);
-            if (base + g >= n) mc.cc = 0u;
-            if (kMergeCull && mc.cc) {
-                // a neighbour cell whose box lies farther than r from ALL vertices of the group cannot hold a photon any of them
-                // accepts (8 corner and 12 edge cells of a 27-neighbourhood are often out of reach): drop it before the sweep.
-                // The test is per (cell, group), so vertices sharing a centre cell keep identical lists (the shortcut below).
-                // 1.1 r^2: slack for the rounding of the cell function; nothing within r is ever dropped.
-                const int3 c0 = gridIndex(eyeP[g].x, eyeP[g].y, eyeP[g].z, P.grid);
-                const float lx = P.grid.minX + (float)(c0.x + lane % 3 - 1) * P.grid.cell, ly = P.grid.minY + (float)(c0.y + (lane / 3) % 3 - 1) * P.grid.cell,
-                            lz = P.grid.minZ + (float)(c0.z + lane / 9 - 1) * P.grid.cell;
-                bool near = false;
+                for (int k = 0; k < kMergeGather; ++k) ctr += eyeP[k];
+                ctr = ctr * (1.0f / kMergeGather);               // a short group repeats its last vertex: still inside the hull
+                float far2 = 0.0f;
 #pragma unroll
-                for (int k = 0; k < kMergeGather; ++k) {
-                    const float dx = fmaxf(fmaxf(lx - eyeP[k].x, eyeP[k].x - (lx + P.grid.cell)), 0.0f);
-                    const float dy = fmaxf(fmaxf(ly - eyeP[k].y, eyeP[k].y - (ly + P.grid.cell)), 0.0f);
-                    const float dz = fmaxf(fmaxf(lz - eyeP[k].z, eyeP[k].z - (lz + P.grid.cell)), 0.0f);
-                    near |= fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= 1.1f * r2;
+                for (int k = 0; k < kMergeGather; ++k) far2 = fmaxf(far2, lengthSq(eyeP[k] - ctr));
+                reach = P.mergeRadius + sqrtf(far2);
+                bx0 = lo.x - kMergeReach; by0 = lo.y - kMergeReach; bz0 = lo.z - kMergeReach;
+                nx = hi.x - lo.x + kMergeSide; ny = hi.y - lo.y + kMergeSide; nz = hi.z - lo.z + kMergeSide;
+            } else {
+                float* park = reinterpret_cast<float*>(list + kMergeMaxList + 1 - 2 * kMergeGather);          // 125 list entries at most in this mode
+                __syncwarp();
+                if (pass == 0 && lane == 0) {
+#pragma unroll
+                    for (int k = 0; k < kMergeGather; ++k) { park[3 * k] = eyeP[k].x; park[3 * k + 1] = eyeP[k].y; park[3 * k + 2] = eyeP[k].z; }
                 }
-                if (!near) mc.cc = 0u;
+                __syncwarp();
+#pragma unroll
+                for (int k = 0; k < kMergeGather; ++k)
+                    eyeP[k] = k == pass ? V3(park[3 * k], park[3 * k + 1], park[3 * k + 2]) : V3(__int_as_float(0x7fc00000));
+#pragma unroll
+                for (int k = 0; k < kMergeGather; ++k) if (k == pass) ctr = eyeP[k];
+                const int3 c = gridIndex(ctr.x, ctr.y, ctr.z, P.grid);
+                reach = P.mergeRadius;
+                bx0 = c.x - kMergeReach; by0 = c.y - kMergeReach; bz0 = c.z - kMergeReach;
+                nx = ny = nz = kMergeSide;
             }
-            // key = first photon of the slot; empty slots get keys no photon index can take
-            cellKey[g * 32 + lane] = mc.cc ? mc.cs : 0xFFFFFF00u + (unsigned)lane;
-            cellList[g * 32 + lane] = make_uint2(mc.cs, mc.cc);
-        }
-        __syncwarp();
-        if (kMergeGather > 1) {
-            // drop table slots already listed by an earlier lane of the same vertex or by an earlier vertex of the group
+            const int nCells = nx * ny * nz, nxy = nx * ny;
+            const float invXY = 1.0f / (float)nxy, invX = 1.0f / (float)nx, reach2 = reach * reach;
+            // ---- list ----
+            uint32_t total = 0;
+            int m = 0;
+            __syncwarp();
 #pragma unroll 1
-            for (int g = 0; g < kMergeGather; ++g) {
-                const uint32_t key = cellKey[g * 32 + lane];
-                bool dup = (__match_any_sync(0xffffffffu, key) & ltMask) != 0u;
-#pragma unroll 1
-                for (int k = 0; k < g; ++k) {
-                    if (__all_sync(0xffffffffu, cellKey[k * 32 + lane] == key)) { dup = true; break; }   // same centre cell: identical lists
-#pragma unroll 1
-                    for (int j = 0; j < 27; ++j) dup |= cellKey[k * 32 + j] == key;
+            for (int i0 = 0; i0 < nCells; i0 += 32) {
+                const int i = i0 + lane;
+                uint32_t cs = 0u, cc = 0u;
+                if (i < nCells) {
+                    const int cz = (int)(((float)i + 0.5f) * invXY), rem = i - cz * nxy;          // exact: i < 512
+                    const int cy = (int)(((float)rem + 0.5f) * invX), cx = rem - cy * nx;
+                    if (cellDist2(P.grid, bx0 + cx, by0 + cy, bz0 + cz, ctr) <= reach2) {
+                        const unsigned hsh = hashCellMagic(bx0 + cx, by0 + cy, bz0 + cz, P.grid.tableSize, P.gridMagic);
+                        const uint32_t s0 = __ldg(P.cellStart + hsh);
+                        if (s0 != 0xFFFFFFFFu) { cs = s0; cc = __ldg(P.cellEnd + hsh) - s0; }
+                    }
                 }
-                if (dup) cellList[g * 32 + lane].y = 0u;
+                // two cells of this round in one table slot: listed once
+                if (cc && (__match_any_sync(__activemask(), cs) & ltMask)) cc = 0u;
+                const unsigned keep = __ballot_sync(0xffffffffu, cc != 0u);
+                uint32_t x = cc;                                                                // inclusive scan of the counts
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+                if (cc) {
+                    const int slot = m + __popc(keep & ltMask);
+                    list[slot] = make_uint2(cs - (total + x - cc), total + x);
+                }
+                total += __shfl_sync(0xffffffffu, x, 31);
+                m += __popc(keep);
+            }
+            if (lane == 0) list[m] = make_uint2(0u, 0xFFFFFFFFu);
+            __syncwarp();
+            if (lane == 0) nCand += (unsigned long long)total * (unsigned)(together ? real : 1);
+            // ---- sweep ----
+            // the vertices' other constants are fetched only now (the records are in L1): they are not live while the list is built
+            if (MIS && lane < kMergeGather) {                  // lane g writes vertex g's
+                const int r = min(base + lane, n - 1);
+                const float4* rp = reinterpret_cast<const float4*>(mq.recs + (mq.order ? __ldg(mq.order + r) : r));
+                const float4 r1 = __ldg(rp + 1), r2q = __ldg(rp + 2), r3 = __ldg(rp + 3);
+                // cos/pi = dot(wi, n/pi);   1 + d_vcm/eta + eyeRev * d_vm
+                vtx[lane] = make_float4(r1.x * (1.0f / kPi), r1.y * (1.0f / kPi), r1.z * (1.0f / kPi),
+                                        1.0f + r2q.w * invEta + cosinePdf(V3(r2q.x, r2q.y, r2q.z)) * r3.w);
             }
             __syncwarp();
-        }
-#pragma unroll 1
-        for (int g = 0; g < kMergeGather; ++g) {
-            const uint2 mine = cellList[g * 32 + lane];
-            nCand += (unsigned long long)mine.y * (unsigned)min(kMergeGather, n - base);
-            unsigned nonEmpty = __ballot_sync(0xffffffffu, mine.y != 0u);
-            while (nonEmpty) {
-                const int c = __ffs(nonEmpty) - 1;
-                nonEmpty &= nonEmpty - 1;
-                const uint2 cell = cellList[g * 32 + c];
-                const uint32_t cend = cell.x + cell.y;
-                uint32_t q = cell.x + lane;
-                // lanes strided over the cell's photons; the next trip's two words are requested before this trip's tests
-                // (two trips per loop turn, so the double buffer needs no register moves)
-                auto test = [&](const float4 Ac, const uint4 Bc) {
-                    const float2 wxy = unpackHalf2(__float_as_uint(Ac.w)), wzb = unpackHalf2(Bc.x), byz = unpackHalf2(Bc.y);
+            auto test = [&](const float4 Ac, const uint4 Bc) {
+                const float2 wxy = unpackHalf2(__float_as_uint(Ac.w)), wzb = unpackHalf2(Bc.x), byz = unpackHalf2(Bc.y);
 #pragma unroll
-                    for (int k = 0; k < kMergeGather; ++k) {
-                        const float dx = eyeP[k].x - Ac.x, dy = eyeP[k].y - Ac.y, dz = eyeP[k].z - Ac.z;
-                        if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= r2) {
-                            float w = 1.0f;
-                            if (MIS) {
-                                const float rev = fmaxf(fmaf(wxy.x, nPi[k].x, fmaf(wxy.y, nPi[k].y, wzb.x * nPi[k].z)), kEps * (1.0f / kPi));
-                                w = rcpApprox(fmaf(rev, __uint_as_float(Bc.z), C[k] + __uint_as_float(Bc.w)));      // the argument is >= 1
-                            }
-                            sum[k].x = fmaf(wzb.y, w, sum[k].x); sum[k].y = fmaf(byz.x, w, sum[k].y); sum[k].z = fmaf(byz.y, w, sum[k].z);
-                            ++nAcc;
+                for (int k = 0; k < kMergeGather; ++k) {
+                    const float dx = eyeP[k].x - Ac.x, dy = eyeP[k].y - Ac.y, dz = eyeP[k].z - Ac.z;
+                    if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= r2) {
+                        float w = 1.0f;
+                        if (MIS) {
+                            float4 v;
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(vtxAddr + k * 16));
+                            const float rev = fmaxf(fmaf(wxy.x, v.x, fmaf(wxy.y, v.y, wzb.x * v.z)), kEps * (1.0f / kPi));
+                            w = rcpApprox(fmaf(rev, __uint_as_float(Bc.z), v.w + __uint_as_float(Bc.w)));      // the argument is >= 1
                         }
+                        sum[k].x = fmaf(wzb.y, w, sum[k].x); sum[k].y = fmaf(byz.x, w, sum[k].y); sum[k].z = fmaf(byz.y, w, sum[k].z);
+                        ++nAcc;
                     }
-                };
-                if (q < cend) {
-                    float4 A0 = __ldg(ph.a + q), A1; uint4 B0 = __ldg(ph.b + q), B1;
-                    while (true) {
-                        const bool more1 = q + 32 < cend;
-                        if (more1) { A1 = __ldg(ph.a + q + 32); B1 = __ldg(ph.b + q + 32); }
-                        test(A0, B0);
-                        if (!more1) break;
-                        const bool more2 = q + 64 < cend;
-                        if (more2) { A0 = __ldg(ph.a + q + 64); B0 = __ldg(ph.b + q + 64); }
-                        test(A1, B1);
-                        if (!more2) break;
-                        q += 64;
-                    }
+                }
+            };
+            // candidate j of the group -> photon index (j only ever grows): the current range's {bias, end} stay in registers and the
+            // pointer moves on only when j has left the range
+            uint32_t lp = listAddr;
+            uint32_t bias, end;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(bias), "=r"(end) : "r"(lp));
+            auto locate = [&](uint32_t j) -> uint32_t {
+                while (j >= end) {
+                    lp += 8u;
+                    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(bias), "=r"(end) : "r"(lp));
+                }
+                return bias + j;
+            };
+            uint32_t j = (uint32_t)lane;
+            if (j < total) {
+                uint32_t q = locate(j);
+                float4 A0 = __ldg(ph.a + q), A1; uint4 B0 = __ldg(ph.b + q), B1;
+                // the next trip's two words are requested before this trip's tests (two trips per loop turn: no register moves)
+                while (true) {
+                    const bool more1 = j + 32 < total;
+                    if (more1) { q = locate(j + 32); A1 = __ldg(ph.a + q); B1 = __ldg(ph.b + q); }
+                    test(A0, B0);
+                    if (!more1) break;
+                    const bool more2 = j + 64 < total;
+                    if (more2) { q = locate(j + 64); A0 = __ldg(ph.a + q); B0 = __ldg(ph.b + q); }
+                    test(A1, B1);
+                    if (!more2) break;
+                    j += 64;
                 }
             }
         }
+        // the G sums are reduced over the warp; lane g then finishes vertex g (albedo, normalisation, one atomic per vertex)
 #pragma unroll
-        for (int g = 0; g < kMergeGather; ++g) {
-            if (base + g >= n) break;
-            const float4* rp = reinterpret_cast<const float4*>(mq.recs + recIdx[g]);
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int g = 0; g < kMergeGather; ++g) {
+                sum[g].x += __shfl_xor_sync(0xffffffffu, sum[g].x, o); sum[g].y += __shfl_xor_sync(0xffffffffu, sum[g].y, o); sum[g].z += __shfl_xor_sync(0xffffffffu, sum[g].z, o);
+            }
+        }
+        if (lane < real) {
+            V3 mine = sum[0];
+#pragma unroll
+            for (int g = 1; g < kMergeGather; ++g) if (lane == g) mine = sum[g];
+            const float4* rp = reinterpret_cast<const float4*>(mq.recs + (mq.order ? __ldg(mq.order + base + lane) : base + lane));
             const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r3 = __ldg(rp + 3), r4 = __ldg(rp + 4);
             const Shading sh = resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y));
-            const V3 K = V3(r3.x, r3.y, r3.z) * sh.m.albedo * (norm * (1.0f / kPi));
-            mergeSplat(P, __float_as_int(r0.w), sum[g] * K, lane);
+            mine = mine * (V3(r3.x, r3.y, r3.z) * sh.m.albedo * (norm * (1.0f / kPi)));
+            if ((mine.x != 0.0f || mine.y != 0.0f || mine.z != 0.0f) && isfinite(mine.x) && isfinite(mine.y) && isfinite(mine.z))
+                atomicAdd(&P.colors[__float_as_int(r0.w)], make_float4(mine.x, mine.y, mine.z, 0.f));
         }
     }
     unsigned long long acc = nAcc;
@@ -913,10 +993,13 @@ __global__ void __launch_bounds__(kMergeThreads) bdMerge(SceneView sc, BdState s
             MergeCtx ctx(resolveShading(sc.mats, __float_as_int(r1.w), sc.textures, make_float2(r4.x, r4.y)), V3(r1.x, r1.y, r1.z));
             ctx.toPrevL = V3(r2q.x, r2q.y, r2q.z); ctx.scale = V3(r3.x, r3.y, r3.z) * norm;
             ctx.eyeDvcmOverEta = r2q.w / P.etaVcm; ctx.eyeDvm = r3.w;
-            const MergeCells mc = mergeCells(P, eyeP, lane);
-            nCand += mc.cc;
+            const int3 c0 = gridIndex(eyeP.x, eyeP.y, eyeP.z, P.grid);
             int count = 0;
             V3 sum(0.0f);
+#pragma unroll 1
+            for (int round = 0; round < (kMergeNbr + 31) / 32; ++round) {
+            const MergeCells mc = mergeCellFine(P, eyeP, c0, round * 32 + lane, r2);
+            nCand += mc.cc;
             unsigned nonEmpty = __ballot_sync(0xffffffffu, mc.cc != 0u);
             while (nonEmpty) {
                 const int c = __ffs(nonEmpty) - 1;
@@ -946,6 +1029,7 @@ __global__ void __launch_bounds__(kMergeThreads) bdMerge(SceneView sc, BdState s
                     }
                 }
             }
+            }
             if (lane < count) sum += mergeOne(P, ctx, accBuf[warp][lane]);
             nMerged += count;
             __syncwarp();
@@ -958,28 +1042,20 @@ __global__ void __launch_bounds__(kMergeThreads) bdMerge(SceneView sc, BdState s
     if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0) atomicAdd(&st.stats[6], (unsigned long long)n);
 }
 
-// ---- spatial binning of a group's Lambert merge records (counting sort: coarse Morton grid over the scene box + cell sub-bin) ----
-// The record count lives on the device, so these kernels are grid-stride over cnt[BC_MERGE] and need no host round trip.
-NV_D uint32_t mortonSpread(uint32_t v) {            // up to 8 bits -> every third bit
-    v = (v | (v << 8)) & 0x300Fu; v = (v | (v << 4)) & 0x30C3u; v = (v | (v << 2)) & 0x9249u;
-    return v;
-}
-NV_D uint32_t mergeBinOf(const MergeBins& b, const GridParams& g, float4 p) {
-    const int hi = (1 << kMergeBinBits) - 1;
-    int ix = min(max((int)((p.x - b.minX) * b.sx), 0), hi), iy = min(max((int)((p.y - b.minY) * b.sy), 0), hi), iz = min(max((int)((p.z - b.minZ) * b.sz), 0), hi);
-    const int3 c = gridIndex(p.x, p.y, p.z, g);
-    const uint32_t sub = (73856093u * (unsigned)c.x ^ 19349663u * (unsigned)c.y ^ 83492791u * (unsigned)c.z) >> 7;
-    return ((mortonSpread(ix) | (mortonSpread(iy) << 1) | (mortonSpread(iz) << 2)) << kMergeSubBits) | (sub & ((1u << kMergeSubBits) - 1u));
-}
-__global__ void bdMergeBinCount(MergeQueue mq, MergeBins b, GridParams g, uint32_t* __restrict__ binCount) {
+// Order of a queue's Lambert merge records for the gather: sorted by the Morton code of the photon-grid cell the vertex lies in (10 bits
+// per axis; `shift` drops low cell bits when the scene spans more than 1024 cells), so that the 4 consecutive records a warp gathers
+// together lie in one cell or in Morton-adjacent ones, and neighbouring warps read neighbouring photon cells (L2). The count is on the
+// device (cnt[BC_MERGE]): keys past it are never read by the device-count radix sort.
+__global__ void bdMergeKeys(MergeQueue mq, GridParams g, int shift, uint32_t* __restrict__ keys, int* __restrict__ order) {
     const int n = min(mq.cnt[BC_MERGE], mq.cap);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        atomicAdd(&binCount[mergeBinOf(b, g, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u);
-}
-__global__ void bdMergeBinScatter(MergeQueue mq, MergeBins b, GridParams g, uint32_t* __restrict__ binStart, int* __restrict__ order) {
-    const int n = min(mq.cnt[BC_MERGE], mq.cap);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        order[atomicAdd(&binStart[mergeBinOf(b, g, __ldg(reinterpret_cast<const float4*>(mq.recs + i)))], 1u)] = i;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 p = __ldg(reinterpret_cast<const float4*>(mq.recs + i));
+        const int3 c = gridIndex(p.x, p.y, p.z, g);
+        const uint32_t cx = (uint32_t)min(max(c.x >> shift, 0), 1023), cy = (uint32_t)min(max(c.y >> shift, 0), 1023), cz = (uint32_t)min(max(c.z >> shift, 0), 1023);
+        auto spread = [](uint32_t v) { v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu; v = (v | (v << 4)) & 0x030C30C3u; v = (v | (v << 2)) & 0x09249249u; return v; };
+        keys[i] = spread(cx) | (spread(cy) << 1) | (spread(cz) << 2);
+        order[i] = i;
+    }
 }
 
 // end of a light pass: publish this rank's photon count in every peer's copy of the slab header and then, behind a system-scope

@@ -45,19 +45,11 @@ struct __align__(16) BdMergeRec { float4 p_pix, n_mat, toPrev_dvcm, beta_dvm, uv
 
 // where one eye step appends its merge records and what the merge kernels consume: Lambert vertices from the front
 // (cnt[BC_MERGE]), every other material from the back (cnt[BC_MERGE_GEN]). Step 0 (primary hits) is merged at once; deeper
-// steps share a queue per group of kMergeGroup steps. The Lambert records of a queue are binned (coarse Morton grid + cell
-// sub-bin) before the gather so that neighbouring warps read the same photon cells (L2 instead of HBM) and the 4 vertices a
-// warp gathers together mostly share one 27-cell neighbourhood.
+// steps share a queue per group of kMergeGroup steps. The Lambert records of a queue are put in photon-cell order (radix sort
+// on the Morton code of the cell, bdMergeKeys) before the gather so that neighbouring warps read the same photon cells (L2 instead
+// of HBM) and the 4 vertices a warp gathers together share one cell neighbourhood.
 struct MergeQueue { BdMergeRec* recs; int cap; int* cnt; const int* order; };
 constexpr int kMergeGroup = 4;
-// bin key = Morton code of a coarse 32^3 grid over the scene box (neighbouring bins -> neighbouring photon cells, L2 reuse),
-// then 6 bits of the vertex's own hash-grid cell, so that consecutive records of a bin mostly share their centre cell and
-// the 4-vertex gather sweeps one 27-cell neighbourhood for all four
-constexpr int kMergeBinBits = 5;
-constexpr int kMergeSubBits = 6;
-constexpr int kMergeBins = 1 << (3 * kMergeBinBits + kMergeSubBits);
-struct MergeBins { float minX, minY, minZ, sx, sy, sz; };
-
 // merge-ready photons in cell order, written by bdReorderPhotons, as two dense 16 B streams so that a warp's candidate loads are
 // two fully coalesced 512 B requests:  a = { pos.xyz, half2(wi.x, wi.y) }   b = { half2(wi.z, beta.x), half2(beta.y, beta.z), d_vm, d_vcm / eta_vcm }
 struct PhotonSoA { const float4* a; const uint4* b; };
@@ -78,7 +70,7 @@ struct BdState {
     BdShadowRec* shadowQ;
     BdMergeRec* mergeQ;         // (1 + kMergeGroup) * nLocal records: [0, nLocal) step 0, the rest the current group of deeper steps
     int* mergeOrder;            // processing order of a group's Lambert records (kMergeGroup * nLocal)
-    uint32_t* mergeBinCount;    // kMergeBins + scan scratch
+    uint32_t* mergeKeys;        // sort keys of a queue's Lambert records (kMergeGroup * nLocal)
     int* counters;     // (kMaxBdDepth + 1) * BC_STRIDE
     unsigned long long* stats;   // [0] closest rays [1] shadow rays [2] photons stored [3] light vertices stored [4] merges accepted [5] merge candidates (photons in the 27 cells) [6] merge queries (eye vertices gathered)
     int nLocal;
@@ -109,7 +101,7 @@ struct BdParams {
     PhotonSoA photons;                 // records in cell order (eye pass), merge-ready
     const uint32_t* cellStart; const uint32_t* cellEnd;
     GridParams grid;
-    MergeBins bins;
+    unsigned long long gridMagic;      // floor((2^64 - 1) / grid.tableSize) + 1: the table slot of a cell without a division (fastMod)
 };
 
 NV_D int localToPixel(const BdParams& P, int l, int& x, int& y) {

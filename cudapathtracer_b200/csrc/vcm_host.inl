@@ -27,6 +27,7 @@ struct BdEngine {
     int maxPhotons = 0, photonCount = 0;
     HashGridDevice grid;
     bool gridAllocated = false;
+    RadixSortPlan mergePlan; bool mergePlanMade = false;      // orders a queue's merge records by photon-grid cell
     int* d_counts = nullptr; int* h_counts = nullptr; int* h_countsDev = nullptr;      // h_counts: mapped page-locked, h_countsDev its device address
     float mergeRadius = 0.f;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -52,11 +53,12 @@ static void bdFree(BdEngine& e) {
     BdState& s = e.st;
     cudaFree(s.rayO); cudaFree(s.rayD); cudaFree(s.beta); cudaFree(s.prevP); cudaFree(s.dv); cudaFree(s.rng); cudaFree(s.hit);
     cudaFree(s.queue[0]); cudaFree(s.queue[1]); cudaFree(s.pathLen); cudaFree(s.medium); cudaFree(s.lvA); cudaFree(s.lvB); cudaFree(s.lvC);
-    cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.mergeOrder); cudaFree(s.mergeBinCount); cudaFree(s.counters); cudaFree(s.stats);
+    cudaFree(s.shadowQ); cudaFree(s.mergeQ); cudaFree(s.mergeOrder); cudaFree(s.mergeKeys); cudaFree(s.counters); cudaFree(s.stats);
     for (int r = 0; r < 16; ++r) if (e.peerBase[r] && e.peerIpc[r]) cudaIpcCloseMemHandle(e.peerBase[r]);
     cudaFree(e.slabs); cudaFree(e.photonsAll); cudaFree(e.photonsSorted); cudaFree(e.d_counts);
     if (e.h_counts) cudaFreeHost(e.h_counts);
     if (e.gridAllocated) hashGridFree(e.grid);
+    if (e.mergePlanMade) radixSortPlanDestroy(e.mergePlan);
     if (e.ev0) { cudaEventDestroy(e.ev0); cudaEventDestroy(e.ev1); }
     for (cudaEvent_t ev : e.evs) cudaEventDestroy(ev);
     if (e.ownStream && e.stream) cudaStreamDestroy(e.stream);
@@ -100,7 +102,7 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
     if (e.mode == BD_MODE_VCM) {
         A((void**)&s.mergeQ, n * (size_t)(1 + kMergeGroup) * sizeof(BdMergeRec));
         A((void**)&s.mergeOrder, n * (size_t)kMergeGroup * sizeof(int));
-        A((void**)&s.mergeBinCount, ((size_t)kMergeBins + 2048) * sizeof(uint32_t));
+        A((void**)&s.mergeKeys, n * (size_t)kMergeGroup * sizeof(uint32_t));
     }
     A((void**)&s.counters, (kMaxBdDepth + 1) * BC_STRIDE * sizeof(int));
     A((void**)&s.stats, 8 * sizeof(unsigned long long));
@@ -124,6 +126,8 @@ static int bdAlloc(BdEngine& e, NovumScene* scene, const NovumRenderConfig& cfg,
         int rc = hashGridAlloc(e.grid, e.maxPhotons);
         if (rc) return rc;
         e.gridAllocated = true;
+        if ((err = radixSortPlanCreate(e.mergePlan, (int)std::min<size_t>(n * (size_t)kMergeGroup, 0x7fffffffull))) != cudaSuccess) return (int)err;
+        e.mergePlanMade = true;
     }
     cudaMemsetAsync(s.stats, 0, 8 * sizeof(unsigned long long), e.stream);
     cudaMemsetAsync(e.slabs, 0, e.slabWords * 16 * e.world * e.slabBuffers, e.stream);
@@ -153,17 +157,13 @@ static BdParams bdParams(const BdEngine& e, int iter, float4* colors) {
     if (e.peerWrite)
         for (int r = 0; r < e.world; ++r)
             if (r != e.rank && e.peerBase[r]) P.peerSlab[P.numPeers++] = (uint4*)e.peerBase[r] + mySlab;
-    for (int k = 0; k < 3; ++k) {
-        float ext = e.scene->sceneMax[k] - e.scene->sceneMin[k];
-        (&P.bins.minX)[k] = e.scene->sceneMin[k];
-        (&P.bins.sx)[k] = ext > 0.0f ? (float)(1 << kMergeBinBits) / ext : 0.0f;
-    }
     {   // PhotonSoA over the one allocation: a | b, each maxPhotons (rounded to 64) 16 B entries
         size_t np = ((size_t)e.maxPhotons + 63) & ~(size_t)63;
         P.photons.a = reinterpret_cast<const float4*>(e.photonsSorted);
         P.photons.b = e.photonsSorted + np;
     }
     P.cellStart = e.grid.cellStart; P.cellEnd = e.grid.cellEnd; P.grid = e.grid.params;
+    P.gridMagic = e.grid.tableSize ? 0xFFFFFFFFFFFFFFFFull / e.grid.tableSize + 1ull : 0ull;
     return P;
 }
 
@@ -174,10 +174,18 @@ namespace nv {
 static inline int bdGrid() { return smCount() * 8; }
 static inline bool bdNested(const BdEngine& e) { return (e.scene->features & NOVUM_FEATURE_NESTED_BIDIR) != 0; }
 
-// bdMergeLambert<MIS>: 4 eye vertices per warp, register allocation held to 64 (8 resident CTAs of 128 threads per SM)
-static void launchMergeLambert(bool mis, int grid, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P, const MergeQueue& mq) {
-    if (mis) bdMergeLambert<true><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
-    else bdMergeLambert<false><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq);
+// bdMergeLambert<MIS, MINB>: 4 eye vertices per warp; MINB = resident CTAs of 128 threads per SM the register allocation is held to
+// (8 -> 64 registers, 7 -> 72, 6 -> 80); NOVUM_MERGE_MINB in the environment picks the build
+static int mergeMinB() {
+    static int v = 0;
+    if (!v) { const char* e = getenv("NOVUM_MERGE_MINB"); const int k = e ? atoi(e) : kMergeCtasPerSm; v = (k == 6 || k == 7) ? k : 8; }
+    return v;
+}
+static void launchMergeLambert(bool mis, cudaStream_t s, const SceneView& sc, const BdState& st, const BdParams& P, const MergeQueue& mq) {
+    const int b = mergeMinB(), grid = smCount() * b;
+    if (b == 8) { if (mis) bdMergeLambert<true, 8><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq); else bdMergeLambert<false, 8><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq); }
+    else if (b == 7) { if (mis) bdMergeLambert<true, 7><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq); else bdMergeLambert<false, 7><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq); }
+    else { if (mis) bdMergeLambert<true, 6><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq); else bdMergeLambert<false, 6><<<grid, kMergeThreads, 0, s>>>(sc, st, P, mq); }
 }
 
 // light pass of iteration `iter` for this rank's rows: fills the light-vertex cache, appends photons to this rank's slab,
@@ -246,7 +254,8 @@ static int bdBuildGrid(BdEngine& e, int iter) {
         ++e.launches;
         src = e.photonsAll;
     }
-    int rc = hashGridBuildAoS(e.grid, reinterpret_cast<const float*>(src), 8, e.photonCount, e.scene->sceneMin, P.mergeRadius, s);
+    // cells of r / kMergeFine (vcm.cu): the merge looks at the cells within reach of a vertex, not at a fixed 27
+    int rc = hashGridBuildAoS(e.grid, reinterpret_cast<const float*>(src), 8, e.photonCount, e.scene->sceneMin, P.mergeRadius / (float)kMergeFine, s);
     if (rc) return rc;
     e.launches += e.grid.launches;
     if (e.photonCount > 0) {
@@ -294,18 +303,22 @@ static int bdEyePass(BdEngine& e, int iter, float4* colors) {
         if (shadows) { bdResolve<<<grid, kBdThreads, 0, s>>>(sc, st, colors, cnt); ++e.launches; bdTick(e, 2); }
         const bool flush = !grouped || step == groupFirst + kMergeGroup - 1 || step == numSteps - 1;
         if (merging && flush) {
-            if (!P.paintWeight) {      // every Lambert queue is binned: records of one cell become neighbours (primary hits: -10 % pairs scanned)
-                bdFillWords<<<bdGrid(), 256, 0, s>>>(reinterpret_cast<uint4*>(st.mergeBinCount), (size_t)kMergeBins * sizeof(uint32_t) / 16, 0u);
-                bdMergeBinCount<<<grid, 256, 0, s>>>(mq, P.bins, P.grid, st.mergeBinCount);
-                int scanLaunches = 0;
-                exclusiveScanU32(st.mergeBinCount, kMergeBins, st.mergeBinCount + kMergeBins, s, &scanLaunches);
-                bdMergeBinScatter<<<grid, 256, 0, s>>>(mq, P.bins, P.grid, st.mergeBinCount, st.mergeOrder);
-                e.launches += 2 + scanLaunches;
+            if (!P.paintWeight) {      // every Lambert queue is put in photon-cell order (bdMergeKeys): radix sort with the count on the device
+                int cellBits = 1;
+                for (int k = 0; k < 3; ++k) {
+                    const float cells = (e.scene->sceneMax[k] - e.scene->sceneMin[k]) / P.grid.cell;
+                    while (cellBits < 30 && (float)(1 << cellBits) < cells + 2.0f) ++cellBits;
+                }
+                const int shift = cellBits > 10 ? cellBits - 10 : 0;
+                bdMergeKeys<<<grid, 256, 0, s>>>(mq, P.grid, shift, st.mergeKeys, st.mergeOrder);
+                int sortLaunches = 0;
+                radixSortPairsDeviceCount(e.mergePlan, st.mergeKeys, reinterpret_cast<uint32_t*>(st.mergeOrder), mq.cap, mq.cnt + BC_MERGE, 30, s, &sortLaunches);
+                e.launches += 1 + sortLaunches;
                 mq.order = st.mergeOrder;
             }
             // Lambert vertices (front of the queue) and all other materials (back): a kernel whose queue is empty exits at once
             if (P.paintWeight) {}
-            else launchMergeLambert(P.doMis != 0, mgrid, s, sc, st, P, mq);
+            else launchMergeLambert(P.doMis != 0, s, sc, st, P, mq);
             bdMerge<<<mgrid, kMergeThreads, 0, s>>>(sc, st, P, mq);
             e.launches += P.paintWeight ? 1 : 2; bdTick(e, 3);
         }
@@ -456,7 +469,8 @@ static int bdPreloadKernels() {
     L((const void*)bdFillWords); L((const void*)bdZeroInts); L((const void*)bdLightStart); L((const void*)bdExtend<false>); L((const void*)bdExtend<true>);
     L((const void*)bdLightStep<false>); L((const void*)bdLightStep<true>); L((const void*)bdResolve); L((const void*)bdPushHeader); L((const void*)bdWaitSlabs); L((const void*)bdSlabCounts);
     L((const void*)bdCompactSlabs); L((const void*)bdReorderPhotons); L((const void*)bdEyeStart); L((const void*)bdEyeStep<false>); L((const void*)bdEyeStep<true>);
-    L((const void*)bdMergeBinCount); L((const void*)bdMergeBinScatter); L((const void*)bdMergeLambert<true>); L((const void*)bdMergeLambert<false>);
+    L((const void*)bdMergeKeys); L((const void*)bdMergeLambert<true, 8>); L((const void*)bdMergeLambert<false, 8>); L((const void*)bdMergeLambert<true, 7>);
+    L((const void*)bdMergeLambert<false, 7>); L((const void*)bdMergeLambert<true, 6>); L((const void*)bdMergeLambert<false, 6>);
     L((const void*)bdMerge);
     if (e != cudaSuccess) return (int)e;
     return hashGridPreload();
