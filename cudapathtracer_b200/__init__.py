@@ -7,6 +7,6 @@ raises, loudly.
 from .binding import (  # noqa: F401
     NovumError, lib, lib_path, Scene, HashGrid, VcmSession, RenderConfig, Camera, RenderStats, Shard, Constants,
     make_scene, load_config, material_table, camera_make, device_count, DECLARED_SYMBOLS,
-    FRAME_PROGRESSIVE, FRAME_FINAL, bmp_row_bytes, frame_finish, frame_finish_device, obj_parse, accum_save, accum_info, accum_load, frame_save_bmp, frame_save_bmp_async, frame_save_wait, save_bmp, gamma_steps,
+    FRAME_PROGRESSIVE, FRAME_FINAL, bmp_row_bytes, frame_finish, frame_finish_device, obj_parse, ObjDeviceMesh, accum_save, accum_info, accum_load, frame_save_bmp, frame_save_bmp_async, frame_save_wait, save_bmp, gamma_steps,
     hashgrid_build_static, STATIC_GRID_MAX_PHOTONS, LaunchCacheStats, TileRank,
 )

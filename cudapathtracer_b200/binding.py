@@ -145,6 +145,16 @@ def _declare(L):
     L.novum_obj_free.restype = None
     L.novum_obj_counts.argtypes = [vp, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci)]
     L.novum_obj_download.argtypes = [vp, vp, vp, vp, vp]
+    L.novum_obj_device_create.argtypes = [C.POINTER(vp)]
+    L.novum_obj_device_destroy.argtypes = [vp]
+    L.novum_obj_device_destroy.restype = None
+    L.novum_obj_device_append_file.argtypes = [vp, C.c_char_p, C.POINTER(cf * 3), ci, cf]
+    L.novum_obj_device_append_text.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(cf * 3), ci, cf]
+    L.novum_obj_device_counts.argtypes = [vp] + [C.POINTER(ci)] * 5
+    L.novum_obj_device_arrays.argtypes = [vp] + [C.POINTER(vp)] * 4
+    L.novum_obj_device_download.argtypes = [vp, vp, vp, vp, vp]
+    L.novum_obj_device_timings.argtypes = [vp, C.POINTER(cf), C.POINTER(cf), C.POINTER(ci), C.POINTER(C.c_longlong)]
+    L.novum_scene_from_obj_device.argtypes = [vp, vp, ci, vp, ci, C.POINTER(vp)]
     L.novum_accum_save.argtypes = [C.c_char_p, vp, ci, ci, ci, C.c_uint64, ci]
     L.novum_accum_info.argtypes = [C.c_char_p, C.POINTER(ci), C.POINTER(ci), C.POINTER(ci), C.POINTER(C.c_uint64), C.POINTER(ci)]
     L.novum_accum_load.argtypes = [C.c_char_p, vp, ci, ci, C.POINTER(ci), C.POINTER(C.c_uint64)]
@@ -355,6 +365,69 @@ def obj_parse(path, emission=(0.0, 0.0, 0.0), material_id=0, y_offset=0.0, threa
         return pos, nrm, uv, tris, n[4].value
     finally:
         lib().novum_obj_free(h)
+
+
+class ObjDeviceMesh:
+    """OBJ files parsed ON THE GPU (novum_obj_device_*, csrc/obj_device.cu): accumulates the files of a scene in device memory, in
+    order, with the arrays of obj_parse bit for bit. NovumError(-5, unsupported) leaves the mesh unchanged: use obj_parse for that file."""
+
+    def __init__(self):
+        self.h = C.c_void_p()
+        _check(lib().novum_obj_device_create(C.byref(self.h)), "novum_obj_device_create")
+
+    def close(self):
+        if self.h:
+            lib().novum_obj_device_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def append_file(self, path, emission=(0.0, 0.0, 0.0), material_id=0, y_offset=0.0):
+        e = (C.c_float * 3)(*[float(x) for x in emission])
+        _check(lib().novum_obj_device_append_file(self.h, os.fsencode(path), C.byref(e), int(material_id), float(y_offset)), "novum_obj_device_append_file")
+
+    def append_text(self, text, emission=(0.0, 0.0, 0.0), material_id=0, y_offset=0.0):
+        e = (C.c_float * 3)(*[float(x) for x in emission])
+        text = bytes(text)
+        _check(lib().novum_obj_device_append_text(self.h, text, len(text), C.byref(e), int(material_id), float(y_offset)), "novum_obj_device_append_text")
+
+    def counts(self):
+        n = [C.c_int() for _ in range(5)]
+        _check(lib().novum_obj_device_counts(self.h, *[C.byref(x) for x in n]), "novum_obj_device_counts")
+        return tuple(x.value for x in n)
+
+    def device_arrays(self):
+        p = [C.c_void_p() for _ in range(4)]
+        _check(lib().novum_obj_device_arrays(self.h, *[C.byref(x) for x in p]), "novum_obj_device_arrays")
+        return tuple(x.value for x in p)
+
+    def download(self):
+        """-> (pos (n,4), nrm (n,4), uv (n,2), tris TRI_DTYPE, n_lights), the layout of obj_parse."""
+        n = self.counts()
+        pos = np.zeros((n[0], 4), np.float32); nrm = np.zeros((n[1], 4), np.float32)
+        uv = np.zeros((n[2], 2), np.float32); tris = np.zeros(n[3], TRI_DTYPE)
+        _check(lib().novum_obj_device_download(self.h, _ptr(pos), _ptr(nrm), _ptr(uv), _ptr(tris)), "novum_obj_device_download")
+        return pos, nrm, uv, tris, n[4]
+
+    def timings(self):
+        up, k, l, b = C.c_float(), C.c_float(), C.c_int(), C.c_longlong()
+        _check(lib().novum_obj_device_timings(self.h, C.byref(up), C.byref(k), C.byref(l), C.byref(b)), "novum_obj_device_timings")
+        return {"upload_ms": up.value, "kernel_ms": k.value, "launches": l.value, "text_bytes": b.value}
+
+    def to_scene(self, mats, textures=None):
+        """The arrays move into a Scene (BVH8 build on the device); the mesh is empty afterwards."""
+        mats = np.ascontiguousarray(mats, MAT_DTYPE)
+        ntex = 0
+        if textures is not None:
+            textures = np.ascontiguousarray(textures, np.float32).reshape(-1, 4)
+            ntex = len(textures)
+        h = C.c_void_p()
+        _check(lib().novum_scene_from_obj_device(self.h, _ptr(mats), len(mats), _ptr(textures), ntex, C.byref(h)), "novum_scene_from_obj_device")
+        return Scene(h)
 
 
 def accum_save(path, colors, sample_count, seed=103033, integrator=0):

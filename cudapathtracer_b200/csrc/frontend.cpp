@@ -613,8 +613,37 @@ int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene
     }
     NovumMaterial mats[24];
     buildMaterialTable(mats, ts, tw, th);
-    HostMesh M;
     const auto parseT0 = std::chrono::steady_clock::now();
+    // The OBJ files are parsed on the device (obj_device.cu) unless NOVUM_OBJ_DEVICE=0; a file with spellings its rules do not read
+    // themselves (NOVUM_E_UNSUPPORTED) sends the whole config through the host loader below, which gives the same arrays.
+    const char* objDev = getenv("NOVUM_OBJ_DEVICE");
+    NovumObjDeviceMesh* dm = nullptr;
+    if (!(objDev && objDev[0] == '0') && novum_obj_device_create(&dm) == 0) {
+        bool ok = true;
+        for (const MeshCfg& m : meshes) {
+            float e[3] = {m.mult * m.color[0], m.mult * m.color[1], m.mult * m.color[2]};
+            bool emissive = m.color[0] * m.color[0] + m.color[1] * m.color[1] + m.color[2] * m.color[2] > 0.f;
+            float yoff = emissive ? -0.01f * renderNumber : 0.f;   // main.cu:476-478
+            if (m.materialID < 0 || m.materialID >= 24) { novum_obj_device_destroy(dm); return NOVUM_E_ARG; }
+            int r = novum_obj_device_append_file(dm, m.path.c_str(), e, m.materialID, yoff);
+            if (r == NOVUM_E_IO) r = novum_obj_device_append_file(dm, (cfgDir + "/" + m.path).c_str(), e, m.materialID, yoff);
+            if (r == NOVUM_E_IO) r = novum_obj_device_append_file(dm, (cfgDir + "/../" + m.path).c_str(), e, m.materialID, yoff);
+            if (r == NOVUM_E_IO) fprintf(stderr, "Error: Could not open OBJ file %s\n", m.path.c_str());   // main.cu:941-944: keeps going
+            else if (r) { ok = false; break; }
+        }
+        int nTri = 0;
+        novum_obj_device_counts(dm, nullptr, nullptr, nullptr, &nTri, nullptr);
+        if (ok && nTri > 0) {
+            const float parseMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - parseT0).count();
+            rc = novum_scene_from_obj_device(dm, mats, 24, texels.data(), (int)texels.size(), out);
+            novum_obj_device_destroy(dm);
+            if (rc == 0) for (const MeshCfg& m : meshes) (*out)->meshPaths.push_back(m.path);
+            if (rc == 0) (*out)->parseMs = parseMs;
+            return rc;
+        }
+        novum_obj_device_destroy(dm);
+    }
+    HostMesh M;
     for (const MeshCfg& m : meshes) {
         float e[3] = {m.mult * m.color[0], m.mult * m.color[1], m.mult * m.color[2]};
         bool emissive = m.color[0] * m.color[0] + m.color[1] * m.color[1] + m.color[2] * m.color[2] > 0.f;

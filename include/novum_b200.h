@@ -27,13 +27,14 @@
 #ifndef NOVUM_B200_H
 #define NOVUM_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define NOVUM_ABI_VERSION 5
+#define NOVUM_ABI_VERSION 6
 
 /* error codes (negative; positive return values are cudaError_t) */
 #define NOVUM_OK             0
@@ -230,6 +231,31 @@ int  novum_obj_parse(const char* path, const float emission[3], int materialID, 
 void novum_obj_free(NovumObjMesh* m);
 int  novum_obj_counts(const NovumObjMesh* m, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights);
 int  novum_obj_download(const NovumObjMesh* m, NovumFloat4* positions, NovumFloat4* normals, NovumFloat2* uvs, NovumTriangle* tris);
+/* ---- the OBJ front end on the device (the step directly before the path; replaces main.cu:936-1068 readObjSimple) ----
+ * The text of the file is copied to the GPU as it is read and parsed there, one thread per line (csrc/obj_device.cu): the arrays are
+ * those of novum_obj_parse bit for bit (positions, generated face normals, the shared zero uv, dropped triangles, light indices), but
+ * they are born in device memory and go straight into the BVH8 build. A mesh object accumulates the files of one scene in order, as
+ * the reference's initRender appends meshes (main.cu:470-503). Files with spellings the device rules do not read themselves (more than
+ * 15 significant digits, inf / nan / hex numbers, faces with more than 16 corners, 2 GiB of text) return NOVUM_E_UNSUPPORTED and leave
+ * the mesh unchanged: parse those with novum_obj_parse. novum_scene_load_config uses this path by itself (NOVUM_OBJ_DEVICE=0 turns
+ * it off) and falls back to the host loader for such files. */
+typedef struct NovumObjDeviceMesh NovumObjDeviceMesh;
+int  novum_obj_device_create(NovumObjDeviceMesh** out);
+void novum_obj_device_destroy(NovumObjDeviceMesh* m);
+int  novum_obj_device_append_file(NovumObjDeviceMesh* m, const char* path, const float emission[3], int materialID, float yOffset);
+/* the same for text that is already in (host) memory */
+int  novum_obj_device_append_text(NovumObjDeviceMesh* m, const char* text, size_t bytes, const float emission[3], int materialID, float yOffset);
+int  novum_obj_device_counts(const NovumObjDeviceMesh* m, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights);
+/* DEVICE pointers to the accumulated arrays (valid until the next append / destroy / novum_scene_from_obj_device) */
+int  novum_obj_device_arrays(const NovumObjDeviceMesh* m, const NovumFloat4** d_positions, const NovumFloat4** d_normals,
+                             const NovumFloat2** d_uvs, const NovumTriangle** d_tris);
+int  novum_obj_device_download(const NovumObjDeviceMesh* m, NovumFloat4* positions, NovumFloat4* normals, NovumFloat2* uvs, NovumTriangle* tris);
+/* wall time of reading + copying the text, CUDA-event time of the parse kernels, their launch count, bytes of text parsed so far */
+int  novum_obj_device_timings(const NovumObjDeviceMesh* m, float* uploadMs, float* kernelMs, int* launches, long long* textBytes);
+/* scene from the mesh: the arrays MOVE into the scene (the mesh is empty afterwards and may be reused or destroyed); materials and
+ * textures are host arrays as in novum_scene_create, whose index checks run on the device here (NOVUM_E_ARG). */
+int  novum_scene_from_obj_device(NovumObjDeviceMesh* m, const NovumMaterial* mats, int nMat, const NovumFloat4* textures, int nTexels,
+                                 NovumScene** out);
 int  novum_material_table(NovumMaterial* out24);                      /* main.cu:397-467, 24 entries */
 int  novum_camera_make(const NovumRenderConfig* cfg, NovumCamera* out); /* objects.cuh:221-266, 309-325 */
 /* copies of the scene arrays back to host, for oracles and tests */

@@ -16,7 +16,7 @@ def test_library_exports_every_declared_symbol(built):
     assert len(nb.DECLARED_SYMBOLS) >= 40
     missing = [s for s in nb.DECLARED_SYMBOLS if not hasattr(L, s)]
     assert not missing, f"declared in novum_b200.h but not exported: {missing}"
-    assert L.novum_abi_version() == 5
+    assert L.novum_abi_version() == 6
 
 
 def test_exports_are_plain_c_symbols(built):

@@ -183,17 +183,20 @@ def test_accumulator_checkpoint_roundtrip_and_damage(built, tmp_path):
         nb.accum_save(str(tmp_path / "no_dir" / "x.novumacc"), acc, 1)
 
 
-def _adversarial_obj(path, rng, n_lines=600):
-    """An OBJ whose result depends on everything the sequential loader decides from 'how far the file has been read'."""
+def _adversarial_obj(path, rng, n_lines=600, device_ok=False):
+    """An OBJ whose result depends on everything the sequential loader decides from 'how far the file has been read'.
+    device_ok: only number spellings the device parser's rules read themselves (obj_parse.cuh: at most 15 significant digits, no nan)."""
     out, nv, nvt, nvn = [], 0, 0, 0
+    long_fmt = "%.15g" if device_ok else "%.17g"
+    odd_vn = ["vn 0 0 0", "vn 1 2", "vn x 0 1" if device_ok else "vn nan 0 1", "vn .5 -.25e1 +1.", "vn 1e-7 1e-7 0"]
     for k in range(n_lines):
         r = rng.random()
         if r < 0.30 or nv < 4:
-            out.append("v %s %s %s" % tuple(rng.choice(["%.6f", "%.3e", "%d", "%.17g"]) % x for x in rng.normal(0, 3, 3))); nv += 1
+            out.append("v %s %s %s" % tuple(rng.choice(["%.6f", "%.3e", "%d", long_fmt]) % x for x in rng.normal(0, 3, 3))); nv += 1
         elif r < 0.38:
             out.append("vt %.5f %.5f" % tuple(rng.random(2))); nvt += 1
         elif r < 0.46:
-            out.append(rng.choice(["vn %.4f %.4f %.4f" % tuple(rng.normal(0, 1, 3)), "vn 0 0 0", "vn 1 2", "vn nan 0 1"])); nvn += 1
+            out.append(rng.choice(["vn %.4f %.4f %.4f" % tuple(rng.normal(0, 1, 3))] + odd_vn)); nvn += 1
         elif r < 0.50:
             out.append(rng.choice(["# comment", "s off", "", "g group", "usemtl m", "   "]))
         else:
@@ -246,3 +249,76 @@ def test_obj_parse_equals_python_loader(scene_dirs):
     want = np.array(tris, g[3].dtype)
     for f in ("aInd", "bInd", "cInd", "naInd", "nbInd", "ncInd", "uvaInd", "uvbInd", "uvcInd", "materialID", "lightInd", "triInd"):
         assert np.array_equal(want[f], g[3][f]), f
+
+
+def _obj_rules_lib(built):
+    """tests/obj_rules_host.cpp: the device parser's per-line rules (csrc/obj_parse.cuh) compiled for the CPU."""
+    import ctypes as C
+    import subprocess
+    here = os.path.dirname(os.path.abspath(__file__))
+    out = os.path.join(here, "_build", "libobjrules.so")
+    src = os.path.join(here, "obj_rules_host.cpp")
+    hdr = os.path.join(here, "..", "cudapathtracer_b200", "csrc", "obj_parse.cuh")
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-I" + os.path.join(here, "..", "include"),
+                               "-I" + os.path.join(here, "..", "cudapathtracer_b200", "csrc"), src, "-o", out])
+    lib = C.CDLL(out)
+    lib.obj_rules_parse.restype = C.c_void_p
+    lib.obj_rules_parse.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_float), C.c_int, C.c_float]
+    lib.obj_rules_free.argtypes = [C.c_void_p]
+    lib.obj_rules_unsupported.argtypes = [C.c_void_p]
+    lib.obj_rules_counts.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 5
+    lib.obj_rules_download.argtypes = [C.c_void_p] + [C.c_void_p] * 4
+    return lib
+
+
+def _obj_rules_parse(lib, text, emission, material_id, y_offset):
+    import ctypes as C
+    from cudapathtracer_b200.binding import TRI_DTYPE as ref_tri_dtype
+    e = (C.c_float * 3)(*emission)
+    h = lib.obj_rules_parse(text, len(text), e, material_id, y_offset)
+    try:
+        n = [C.c_int() for _ in range(5)]
+        lib.obj_rules_counts(h, *[C.byref(x) for x in n])
+        pos = np.zeros((n[0].value, 4), np.float32); nrm = np.zeros((n[1].value, 4), np.float32)
+        uv = np.zeros((n[2].value, 2), np.float32); tris = np.zeros(n[3].value, ref_tri_dtype)
+        lib.obj_rules_download(h, pos.ctypes.data, nrm.ctypes.data, uv.ctypes.data, tris.ctypes.data)
+        return (pos, nrm, uv, tris, n[4].value), bool(lib.obj_rules_unsupported(h))
+    finally:
+        lib.obj_rules_free(h)
+
+
+def test_obj_device_rules_equal_host_loader(built, tmp_path):
+    """The per-line rules the device OBJ parser runs (obj_parse.cuh), driven in file order on the CPU, give the host loader's arrays bit
+    for bit; spellings outside the rules are reported as unsupported instead of being guessed."""
+    lib = _obj_rules_lib(built)
+    rng = np.random.default_rng(77)
+    for trial in range(16):
+        p = str(tmp_path / f"dev{trial}.obj")
+        _adversarial_obj(p, rng, n_lines=700, device_ok=True)
+        e = (0.0, 0.0, 0.0) if trial % 3 else (5.0, 4.0, 3.0)
+        ref = nb.obj_parse(p, e, 7, 0.25, threads=1, chunk_bytes=1 << 30)
+        got, unsupported = _obj_rules_parse(lib, open(p, "rb").read(), e, 7, 0.25)
+        assert not unsupported, trial
+        for a, b in zip(ref[:4], got[:4]):
+            assert a.shape == b.shape and a.tobytes() == b.tobytes(), trial
+        assert got[4] == ref[4]
+    # hand-written corner cases: empty file pieces, no trailing newline, blank lines, a face before its vertices, NUL inside a line
+    cases = [b"", b"\n", b"v 1 2 3", b"v 1 2 3\nv 4 5 6\nv 7 8 10\nf 1 2 3", b"f 1 2 3\nv 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n\n\n",
+             b"v 0 0 0\nv 1 0 0\nv 0 1 0\nv 1 1 0\nvt 0.5 0.25\nf 1/1 2/1 3/1 4/1\nf 1 2 3\nf 1//1 2//1 3//1\nvn 0 0 1\nf 2//1 3//1 4//1\n",
+             b"v 0 0 0\nv 1 0 0\nv 0 1\x00 5\nf 1 2 3\n", b"v 0 0 0\r\nv 2 0 0\r\nv 0 2 0\r\nf 1/ 2/ 3/\r\nf 1// 2// 3//\r\nf 0 1 2 3\r\n",
+             b"vt 1\nvtx 3 4\nvnormal 1 0 0\nv\t1 1 1\nv 2 1 1\nv 1 2 1\nf\t1 2 3 1 2\n", b"v 1e3 -2.5E-2 +.5\nv 1. 0 0\nv 0 1e+1 0\nf 1 2 3\n"]
+    for text in cases:
+        p = str(tmp_path / "case.obj")
+        open(p, "wb").write(text)
+        ref = nb.obj_parse(p, (1.0, 0.0, 0.0), 3, -0.5, threads=1, chunk_bytes=1 << 30)
+        got, unsupported = _obj_rules_parse(lib, text, (1.0, 0.0, 0.0), 3, -0.5)
+        assert not unsupported, text
+        for a, b in zip(ref[:4], got[:4]):
+            assert a.shape == b.shape and a.tobytes() == b.tobytes(), text
+        assert got[4] == ref[4], text
+    for text in (b"v 0.12345678901234567 0 0\n", b"v nan 0 0\n", b"v inf 0 0\n", b"v 0x10 0 0\n", b"v 1e40 0 0\n", b"vn 1 1 1e-30\n",
+                 b"v 0 0 0\nf " + b" ".join(b"1" for _ in range(17)) + b"\n", b"v 0 0 0\nf 12345678901 1 1\n"):
+        _, unsupported = _obj_rules_parse(lib, text, (0.0, 0.0, 0.0), 0, 0.0)
+        assert unsupported, text
