@@ -15,6 +15,7 @@ Workloads = BASELINE.json configs on the generated stand-in scenes (the referenc
   trace_batch  SURVEY 8d micro: closest-hit / any-hit kernels alone on identical ray batches (ours vs the reference's routines)
   hashgrid     SURVEY 8d micro / a15: photon hash grid build vs the reference's buildHashGrid on identical photon sets
   frame_finish SURVEY 8f row 2: the step after the path (clean + tonemap + gamma + BGR8 rows of a 4K frame), metric Mpixels/s
+  obj_parse    SURVEY 8f row 1: the step before the path (OBJ text -> device arrays, parsed on the GPU), metric MB/s of OBJ text
 metric = Mrays/s: closest-hit + shadow rays actually traced (device counters); paths/s is reported beside it.
 
   python bench.py --gpus N --steps K --warmup W            our arm (torchrun for N > 1)
@@ -657,6 +658,104 @@ def run_frame_reference(args):
                       "e2e": {"value": val, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+OBJ_DESC = "OBJ front end (SURVEY 8f row 1): the dragon stand-in's 92 MB of OBJ text -> positions / normals / uvs / 80 B Triangle records in device memory"
+
+
+def run_obj(args):
+    """--workload obj_parse: the step before the path. One step = one parse of the dragon stand-in's OBJ file into device arrays.
+    `value` = text already in HBM (novum_obj_device_append_device_text: 12 launches + 3 count read-backs); `e2e` = file (page cache)
+    -> pinned double buffers -> HBM -> arrays (novum_obj_device_append_file). Parity of this very run: the arrays equal the host
+    loader's bit for bit (novum_obj_parse, the restatement of main.cu:936-1068 that tests/test_host.py pins)."""
+    import numpy as np
+    import torch
+    import cudapathtracer_b200 as nb
+    if not torch.cuda.is_available() or nb.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
+    sdir = scene_dir_for("dragon_nee", args.detail, 0, None)
+    path = os.path.join(sdir, "scenedata", "dragon_vrip.obj")
+    raw = np.fromfile(path, np.uint8)
+    nbytes = int(raw.size)
+    d_text = torch.from_numpy(raw).cuda()
+    m = nb.ObjDeviceMesh()
+    clocks = ClockSampler(0)
+    for i in range(max(args.warmup, 1)):
+        m.reset(); m.append_device_text(d_text.data_ptr(), nbytes, (0.0, 0.0, 0.0), 5, 0.0)
+    got = m.download()
+    torch.cuda.synchronize()
+    clocks.start()
+    kernel_ms, wall = [], []
+    for i in range(args.steps):
+        m.reset()
+        t0 = time.time()
+        m.append_device_text(d_text.data_ptr(), nbytes, (0.0, 0.0, 0.0), 5, 0.0)
+        wall.append((time.time() - t0) * 1e3)
+        kernel_ms.append(m.timings()["kernel_ms"])
+    ms = float(np.mean(kernel_ms))
+    e2e, up = [], []
+    for i in range(args.warmup + args.steps):
+        m.reset()
+        t0 = time.time()
+        m.append_file(path, (0.0, 0.0, 0.0), 5, 0.0)
+        if i >= args.warmup:
+            e2e.append((time.time() - t0) * 1e3); up.append(m.timings()["upload_ms"])
+    clk = clocks.stop()
+    e2e_ms = float(np.mean(e2e))
+    n = m.counts()
+    t0 = time.time(); ref = nb.obj_parse(path, (0.0, 0.0, 0.0), 5, 0.0); host_ms = (time.time() - t0) * 1e3
+    t0 = time.time(); ref = nb.obj_parse(path, (0.0, 0.0, 0.0), 5, 0.0); host_ms = min(host_ms, (time.time() - t0) * 1e3)
+    parity = all(a.shape == b.shape and a.tobytes() == b.tobytes() for a, b in zip(ref[:4], got[:4]))
+    m.close()
+    out_bytes = 16 * n[0] + 16 * n[1] + 8 * n[2] + 80 * n[3]
+    algo = nbytes + out_bytes                 # text read once + every record written once
+    peak, peak_src = peaks()
+    line = {"metric": "MB/s of OBJ text", "value": nbytes / (ms * 1e-3) / 1e6, "unit": "MB/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": OBJ_DESC, "text_bytes": nbytes, "positions": n[0], "normals": n[1], "uvs": n[2], "triangles": n[3],
+                       "l2": "92 MB of text + 100 MB of records per step against a 126 MB L2; the text is re-read by three line passes",
+                       "timing": "CUDA events around the 12 launches of one parse on the parser's stream (includes the three count read-backs between them)"},
+            "e2e": {"value": nbytes / (e2e_ms * 1e-3) / 1e6, "unit": "MB/s", "ms_per_step": e2e_ms, "read_and_copy_ms": float(np.mean(up)),
+                    "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 3 * 32,
+                    "note": "novum_obj_device_append_file: pread of the file (page cache) into pinned double buffers by 4 threads, copies queued as the "
+                            "pieces arrive, then the parse; the arrays stay in device memory for the BVH8 build (nothing but three 32 B count records comes back)"},
+            "gpu_launches": 12 * args.steps, "clocks": clk, "parity_ok": bool(parity), "parity": "all four arrays equal novum_obj_parse (host loader) bit for bit",
+            "host_call_ms": float(np.mean(wall)),
+            "roofline": {"bound": "hbm", "kernel": "objEmit + objFaceCount + objPositions (one thread per line)", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes": algo,
+                         "note": "text read once + records written once over the whole 12-launch parse; the parse is latency-bound byte work (one thread walks "
+                                 "one ~70-character line), far from the HBM roof - it is sized against the 3.6 ms it takes to get the text to the GPU"},
+            "cpu_baseline": {"value": nbytes / (host_ms * 1e-3) / 1e6, "unit": "MB/s", "cores": min(16, os.cpu_count() or 1), "kind": "port", "ms": host_ms,
+                             "sample": "novum_obj_parse (the product's own multi-threaded host loader = main.cu:936-1068 restated) on the same file, best of 2"}}
+    print(json.dumps(line))
+
+
+def run_obj_reference(args):
+    """The reference's own readObjSimple (single-threaded istringstream parser, main.cu:936-1068) on the same file, timed inside novum_ref."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    ref = os.path.join(REPO, "oracle", "_ref", "novum_ref")
+    sdir = scene_dir_for("dragon_nee", args.detail, 0, None)
+    path = os.path.join(sdir, "scenedata", "dragon_vrip.obj")
+    nbytes = os.path.getsize(path)
+    if not os.path.exists(ref):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/novum_ref not built on this box"}))
+        return
+    best = None
+    for i in range(max(1, min(args.steps, 3))):
+        out = subprocess.check_output([ref, "render", sdir, "--spp", "1", "--out", os.path.join(tempfile.gettempdir(), "ref.raw")], stderr=subprocess.STDOUT).decode()
+        j = json.loads(re.search(r"NOVUM_REF_JSON (\{.*\})", out).group(1))
+        if "obj_parse_s" not in j:
+            print(json.dumps({"impl": "reference", "unavailable": "novum_ref on this box predates the obj_parse_s field"}))
+            return
+        best = j["obj_parse_s"] if best is None else min(best, j["obj_parse_s"])
+    val = nbytes / best / 1e6
+    print(json.dumps({"impl": "reference", "metric": "MB/s of OBJ text", "value": val, "unit": "MB/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": best * 1e3, "higher_is_better": True, "config": {"workload": OBJ_DESC, "text_bytes": nbytes},
+                      "cpu_baseline": {"value": val, "unit": "MB/s", "cores": 1, "kind": "reference",
+                                       "sample": "readObjSimple over the scene's meshes inside novum_ref (all but 2 KB of the text is the dragon), best of up to 3 runs"},
+                      "e2e": {"value": val, "unit": "MB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
 TRACE_DESC = "ray batches on the dragon stand-in's BVH (SURVEY 8d micro): primary-like, cosine-bounce secondary and shadow rays, closest-hit / any-hit"
 
 
@@ -992,7 +1091,7 @@ def main():
     ap.add_argument("--steps", type=int, default=None, help="timed steps (default 4; frame_finish: 50 — its step is a 55 us kernel)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish", "trace_batch", "hashgrid"])
+    ap.add_argument("--workload", default="rainbow_vcm", choices=sorted(WORKLOADS) + ["frame_finish", "trace_batch", "hashgrid", "obj_parse"])
     ap.add_argument("--grid-small", action="store_true", help="hashgrid: one 200k-photon case (used by the GPU test suite)")
     ap.add_argument("--grid-full", action="store_true", help="hashgrid: add the 82.9 M-photon worst case of a 4K VCM iteration")
     ap.add_argument("--rays-side", type=int, default=2048, help="trace_batch: the primary batch is rays_side^2 rays (2048 -> 4.19 M)")
@@ -1007,13 +1106,15 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.steps is None:
-        args.steps = 50 if (args.workload in ("frame_finish", "trace_batch") and args.impl == "ours") else 4
+        args.steps = 50 if (args.workload in ("frame_finish", "trace_batch") and args.impl == "ours") else (10 if args.workload == "obj_parse" else 4)
     if args.workload == "trace_batch":
         run_trace(args)
     elif args.workload == "hashgrid":
         run_grid(args)
     elif args.workload == "frame_finish":
         (run_frame_reference if args.impl == "reference" else run_frame)(args)
+    elif args.workload == "obj_parse":
+        (run_obj_reference if args.impl == "reference" else run_obj)(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

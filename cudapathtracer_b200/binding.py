@@ -150,6 +150,8 @@ def _declare(L):
     L.novum_obj_device_destroy.restype = None
     L.novum_obj_device_append_file.argtypes = [vp, C.c_char_p, C.POINTER(cf * 3), ci, cf]
     L.novum_obj_device_append_text.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(cf * 3), ci, cf]
+    L.novum_obj_device_append_device_text.argtypes = [vp, vp, C.c_size_t, C.POINTER(cf * 3), ci, cf]
+    L.novum_obj_device_reset.argtypes = [vp]
     L.novum_obj_device_counts.argtypes = [vp] + [C.POINTER(ci)] * 5
     L.novum_obj_device_arrays.argtypes = [vp] + [C.POINTER(vp)] * 4
     L.novum_obj_device_download.argtypes = [vp, vp, vp, vp, vp]
@@ -394,6 +396,14 @@ class ObjDeviceMesh:
         e = (C.c_float * 3)(*[float(x) for x in emission])
         text = bytes(text)
         _check(lib().novum_obj_device_append_text(self.h, text, len(text), C.byref(e), int(material_id), float(y_offset)), "novum_obj_device_append_text")
+
+    def append_device_text(self, d_text, nbytes, emission=(0.0, 0.0, 0.0), material_id=0, y_offset=0.0):
+        e = (C.c_float * 3)(*[float(x) for x in emission])
+        _check(lib().novum_obj_device_append_device_text(self.h, C.c_void_p(int(d_text)), int(nbytes), C.byref(e), int(material_id), float(y_offset)),
+               "novum_obj_device_append_device_text")
+
+    def reset(self):
+        _check(lib().novum_obj_device_reset(self.h), "novum_obj_device_reset")
 
     def counts(self):
         n = [C.c_int() for _ in range(5)]

@@ -187,29 +187,48 @@ void freeBvh8(Bvh8Device& b) {
 cudaError_t buildBvh8(const float4* d_positions, const NovumTriangle* d_tris, int n, const DMat* d_mats,
                       cudaStream_t stream, Bvh8Device& out) {
     if (n <= 0) return cudaErrorInvalidValue;
-    cudaEvent_t ev0, ev1;
-    NV_CK(cudaEventCreate(&ev0)); NV_CK(cudaEventCreate(&ev1));
+    // everything the build owns for its duration, released on every way out (an early error return used to leak all of it)
+    struct Owned {
+        cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+        char* arena = nullptr;
+        RadixSortPlan plan; bool planMade = false;
+        ~Owned() {
+            if (ev0) cudaEventDestroy(ev0);
+            if (ev1) cudaEventDestroy(ev1);
+            if (planMade) radixSortPlanDestroy(plan);
+            cudaFree(arena);
+        }
+    } own;
+    NV_CK(cudaEventCreate(&own.ev0)); NV_CK(cudaEventCreate(&own.ev1));
+    cudaEvent_t ev0 = own.ev0, ev1 = own.ev1;
     NV_CK(cudaEventRecord(ev0, stream));
     int launches = 0;
     float4 *triLo, *triHi, *nodeLo, *nodeHi;
     uint32_t *bounds, *keys, *vals;
     int *left, *right, *parent, *rfirst, *rlast, *flags, *counters;
     uint2 *tasksA, *tasksB;
-    const int numB2 = 2 * n - 1;
-    NV_CK(cudaMalloc(&triLo, sizeof(float4) * n)); NV_CK(cudaMalloc(&triHi, sizeof(float4) * n));
-    NV_CK(cudaMalloc(&nodeLo, sizeof(float4) * numB2)); NV_CK(cudaMalloc(&nodeHi, sizeof(float4) * numB2));
-    NV_CK(cudaMalloc(&bounds, 18 * sizeof(uint32_t)));
-    NV_CK(cudaMalloc(&keys, sizeof(uint32_t) * n)); NV_CK(cudaMalloc(&vals, sizeof(uint32_t) * n));
-    int ni = n > 1 ? n - 1 : 1;
-    NV_CK(cudaMalloc(&left, sizeof(int) * ni)); NV_CK(cudaMalloc(&right, sizeof(int) * ni));
-    NV_CK(cudaMalloc(&rfirst, sizeof(int) * ni)); NV_CK(cudaMalloc(&rlast, sizeof(int) * ni));
-    NV_CK(cudaMalloc(&flags, sizeof(int) * ni));
-    NV_CK(cudaMalloc(&parent, sizeof(int) * numB2));
-    NV_CK(cudaMalloc(&counters, 4 * sizeof(int)));
-    NV_CK(cudaMalloc(&tasksA, sizeof(uint2) * n)); NV_CK(cudaMalloc(&tasksB, sizeof(uint2) * n));
     float4* nodesTmp; float4* trisOut;
-    NV_CK(cudaMalloc(&nodesTmp, sizeof(float4) * 5 * (size_t)n));
-    NV_CK(cudaMalloc(&trisOut, sizeof(float4) * 3 * (size_t)n));
+    const int numB2 = 2 * n - 1;
+    const int ni = n > 1 ? n - 1 : 1;
+    // ONE allocation for the scratch arrays (18 separate cudaMalloc calls before): carved in 256 B steps
+    size_t arenaBytes = 0;
+    auto carve = [&](size_t bytes) { const size_t at = arenaBytes; arenaBytes += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t oTriLo = carve(sizeof(float4) * n), oTriHi = carve(sizeof(float4) * n);
+    const size_t oNodeLo = carve(sizeof(float4) * numB2), oNodeHi = carve(sizeof(float4) * numB2);
+    const size_t oBounds = carve(18 * sizeof(uint32_t));
+    const size_t oKeys = carve(sizeof(uint32_t) * n), oVals = carve(sizeof(uint32_t) * n);
+    const size_t oLeft = carve(sizeof(int) * ni), oRight = carve(sizeof(int) * ni), oRfirst = carve(sizeof(int) * ni), oRlast = carve(sizeof(int) * ni);
+    const size_t oFlags = carve(sizeof(int) * ni), oParent = carve(sizeof(int) * numB2), oCounters = carve(4 * sizeof(int));
+    const size_t oTasksA = carve(sizeof(uint2) * n), oTasksB = carve(sizeof(uint2) * n);
+    const size_t oNodesTmp = carve(sizeof(float4) * 5 * (size_t)n), oTrisOut = carve(sizeof(float4) * 3 * (size_t)n);
+    NV_CK(cudaMalloc((void**)&own.arena, arenaBytes));
+    char* const A = own.arena;
+    triLo = (float4*)(A + oTriLo); triHi = (float4*)(A + oTriHi); nodeLo = (float4*)(A + oNodeLo); nodeHi = (float4*)(A + oNodeHi);
+    bounds = (uint32_t*)(A + oBounds); keys = (uint32_t*)(A + oKeys); vals = (uint32_t*)(A + oVals);
+    left = (int*)(A + oLeft); right = (int*)(A + oRight); rfirst = (int*)(A + oRfirst); rlast = (int*)(A + oRlast);
+    flags = (int*)(A + oFlags); parent = (int*)(A + oParent); counters = (int*)(A + oCounters);
+    tasksA = (uint2*)(A + oTasksA); tasksB = (uint2*)(A + oTasksB);
+    nodesTmp = (float4*)(A + oNodesTmp); trisOut = (float4*)(A + oTrisOut);
     NV_CK(cudaMemsetAsync(parent, 0xff, sizeof(int) * numB2, stream));
     NV_CK(cudaMemsetAsync(flags, 0, sizeof(int) * ni, stream));
 
@@ -218,9 +237,9 @@ cudaError_t buildBvh8(const float4* d_positions, const NovumTriangle* d_tris, in
     triBoundsKernel<<<G, T, 0, stream>>>(d_positions, d_tris, n, triLo, triHi, bounds);
     mortonKernel<<<G, T, 0, stream>>>(triLo, triHi, n, bounds, keys, vals);
     launches += 3;
-    RadixSortPlan plan;
-    NV_CK(radixSortPlanCreate(plan, n));
-    NV_CK(radixSortPairs(plan, keys, vals, n, 30, stream, &launches));
+    NV_CK(radixSortPlanCreate(own.plan, n));
+    own.planMade = true;
+    NV_CK(radixSortPairs(own.plan, keys, vals, n, 30, stream, &launches));
     if (n > 1) {
         radixTreeKernel<<<(n - 1 + T - 1) / T, T, 0, stream>>>(keys, n, left, right, parent, rfirst, rlast);
         ++launches;
@@ -266,11 +285,6 @@ cudaError_t buildBvh8(const float4* d_positions, const NovumTriangle* d_tris, in
     for (int k = 0; k < 3; ++k) { out.boundsMin[k] = decF(hb[12 + k]) - 0.000001f; out.boundsMax[k] = decF(hb[15 + k]) + 0.000001f; }
     cudaEventElapsedTime(&out.buildMs, ev0, ev1);
     out.kernelLaunches = launches; out.levels = levels;
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
-    radixSortPlanDestroy(plan);
-    cudaFree(triLo); cudaFree(triHi); cudaFree(nodeLo); cudaFree(nodeHi); cudaFree(bounds); cudaFree(keys); cudaFree(vals);
-    cudaFree(left); cudaFree(right); cudaFree(parent); cudaFree(rfirst); cudaFree(rlast); cudaFree(flags); cudaFree(counters);
-    cudaFree(tasksA); cudaFree(tasksB); cudaFree(nodesTmp); cudaFree(trisOut);
     return cudaGetLastError();
 }
 

@@ -635,6 +635,12 @@ int novum_scene_load_config(const char* configPath, int renderNumber, NovumScene
         novum_obj_device_counts(dm, nullptr, nullptr, nullptr, &nTri, nullptr);
         if (ok && nTri > 0) {
             const float parseMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - parseT0).count();
+            if (getenv("NOVUM_OBJ_TIMING")) {
+                float up = 0.f, k = 0.f; int l = 0; long long b = 0;
+                novum_obj_device_timings(dm, &up, &k, &l, &b);
+                fprintf(stderr, "device OBJ front end: %.1f ms for %lld bytes (read + copy %.1f ms, kernels %.2f ms in %d launches; the rest is allocation)\n",
+                        parseMs, b, up, k, l);
+            }
             rc = novum_scene_from_obj_device(dm, mats, 24, texels.data(), (int)texels.size(), out);
             novum_obj_device_destroy(dm);
             if (rc == 0) for (const MeshCfg& m : meshes) (*out)->meshPaths.push_back(m.path);

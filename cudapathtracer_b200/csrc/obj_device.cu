@@ -296,6 +296,7 @@ struct ObjDeviceMesh {
     float uploadMs = 0.f, parseMs = 0.f;                   // wall time of reading + copying the text; CUDA-event time of the kernels
     int launches = 0;
     size_t textBytes = 0;
+    char* scratch[3] = {nullptr, nullptr, nullptr}; size_t scratchCap[3] = {0, 0, 0};   // tile counts + counters | per-line arrays | text: kept across files
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
@@ -320,11 +321,23 @@ static int objParseText(ObjDeviceMesh& M, const char* d_text, uint32_t bytes, co
     cudaStream_t s = M.stream;
     cudaError_t e;
     const int nTiles = (int)((bytes + kObjTileBytes - 1) / kObjTileBytes);
+    auto scratch = [&](int k, size_t bytes, void** out) -> int {        // the mesh keeps its two scratch buffers (grown by half when too small)
+        if (bytes > M.scratchCap[k]) {
+            cudaFree(M.scratch[k]); M.scratch[k] = nullptr; M.scratchCap[k] = 0;
+            const size_t want = bytes + bytes / 2;
+            cudaError_t a = cudaMalloc((void**)&M.scratch[k], want);
+            if (a != cudaSuccess) return (int)a;
+            M.scratchCap[k] = want;
+        }
+        *out = M.scratch[k];
+        return 0;
+    };
     int* d_tile = nullptr;             // [nTiles] ints, then the counters
-    if ((e = cudaMalloc((void**)&d_tile, sizeof(int) * (size_t)nTiles + sizeof(ObjCounters) + 16)) != cudaSuccess) return (int)e;
+    int rc = scratch(0, sizeof(int) * (size_t)nTiles + sizeof(ObjCounters) + 16, (void**)&d_tile);
+    if (rc) return rc;
     ObjCounters* d_cnt = reinterpret_cast<ObjCounters*>(d_tile + ((nTiles + 3) & ~3));
     char* d_lines = nullptr;           // lineStart | lineCounts | block arrays | types
-    auto fail = [&](int rc) { cudaStreamSynchronize(s); cudaFree(d_tile); cudaFree(d_lines); return rc; };
+    auto fail = [&](int code) { cudaStreamSynchronize(s); return code; };
     ObjCounters h{};
     h.firstZeroLine = kObjNoLine;
     cudaMemcpyAsync(d_cnt, &h, sizeof(h), cudaMemcpyHostToDevice, s);
@@ -338,7 +351,7 @@ static int objParseText(ObjDeviceMesh& M, const char* d_text, uint32_t bytes, co
     const int nBlocks = (int)((numLines + kObjLineThreads - 1) / kObjLineThreads);
     const size_t offCounts = sizeof(uint32_t) * ((numLines + 1 + 3) & ~(size_t)3), offBlocks = offCounts + sizeof(uint32_t) * ((numLines + 3) & ~(size_t)3),
                  offTypes = offBlocks + sizeof(int) * 4 * (size_t)((nBlocks + 3) & ~3);
-    if ((e = cudaMalloc((void**)&d_lines, offTypes + numLines + 16)) != cudaSuccess) return fail((int)e);
+    if ((rc = scratch(1, offTypes + numLines + 16, (void**)&d_lines))) return fail(rc);
     uint32_t* d_lineStart = reinterpret_cast<uint32_t*>(d_lines);
     uint32_t* d_lineCounts = reinterpret_cast<uint32_t*>(d_lines + offCounts);
     int* d_blockPos = reinterpret_cast<int*>(d_lines + offBlocks);
@@ -351,8 +364,7 @@ static int objParseText(ObjDeviceMesh& M, const char* d_text, uint32_t bytes, co
     cudaMemcpyAsync(&h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, s);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail((int)e);
     if ((long long)M.nPos + h.nPos > 0x7fffffffLL) return fail(NOVUM_E_UNSUPPORTED);
-    int rc = objGrow(M.pos, M.capPos, (size_t)M.nPos, (size_t)M.nPos + (size_t)h.nPos, s);
-    if (rc) return fail(rc);
+    if ((rc = objGrow(M.pos, M.capPos, (size_t)M.nPos, (size_t)M.nPos + (size_t)h.nPos, s))) return fail(rc);
     objPositions<<<nBlocks, kObjLineThreads, 0, s>>>(L, d_types, d_blockPos, M.nPos, yOffset, M.pos, d_cnt);
     objFaceCount<<<nBlocks, kObjLineThreads, 0, s>>>(L, d_types, d_blockPos, M.nPos, M.pos, d_lineCounts, d_blockNrm, d_blockUv, d_blockTri, d_cnt);
     objScanInts<<<1, 1024, 0, s>>>(d_blockNrm, nBlocks, &d_cnt->nNrm, 0);
@@ -385,16 +397,20 @@ static int objParseText(ObjDeviceMesh& M, const char* d_text, uint32_t bytes, co
     M.parseMs += ms; M.launches += 12;
     if (isLight && h.nTri > 0) { M.lightRanges.push_back({M.nTri, h.nTri}); M.numLights += h.nTri; }
     M.nPos += h.nPos; M.nNrm += h.nNrm; M.nUv += addUv; M.nTri += h.nTri;
-    cudaFree(d_tile); cudaFree(d_lines);
     return 0;
 }
 
-// device buffer for `bytes` of text, padded with NUL to whole tiles (the kernels read 16 B words and whole tiles)
-static int objAllocText(size_t bytes, char** d_text, cudaStream_t s) {
+// device buffer for `bytes` of text, padded with NUL to whole tiles (the kernels read 16 B words and whole tiles); the mesh keeps it
+static int objAllocText(ObjDeviceMesh& M, size_t bytes, char** d_text) {
     const size_t padded = (bytes + kObjTileBytes - 1) / kObjTileBytes * kObjTileBytes + 16;
-    cudaError_t e = cudaMalloc((void**)d_text, padded);
-    if (e != cudaSuccess) return (int)e;
-    cudaMemsetAsync(*d_text + bytes, 0, padded - bytes, s);
+    if (padded > M.scratchCap[2]) {
+        cudaFree(M.scratch[2]); M.scratch[2] = nullptr; M.scratchCap[2] = 0;
+        cudaError_t e = cudaMalloc((void**)&M.scratch[2], padded + padded / 8);
+        if (e != cudaSuccess) return (int)e;
+        M.scratchCap[2] = padded + padded / 8;
+    }
+    *d_text = M.scratch[2];
+    cudaMemsetAsync(*d_text + bytes, 0, padded - bytes, M.stream);
     return 0;
 }
 
@@ -423,7 +439,7 @@ static int objUploadFile(ObjDeviceMesh& M, const char* path, char** d_text, size
                 if (cudaHostAlloc((void**)&g_objStaging.buf[r][k], kObjPiece, cudaHostAllocPortable) != cudaSuccess) { close(fd); return NOVUM_E_IO; }
         g_objStaging.ready = true;
     }
-    int rc = objAllocText(sz, d_text, M.stream);
+    int rc = objAllocText(M, sz, d_text);
     if (rc) { close(fd); return rc; }
     const int nPieces = (int)((sz + kObjPiece - 1) / kObjPiece);
     const int readers = std::max(1, std::min(kObjReaders, std::min(nPieces, (int)std::thread::hardware_concurrency())));
@@ -458,7 +474,7 @@ static int objUploadFile(ObjDeviceMesh& M, const char* path, char** d_text, size
     work(0);
     for (std::thread& t : pool) t.join();
     close(fd);
-    if (bad.load()) { cudaStreamSynchronize(M.stream); cudaFree(*d_text); *d_text = nullptr; return bad.load() == 1 ? NOVUM_E_IO : (int)cudaGetLastError(); }
+    if (bad.load()) { cudaStreamSynchronize(M.stream); *d_text = nullptr; return bad.load() == 1 ? NOVUM_E_IO : (int)cudaGetLastError(); }
     M.uploadMs += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     M.textBytes += sz;
     return 0;
@@ -473,7 +489,8 @@ static int objMeshInit(ObjDeviceMesh& M) {
     return 0;
 }
 static void objMeshRelease(ObjDeviceMesh& M) {
-    cudaFree(M.pos); cudaFree(M.nrm); cudaFree(M.uv); cudaFree(M.tris);
+    cudaFree(M.pos); cudaFree(M.nrm); cudaFree(M.uv); cudaFree(M.tris); cudaFree(M.scratch[0]); cudaFree(M.scratch[1]); cudaFree(M.scratch[2]);
+    for (int k = 0; k < 3; ++k) { M.scratch[k] = nullptr; M.scratchCap[k] = 0; }
     M.pos = M.nrm = nullptr; M.uv = nullptr; M.tris = nullptr;
     if (M.ev0) { cudaEventDestroy(M.ev0); cudaEventDestroy(M.ev1); M.ev0 = M.ev1 = nullptr; }
     if (M.stream) { cudaStreamDestroy(M.stream); M.stream = nullptr; }
@@ -483,24 +500,33 @@ int objAppendFile(ObjDeviceMesh& M, const char* path, const float emission[3], i
     char* d_text = nullptr; size_t bytes = 0;
     int rc = objUploadFile(M, path, &d_text, &bytes);
     if (rc || bytes == 0) return rc;
-    rc = objParseText(M, d_text, (uint32_t)bytes, emission, materialID, yOffset);
-    cudaFree(d_text);
-    return rc;
+    return objParseText(M, d_text, (uint32_t)bytes, emission, materialID, yOffset);
 }
 
 int objAppendText(ObjDeviceMesh& M, const char* text, size_t bytes, const float emission[3], int materialID, float yOffset) {
     if (bytes == 0) return 0;
     if (bytes >= 0x7fffff00ull) return NOVUM_E_UNSUPPORTED;
     char* d_text = nullptr;
-    int rc = objAllocText(bytes, &d_text, M.stream);
+    int rc = objAllocText(M, bytes, &d_text);
     if (rc) return rc;
     cudaError_t e = cudaMemcpyAsync(d_text, text, bytes, cudaMemcpyHostToDevice, M.stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(M.stream);
-    if (e != cudaSuccess) { cudaFree(d_text); return (int)e; }
+    if (e != cudaSuccess) return (int)e;
     M.textBytes += bytes;
-    rc = objParseText(M, d_text, (uint32_t)bytes, emission, materialID, yOffset);
-    cudaFree(d_text);
-    return rc;
+    return objParseText(M, d_text, (uint32_t)bytes, emission, materialID, yOffset);
+}
+
+// text that already lives in device memory: copied once more into a buffer padded to whole tiles (the caller's buffer may end anywhere)
+int objAppendDeviceText(ObjDeviceMesh& M, const char* d_src, size_t bytes, const float emission[3], int materialID, float yOffset) {
+    if (bytes == 0) return 0;
+    if (bytes >= 0x7fffff00ull) return NOVUM_E_UNSUPPORTED;
+    char* d_text = nullptr;
+    int rc = objAllocText(M, bytes, &d_text);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpyAsync(d_text, d_src, bytes, cudaMemcpyDeviceToDevice, M.stream);
+    if (e != cudaSuccess) { cudaStreamSynchronize(M.stream); return (int)e; }
+    M.textBytes += bytes;
+    return objParseText(M, d_text, (uint32_t)bytes, emission, materialID, yOffset);
 }
 
 }  // namespace nv
@@ -535,6 +561,21 @@ int novum_obj_device_append_text(NovumObjDeviceMesh* m, const char* text, size_t
     if (!m || (!text && bytes)) return NOVUM_E_ARG;
     const float zero[3] = {0.f, 0.f, 0.f};
     return nv::objAppendText(m->M, text, bytes, emission ? emission : zero, materialID, yOffset);
+}
+
+int novum_obj_device_append_device_text(NovumObjDeviceMesh* m, const char* d_text, size_t bytes, const float emission[3], int materialID, float yOffset) {
+    if (!m || (!d_text && bytes)) return NOVUM_E_ARG;
+    const float zero[3] = {0.f, 0.f, 0.f};
+    return nv::objAppendDeviceText(m->M, d_text, bytes, emission ? emission : zero, materialID, yOffset);
+}
+
+int novum_obj_device_reset(NovumObjDeviceMesh* m) {
+    if (!m) return NOVUM_E_ARG;
+    nv::ObjDeviceMesh& M = m->M;
+    M.nPos = M.nNrm = M.nUv = M.nTri = M.numLights = 0;
+    M.lightRanges.clear();
+    M.uploadMs = M.parseMs = 0.f; M.launches = 0; M.textBytes = 0;
+    return 0;
 }
 
 int novum_obj_device_counts(const NovumObjDeviceMesh* m, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights) {
@@ -595,6 +636,8 @@ int novum_scene_from_obj_device(NovumObjDeviceMesh* m, const NovumMaterial* mats
         if (e != cudaSuccess) return (int)e;
         if (bad) return NOVUM_E_ARG;
     }
+    // the parser's text and scratch buffers go back to the driver before the BVH8 build asks for its own scratch
+    for (int k = 0; k < 3; ++k) { cudaFree(M.scratch[k]); M.scratch[k] = nullptr; M.scratchCap[k] = 0; }
     NovumScene* s = new NovumScene();
     s->nPos = M.nPos; s->nNorm = M.nNrm; s->nUV = M.nUv; s->nTri = M.nTri; s->nMat = nMat; s->nTexels = nTexels; s->nLights = M.numLights;
     // the scene takes the mesh's arrays over (the mesh is empty afterwards); arrays a file never filled get the 16 B the upload path gives them

@@ -245,6 +245,10 @@ void novum_obj_device_destroy(NovumObjDeviceMesh* m);
 int  novum_obj_device_append_file(NovumObjDeviceMesh* m, const char* path, const float emission[3], int materialID, float yOffset);
 /* the same for text that is already in (host) memory */
 int  novum_obj_device_append_text(NovumObjDeviceMesh* m, const char* text, size_t bytes, const float emission[3], int materialID, float yOffset);
+/* the same for text that is already in DEVICE memory (copied once into a padded buffer of the parser's own) */
+int  novum_obj_device_append_device_text(NovumObjDeviceMesh* m, const char* d_text, size_t bytes, const float emission[3], int materialID, float yOffset);
+/* empties the mesh but keeps its device memory (arrays and scratch) for the next files; timings restart at zero */
+int  novum_obj_device_reset(NovumObjDeviceMesh* m);
 int  novum_obj_device_counts(const NovumObjDeviceMesh* m, int* nPos, int* nNorm, int* nUV, int* nTri, int* nLights);
 /* DEVICE pointers to the accumulated arrays (valid until the next append / destroy / novum_scene_from_obj_device) */
 int  novum_obj_device_arrays(const NovumObjDeviceMesh* m, const NovumFloat4** d_positions, const NovumFloat4** d_normals,

@@ -99,8 +99,8 @@ static int cmdRender(int argc, char** argv) {
     cudaMemcpyFromSymbol(rayCnt, g_refRayCounters, sizeof(rayCnt));
 #endif
     printf("\nNOVUM_REF_JSON {\"integrator\": \"%s\", \"w\": %d, \"h\": %d, \"spp\": %d, \"tris\": %d, \"lights\": %d, \"bvh_nodes\": %d, "
-           "\"launch_ms\": %.3f, \"launch_ms_each\": %s, \"launch_wall_s\": %.4f, \"bvh_build_s\": %.4f, \"closest_rays\": %llu, \"shadow_rays\": %llu, \"cuda_error\": %d}\n",
-           config.integratorType.c_str(), w, h, config.sampleCount, nt, nl, (int)S.bvh.size(), ms, eachMs.c_str(), wall, S.buildSeconds, rayCnt[0], rayCnt[1], (int)err);
+           "\"launch_ms\": %.3f, \"launch_ms_each\": %s, \"launch_wall_s\": %.4f, \"bvh_build_s\": %.4f, \"obj_parse_s\": %.4f, \"closest_rays\": %llu, \"shadow_rays\": %llu, \"cuda_error\": %d}\n",
+           config.integratorType.c_str(), w, h, config.sampleCount, nt, nl, (int)S.bvh.size(), ms, eachMs.c_str(), wall, S.buildSeconds, S.parseSeconds, rayCnt[0], rayCnt[1], (int)err);
     return err == cudaSuccess ? 0 : 2;
 }
 

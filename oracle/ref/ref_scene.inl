@@ -16,6 +16,7 @@ struct RefScene {
     float4 sceneCenter, sceneMin; float sceneRadius;
     Material* mats_d; float4* textures_d; Vertices* verts_d; Vertices tmp; Triangle *scene_d, *lights_d; BVHnode* BVH_d; int* BVHindices_d;
     double buildSeconds;
+    double parseSeconds;      // the reference's readObjSimple over the config's meshes (main.cu:474-482)
 };
 
 static int buildRefScene(RefScene& S, int sppOverride) {
@@ -74,8 +75,10 @@ static int buildRefScene(RefScene& S, int sppOverride) {
     cudaMemcpy(S.mats_d, mats.data(), mats.size() * sizeof(Material), cudaMemcpyHostToDevice);
     cudaMalloc(&S.textures_d, pixels.size() * sizeof(float4) + 16);
     cudaMemcpy(S.textures_d, pixels.data(), pixels.size() * sizeof(float4), cudaMemcpyHostToDevice);
+    auto tParse = std::chrono::high_resolution_clock::now();
     for (MeshConfig c : config.meshes)      // main.cu:474-482 (render number 0: no light offset)
         readObjSimple(c.path, S.points, S.normals, S.colors, S.uvs, S.mesh, S.lightsvec, f4(), c.emissionMultiplier * c.emissionColor, c.materialID);
+    S.parseSeconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - tParse).count();
     if (S.mesh.empty()) return 2;
     S.colors.assign(S.points.size(), f4());        // the reference leaves `colors` empty and reads it out of bounds (dead code after DCE)
     cudaMalloc(&S.verts_d, sizeof(Vertices));
