@@ -339,7 +339,7 @@ def run_ours(args):
         sm_hz = (clk["sm_mhz"] if clk and clk.get("sm_mhz") else 1965) * 1e6
         issue_peak = 148 * 4 * sm_hz                                         # warp instructions per second
         pairs_s = merge_cand / (eff_ms[3] * 1e-3)
-        m = {"bound": "issue", "kernel": "bdMergeLambert + bdMerge (photon gather over 27 hash-grid cells)", "pairs_per_s": pairs_s,
+        m = {"bound": "issue", "kernel": "bdMergeLambert + bdMerge (photon gather over the reachable r/2 hash-grid cells of a 4-vertex group)", "pairs_per_s": pairs_s,
              "photons_scanned_per_query": merge_cand / merge_q, "photons_merged_per_query": merge_acc / merge_q,
              "scanned_per_merged": merge_cand / max(1, merge_acc), "ms_share": stage_ms[3] / ssum,
              "issue_peak_warp_inst_per_s": issue_peak}

@@ -692,8 +692,9 @@ constexpr int kMergeFine = 2;
 constexpr int kMergeReach = kMergeFine;                       // cells on either side of the vertex's own cell
 constexpr int kMergeSide = 2 * kMergeReach + 1;               // 5
 constexpr int kMergeNbr = kMergeSide * kMergeSide * kMergeSide;   // 125
-constexpr int kMergeMaxBox = 512;                             // largest cell box a group of vertices may span and still be gathered together
+constexpr int kMergeMaxBox = 256;                             // largest cell box a group of vertices may span and still be gathered together
 constexpr int kMergeMaxList = kMergeMaxBox;
+constexpr int kMergeSeen = 2 * kMergeMaxBox;                  // slots of the per-warp set of ranges already listed (load factor <= 1/2)
 
 // squared distance from p to the box of cell c (slightly shrunk distances: 1e-4 cell of slack absorbs the rounding of the cell function,
 // nothing within r is ever dropped)
@@ -740,9 +741,11 @@ NV_D void mergeSplat(const BdParams& P, int pix, V3 sum, int lane) {
 //   list    the cells of the box spanned by the G neighbourhoods are enumerated across the lanes (distinct cells by construction);
 //           a cell is kept if its box comes within reach of the group (one sphere around the group: centre = mean vertex, radius =
 //           r + largest offset) and its table slot is not empty; kept cells are appended to a shared-memory list with ballot / popc,
-//           together with the running sum of their photon counts. Two distinct cells that collide in the hash table within one round
-//           of 32 are listed once; across rounds a colliding slot is swept twice, as the reference sweeps it once per colliding
-//           neighbour (deviceCode.cu:2968-2995; ~1e-6 of the pairs).
+//           together with the running sum of their photon counts. Two distinct cells of the box that collide in the hash table name
+//           the same photon range: a range is listed ONCE per group (a small open-addressing set of range starts in shared memory,
+//           claimed with atomicCAS), so that no photon is merged twice into a vertex. (The reference sweeps a colliding slot once per
+//           colliding neighbour, deviceCode.cu:2968-2995, and so counts those photons twice; with 125 r/2-cells per neighbourhood
+//           instead of 27 r-cells that would no longer be a 1e-6 effect on small scenes, whose tables are small.)
 //   sweep   the listed ranges are walked as ONE sequence: candidate j of the group belongs to lane j % 32, which finds its range by
 //           advancing a pointer through the prefix sums - every trip is a full warp whatever the sizes of the cells (per-cell strides
 //           left the last trip of each cell partly empty, which matters once cells hold ~40 photons instead of ~170).
@@ -758,8 +761,10 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
     const PhotonSoA ph = P.photons;
     const unsigned ltMask = (1u << lane) - 1u;
     __shared__ uint2 listAll[kMergeWarps][kMergeMaxList + 1];         // {first photon - candidates listed before this range, candidates listed up to its end}
+    __shared__ uint32_t seenAll[kMergeWarps][kMergeSeen];            // first photon of every range listed for the current group (0xFFFFFFFF = free)
     __shared__ float4 vtxAll[kMergeWarps][kMergeGather];             // {n/pi, 1 + d_vcm/eta + eyeRev * d_vm} of the gathered vertices: warp-uniform, read where a photon is accepted
     uint2* list = listAll[threadIdx.x >> 5];
+    uint32_t* seen = seenAll[threadIdx.x >> 5];
     float4* vtx = vtxAll[threadIdx.x >> 5];
     // shared-memory addresses kept in registers (the asm keeps the compiler from recomputing them from %tid at every use in the sweep)
     uint32_t listAddr, vtxAddr;
@@ -830,13 +835,15 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
             // ---- list ----
             uint32_t total = 0;
             int m = 0;
+#pragma unroll
+            for (int k = 0; k < kMergeSeen / 128; ++k) reinterpret_cast<uint4*>(seen)[lane + 32 * k] = make_uint4(~0u, ~0u, ~0u, ~0u);
             __syncwarp();
 #pragma unroll 1
             for (int i0 = 0; i0 < nCells; i0 += 32) {
                 const int i = i0 + lane;
                 uint32_t cs = 0u, cc = 0u;
                 if (i < nCells) {
-                    const int cz = (int)(((float)i + 0.5f) * invXY), rem = i - cz * nxy;          // exact: i < 512
+                    const int cz = (int)(((float)i + 0.5f) * invXY), rem = i - cz * nxy;          // exact: i < 256
                     const int cy = (int)(((float)rem + 0.5f) * invX), cx = rem - cy * nx;
                     if (cellDist2(P.grid, bx0 + cx, by0 + cy, bz0 + cz, ctr) <= reach2) {
                         const unsigned hsh = hashCellMagic(bx0 + cx, by0 + cy, bz0 + cz, P.grid.tableSize, P.gridMagic);
@@ -844,8 +851,16 @@ __global__ void __launch_bounds__(kMergeThreads, MINB) bdMergeLambert(SceneView 
                         if (s0 != 0xFFFFFFFFu) { cs = s0; cc = __ldg(P.cellEnd + hsh) - s0; }
                     }
                 }
-                // two cells of this round in one table slot: listed once
-                if (cc && (__match_any_sync(__activemask(), cs) & ltMask)) cc = 0u;
+                if (cc) {      // claim the range for this group: listed once however many cells of the box share its table slot
+                    uint32_t at = (cs * 2654435761u) >> (32 - 9);
+                    static_assert(kMergeSeen == 512, "9 hash bits");
+                    while (true) {
+                        const uint32_t old = atomicCAS(seen + at, 0xFFFFFFFFu, cs);
+                        if (old == 0xFFFFFFFFu) break;
+                        if (old == cs) { cc = 0u; break; }
+                        at = (at + 1u) & (kMergeSeen - 1);
+                    }
+                }
                 const unsigned keep = __ballot_sync(0xffffffffu, cc != 0u);
                 uint32_t x = cc;                                                                // inclusive scan of the counts
 #pragma unroll
