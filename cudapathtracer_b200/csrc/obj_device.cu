@@ -436,7 +436,11 @@ static int objUploadFile(ObjDeviceMesh& M, const char* path, char** d_text, size
     if (!g_objStaging.ready) {
         for (int r = 0; r < kObjReaders; ++r)
             for (int k = 0; k < 2; ++k)
-                if (cudaHostAlloc((void**)&g_objStaging.buf[r][k], kObjPiece, cudaHostAllocPortable) != cudaSuccess) { close(fd); return NOVUM_E_IO; }
+                if (!g_objStaging.buf[r][k]) {
+                    // not NOVUM_E_IO: the caller takes that for "no such file" and tries the next path (a positive code sends it to the host loader)
+                    const cudaError_t pe = cudaHostAlloc((void**)&g_objStaging.buf[r][k], kObjPiece, cudaHostAllocPortable);
+                    if (pe != cudaSuccess) { g_objStaging.buf[r][k] = nullptr; close(fd); return (int)pe; }
+                }
         g_objStaging.ready = true;
     }
     int rc = objAllocText(M, sz, d_text);
